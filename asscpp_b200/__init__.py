@@ -1,0 +1,262 @@
+"""asscpp_b200 -- B200-native viewpoint coverage evaluation (frustum cull -> 3D-DDA occlusion ->
+coverage gain), the data-parallel hot path of kucars/asscpp.
+
+The product is the C-ABI library `asscpp_b200/lib/libasscpp_b200.so` (include/asscpp_gpu.h) and the
+C++ shim of the reference's OcclusionCulling class (include/cscpp/occlusion_culling.h).  This Python
+package is a thin ctypes mirror used by the tests, the benchmark and Python callers; it adds no
+compute of its own and has no fallback when the CUDA library is absent.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from ._abi import (EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, RESULT_DTYPE, VS_GRID_GLOBAL, VS_GRID_SHARED,
+                   VS_ORDERED, ModelInfo, Params)
+
+__all__ = [
+    "CoverageContext", "CoveredSet", "AsscppError", "default_params", "synth_structure", "synth_views",
+    "robot2sensor", "frustum_planes", "EVAL_HASH", "EVAL_BRUTE", "EVAL_FORCE_GLOBAL", "RESULT_DTYPE",
+]
+
+SEED_STRUCTURE, SEED_POINTS, SEED_VIEWS = 0xA55C0001, 0xA55C0002, 0xA55C0003
+
+
+class AsscppError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("asscpp error %d: %s" % (code, msg))
+        self.code = code
+
+
+def _ptr(a, ty):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ty))
+
+
+def default_params(**kw):
+    """Reference literals (occlusion_culling.cpp:41,73-76; heuristic.cpp:479), overridable."""
+    p = Params()
+    _abi.load().asscpp_default_params(C.byref(p))
+    for k, v in kw.items():
+        if k == "pcd_origin":
+            p.pcd_origin[:] = v
+        else:
+            setattr(p, k, v)
+    return p
+
+
+def synth_structure(n, structure_seed=SEED_STRUCTURE, point_seed=SEED_POINTS):
+    out = np.empty((n, 3), np.float32)
+    rc = _abi.load().asscpp_synth_structure_v1(structure_seed, point_seed, n, _ptr(out, C.c_float))
+    if rc:
+        raise AsscppError(rc, "synth_structure")
+    return out
+
+
+def synth_views(nviews, structure_seed=SEED_STRUCTURE, view_seed=SEED_VIEWS):
+    out = np.empty((nviews, 7), np.float64)
+    rc = _abi.load().asscpp_synth_views_v1(structure_seed, view_seed, nviews, _ptr(out, C.c_double))
+    if rc:
+        raise AsscppError(rc, "synth_views")
+    return out
+
+
+def robot2sensor(robot_pose, offset, rpy):
+    """sspp/src/sensors.cpp:47-90."""
+    rp = np.ascontiguousarray(robot_pose, np.float64)
+    off = np.ascontiguousarray(offset, np.float64)
+    r = np.ascontiguousarray(rpy, np.float64)
+    out = np.zeros(7, np.float64)
+    rc = _abi.load().asscpp_robot2sensor(_ptr(rp, C.c_double), _ptr(off, C.c_double), _ptr(r, C.c_double),
+                                         _ptr(out, C.c_double))
+    if rc:
+        raise AsscppError(rc, "robot2sensor")
+    return out
+
+
+def frustum_planes(params, pose):
+    pose = np.ascontiguousarray(pose, np.float64)
+    pl = np.zeros(24, np.float32)
+    o = np.zeros(3, np.float32)
+    rc = _abi.load().asscpp_frustum_planes(C.byref(params), _ptr(pose, C.c_double), _ptr(pl, C.c_float),
+                                           _ptr(o, C.c_float))
+    if rc:
+        raise AsscppError(rc, "frustum_planes")
+    return pl.reshape(6, 4), o
+
+
+class CoveredSet:
+    """Device-resident covered set (points + coverage voxels); Node::cloud_filtered / globalCloud."""
+
+    def __init__(self, ctx, handle):
+        self.ctx, self.handle = ctx, handle
+
+    def free(self):
+        if self.handle is not None:
+            self.ctx._ck(self.ctx.L.asscpp_covered_free(self.ctx.h, self.handle))
+            self.handle = None
+
+    def clear(self):
+        self.ctx._ck(self.ctx.L.asscpp_covered_clear(self.ctx.h, self.handle))
+
+    def clone(self):
+        out = C.c_int()
+        self.ctx._ck(self.ctx.L.asscpp_covered_clone(self.ctx.h, self.handle, C.byref(out)))
+        return CoveredSet(self.ctx, out.value)
+
+    def or_set(self, other):
+        self.ctx._ck(self.ctx.L.asscpp_covered_or_set(self.ctx.h, self.handle, other.handle))
+
+    def or_views(self, poses, min_visible=-1):
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        self.ctx._ck(self.ctx.L.asscpp_covered_or_views(self.ctx.h, self.handle, _ptr(poses, C.c_double),
+                                                        poses.shape[0], min_visible))
+
+    def or_points(self, idx):
+        idx = np.ascontiguousarray(idx, np.int32)
+        self.ctx._ck(self.ctx.L.asscpp_covered_or_points(self.ctx.h, self.handle, _ptr(idx, C.c_int32), idx.shape[0]))
+
+    def popcount(self):
+        a, b = C.c_int64(), C.c_int64()
+        self.ctx._ck(self.ctx.L.asscpp_covered_popcount(self.ctx.h, self.handle, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def export(self):
+        pts = np.zeros((self.ctx.n_points + 63) // 64, np.uint64)
+        vox = np.zeros((self.ctx.n_cov_voxels + 63) // 64, np.uint64)
+        self.ctx._ck(self.ctx.L.asscpp_covered_export(self.ctx.h, self.handle, _ptr(pts, C.c_uint64),
+                                                      _ptr(vox, C.c_uint64)))
+        return pts, vox
+
+    def load(self, point_bits, voxel_bits):
+        pts = None if point_bits is None else np.ascontiguousarray(point_bits, np.uint64)
+        vox = None if voxel_bits is None else np.ascontiguousarray(voxel_bits, np.uint64)
+        self.ctx._ck(self.ctx.L.asscpp_covered_import(self.ctx.h, self.handle, _ptr(pts, C.c_uint64),
+                                                      _ptr(vox, C.c_uint64)))
+
+    def coverage_percent(self):
+        out = C.c_float()
+        self.ctx._ck(self.ctx.L.asscpp_coverage_percent(self.ctx.h, self.handle, C.byref(out)))
+        return out.value
+
+
+class CoverageContext:
+    """One model cloud resident on one GPU (asscpp_create)."""
+
+    def __init__(self, xyz, params=None, device=0):
+        self.L = _abi.load()
+        self.params = params or default_params()
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        self.h = C.c_void_p()
+        rc = self.L.asscpp_create(device, _ptr(xyz, C.c_float), xyz.shape[0], C.byref(self.params), C.byref(self.h))
+        if rc:
+            self.h = C.c_void_p()
+            raise AsscppError(rc, (self.L.asscpp_last_error(None) or b"").decode())
+        info = ModelInfo()
+        self._ck(self.L.asscpp_model_info(self.h, C.byref(info)))
+        self.info = info
+        self.n_points, self.n_occ_voxels, self.n_cov_voxels = info.n_points, info.n_occ_voxels, info.n_cov_voxels
+        self.device = device
+
+    def _ck(self, rc):
+        if rc:
+            raise AsscppError(rc, (self.L.asscpp_last_error(self.h) or b"").decode())
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.L.asscpp_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- evaluation ------------------------------------------------------------------------------
+    def eval_async(self, poses, covered=None, flags=0):
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        self._ck(self.L.asscpp_eval_batch(self.h, _ptr(poses, C.c_double), poses.shape[0],
+                                          -1 if covered is None else covered.handle, flags))
+        return poses.shape[0]
+
+    def results(self, nviews):
+        out = np.zeros(nviews, RESULT_DTYPE)
+        self._ck(self.L.asscpp_get_results(self.h, out.ctypes.data_as(C.c_void_p), nviews))
+        return out
+
+    def eval_batch(self, poses, covered=None, flags=0):
+        return self.results(self.eval_async(poses, covered, flags))
+
+    def eval_device(self, d_poses_ptr, nviews, covered=None, flags=0):
+        """poses already in HBM (raw device pointer); results stay on the device."""
+        out = C.c_void_p()
+        self._ck(self.L.asscpp_eval_batch_device(self.h, C.c_void_p(d_poses_ptr), nviews,
+                                                 -1 if covered is None else covered.handle, flags, C.byref(out)))
+        return out.value
+
+    def get_visible(self, pose):
+        pose = np.ascontiguousarray(pose, np.float64)
+        idx = np.zeros(max(self.n_points, 1), np.int32)
+        n = C.c_int64()
+        self._ck(self.L.asscpp_get_visible(self.h, _ptr(pose, C.c_double), _ptr(idx, C.c_int32), idx.shape[0],
+                                           C.byref(n)))
+        return idx[: n.value].copy()
+
+    def new_set(self):
+        out = C.c_int()
+        self._ck(self.L.asscpp_covered_new(self.h, C.byref(out)))
+        return CoveredSet(self, out.value)
+
+    def coverage_percent_cloud(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = C.c_float()
+        self._ck(self.L.asscpp_coverage_percent_cloud(self.h, _ptr(xyz, C.c_float), xyz.shape[0], C.byref(out)))
+        return out.value
+
+    # -- streams / timing --------------------------------------------------------------------------
+    def sync(self):
+        self._ck(self.L.asscpp_sync(self.h))
+
+    def stream(self):
+        return self.L.asscpp_get_stream(self.h)
+
+    def timer_begin(self):
+        self._ck(self.L.asscpp_timer_begin(self.h))
+
+    def timer_end(self):
+        ms = C.c_float()
+        self._ck(self.L.asscpp_timer_end(self.h, C.byref(ms)))
+        return ms.value
+
+    def eval_kernel_ms(self):
+        ms, n = C.c_float(), C.c_int64()
+        self._ck(self.L.asscpp_eval_kernel_ms(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def launch_count(self):
+        return self.L.asscpp_launch_count(self.h)
+
+    # -- multi-GPU -----------------------------------------------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        buf = np.zeros(128, np.uint8)
+        rc = _abi.load().asscpp_comm_unique_id(_ptr(buf, C.c_uint8))
+        if rc:
+            raise AsscppError(rc, (_abi.load().asscpp_last_error(None) or b"").decode())
+        return buf
+
+    def comm_init(self, nranks, rank, uid):
+        uid = np.ascontiguousarray(uid, np.uint8)
+        self._ck(self.L.asscpp_comm_init(self.h, nranks, rank, _ptr(uid, C.c_uint8)))
+        self.nranks, self.rank = nranks, rank
+
+    def allgather_results(self, nviews_local):
+        out = np.zeros(nviews_local * self.nranks, RESULT_DTYPE)
+        self._ck(self.L.asscpp_allgather_results(self.h, nviews_local, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def allreduce_or(self, covered):
+        self._ck(self.L.asscpp_allreduce_or(self.h, covered.handle))
+
+    def comm_destroy(self):
+        self._ck(self.L.asscpp_comm_destroy(self.h))

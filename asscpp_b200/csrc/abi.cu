@@ -1,0 +1,794 @@
+// abi.cu -- the C ABI of include/asscpp_gpu.h: context, device memory, kernel sequencing.
+// No torch, no CPU fallback: every compute entry point launches the sm_100a kernels of kernels.cu.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.h"
+#include "kernels.h"
+#include "preprocess.h"
+
+using namespace asscpp;
+
+namespace {
+
+std::string g_create_error;
+
+// ---- NCCL through dlopen (the library is torch's bundled libnccl.so.2 or the system one) -------
+struct NcclUniqueId { char internal[128]; };
+typedef void* NcclComm;
+struct NcclApi {
+  void* handle = nullptr;
+  int (*GetUniqueId)(NcclUniqueId*) = nullptr;
+  int (*CommInitRank)(NcclComm*, int, NcclUniqueId, int) = nullptr;
+  int (*AllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t) = nullptr;
+  int (*CommDestroy)(NcclComm) = nullptr;
+  const char* (*GetErrorString)(int) = nullptr;
+  bool load(std::string* err) {
+    if (handle) return true;
+    const char* env = getenv("ASSCPP_NCCL_LIB");
+    const char* names[] = {env, "libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+      if (!nm || !*nm) continue;
+      handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+      if (handle) break;
+    }
+    if (!handle) { *err = std::string("cannot dlopen libnccl: ") + dlerror(); return false; }
+    GetUniqueId = (int (*)(NcclUniqueId*))dlsym(handle, "ncclGetUniqueId");
+    CommInitRank = (int (*)(NcclComm*, int, NcclUniqueId, int))dlsym(handle, "ncclCommInitRank");
+    AllGather = (int (*)(const void*, void*, size_t, int, NcclComm, cudaStream_t))dlsym(handle, "ncclAllGather");
+    CommDestroy = (int (*)(NcclComm))dlsym(handle, "ncclCommDestroy");
+    GetErrorString = (const char* (*)(int))dlsym(handle, "ncclGetErrorString");
+    if (!GetUniqueId || !CommInitRank || !AllGather || !CommDestroy) { *err = "libnccl lacks required symbols"; return false; }
+    return true;
+  }
+};
+NcclApi g_nccl;
+constexpr int kNcclUint8 = 1;
+
+struct CoveredSet {
+  uint32_t* buf = nullptr;  // [pts words | vox words] contiguous (one allgather moves both)
+  bool used = false;
+};
+
+}  // namespace
+
+struct AsscppCtx {
+  int device = 0;
+  int sm_count = 0;
+  cudaStream_t stream = nullptr;
+  AsscppParams params;
+  FrustumConst fc;
+  ModelDev m;
+  std::vector<void*> allocs;  // everything cudaMalloc'ed for the model + scratch
+  int64_t cov_keys_n = 0;
+  int64_t* d_cov_keys = nullptr;
+  int32_t cov_min_b[3], cov_div[3];
+  // sizes
+  int64_t pts_words = 0, vox_words = 0;  // uint32 words, even counts
+  int ctas = 0, ordered_ctas = 8;
+  size_t smem_bytes = 0;
+  uint32_t smem_grid_words = 0;
+  int64_t chunk_cap = 0, list_cap = 0, grid_cap_words = 0, cov_words = 0;
+  uint2* d_chunk_list = nullptr;
+  uint32_t *d_vox_list = nullptr, *d_grid_scratch = nullptr, *d_cov_scratch = nullptr;
+  uint8_t* d_vstate = nullptr;
+  int32_t* d_counters = nullptr;  // [0] work counter, [1] ordered count
+  unsigned long long* d_pop = nullptr;  // 2 popcount cells
+  // per-batch buffers (grown on demand)
+  int64_t view_cap = 0;
+  double* d_poses = nullptr;
+  ViewDev* d_views = nullptr;
+  AsscppViewResult* d_results = nullptr;
+  int32_t* d_ordered_list = nullptr;
+  int64_t last_nviews = -1;
+  std::vector<AsscppViewResult> h_results;
+  // staging
+  uint32_t* d_tmp_bits = nullptr;  // pts_words, original-index space staging
+  int64_t idx_cap = 0;
+  int32_t* d_idx = nullptr;
+  int64_t cloud_cap = 0;
+  float* d_cloud = nullptr;
+  std::vector<CoveredSet> sets;
+  int tmp_set = -1;
+  // timing
+  cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+  bool timing = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kernel_events;
+  size_t kernel_events_used = 0;
+  float last_kernel_ms = 0;
+  int64_t last_kernel_launches = 0;
+  int64_t launches = 0;
+  // nccl
+  NcclComm comm = nullptr;
+  int nranks = 1, rank = 0;
+  void* d_gather = nullptr;
+  size_t gather_bytes = 0;
+  std::string err;
+};
+
+namespace {
+
+#define CU(ctx, expr)                                                                       \
+  do {                                                                                      \
+    cudaError_t e__ = (expr);                                                               \
+    if (e__ != cudaSuccess) {                                                               \
+      (ctx)->err = std::string(#expr) + ": " + cudaGetErrorString(e__);                     \
+      return ASSCPP_ECUDA;                                                                  \
+    }                                                                                       \
+  } while (0)
+
+template <class T>
+int dev_alloc(AsscppCtx* c, T** p, int64_t count, bool track = true) {
+  *p = nullptr;
+  size_t bytes = (size_t)std::max<int64_t>(count, 1) * sizeof(T);
+  cudaError_t e = cudaMalloc((void**)p, bytes);
+  if (e != cudaSuccess) {
+    c->err = std::string("cudaMalloc(") + std::to_string(bytes) + "): " + cudaGetErrorString(e);
+    return e == cudaErrorMemoryAllocation ? ASSCPP_ENOMEM : ASSCPP_ECUDA;
+  }
+  if (track) c->allocs.push_back(*p);
+  return ASSCPP_OK;
+}
+
+template <class T>
+int upload(AsscppCtx* c, const T** dst, const std::vector<T>& src) {
+  T* p;
+  int rc = dev_alloc(c, &p, (int64_t)src.size());
+  if (rc) return rc;
+  if (!src.empty()) CU(c, cudaMemcpy(p, src.data(), src.size() * sizeof(T), cudaMemcpyHostToDevice));
+  *dst = p;
+  return ASSCPP_OK;
+}
+
+int64_t set_words(const AsscppCtx* c) { return c->pts_words + c->vox_words; }
+
+CoveredDev set_dev(const AsscppCtx* c, int id) {
+  CoveredDev d;
+  d.pts = c->sets[id].buf;
+  d.vox = c->sets[id].buf + c->pts_words;
+  return d;
+}
+
+bool valid_set(const AsscppCtx* c, int id) {
+  return id >= 0 && id < (int)c->sets.size() && c->sets[id].used;
+}
+
+int new_set(AsscppCtx* c, int* out) {
+  int id = -1;
+  for (size_t i = 0; i < c->sets.size(); ++i)
+    if (!c->sets[i].used) { id = (int)i; break; }
+  if (id < 0) { c->sets.push_back(CoveredSet()); id = (int)c->sets.size() - 1; }
+  if (!c->sets[id].buf) {
+    int rc = dev_alloc(c, &c->sets[id].buf, set_words(c), false);
+    if (rc) return rc;
+  }
+  CU(c, cudaMemsetAsync(c->sets[id].buf, 0, (size_t)set_words(c) * 4, c->stream));
+  c->sets[id].used = true;
+  *out = id;
+  return ASSCPP_OK;
+}
+
+int ensure_views(AsscppCtx* c, int64_t nviews) {
+  if (nviews <= c->view_cap) return ASSCPP_OK;
+  CU(c, cudaStreamSynchronize(c->stream));
+  int64_t cap = std::max<int64_t>(nviews, c->view_cap * 2);
+  cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
+  c->d_poses = nullptr; c->d_views = nullptr; c->d_results = nullptr; c->d_ordered_list = nullptr;
+  c->view_cap = 0;
+  int rc;
+  if ((rc = dev_alloc(c, &c->d_poses, cap * 7, false))) return rc;
+  if ((rc = dev_alloc(c, &c->d_views, cap, false))) return rc;
+  if ((rc = dev_alloc(c, &c->d_results, cap, false))) return rc;
+  if ((rc = dev_alloc(c, &c->d_ordered_list, cap, false))) return rc;
+  c->view_cap = cap;
+  return ASSCPP_OK;
+}
+
+// planes -> eval -> ordered, all on the context's stream
+int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_set, int accum_set,
+             int64_t accum_min_visible, uint32_t flags) {
+  if (nviews < 0 || nviews > 0x7fffffffLL) { c->err = "nviews out of range"; return ASSCPP_EINVAL; }
+  if (covered_set != -1 && !valid_set(c, covered_set)) { c->err = "bad covered set handle"; return ASSCPP_EINVAL; }
+  if (accum_set != -1 && !valid_set(c, accum_set)) { c->err = "bad accumulator set handle"; return ASSCPP_EINVAL; }
+  c->last_nviews = nviews;
+  if (nviews == 0) return ASSCPP_OK;
+  CU(c, cudaMemsetAsync(c->d_counters, 0, 2 * sizeof(int32_t), c->stream));
+  launch_planes(d_poses, nviews, c->fc, c->d_views, c->stream);
+  EvalArgs a;
+  a.m = c->m;
+  a.views = c->d_views;
+  a.nviews = nviews;
+  a.work_counter = c->d_counters;
+  a.results = c->d_results;
+  a.covered.pts = nullptr; a.covered.vox = nullptr;
+  if (covered_set >= 0) a.covered = set_dev(c, covered_set);
+  a.accum.pts = nullptr; a.accum.vox = nullptr;
+  if (accum_set >= 0) a.accum = set_dev(c, accum_set);
+  a.accum_min_visible = accum_min_visible;
+  a.flags = flags;
+  a.chunk_list = c->d_chunk_list; a.chunk_cap = c->chunk_cap;
+  a.vox_list = c->d_vox_list; a.list_cap = c->list_cap;
+  a.grid_scratch = c->d_grid_scratch; a.grid_cap_words = c->grid_cap_words;
+  a.cov_scratch = c->d_cov_scratch; a.cov_words = c->cov_words;
+  a.vstate = c->d_vstate;
+  a.ordered_list = c->d_ordered_list;
+  a.ordered_count = c->d_counters + 1;
+  a.smem_grid_words = c->smem_grid_words;
+  int ctas = (int)std::min<int64_t>(c->ctas, nviews);
+  std::pair<cudaEvent_t, cudaEvent_t>* evp = nullptr;
+  if (c->timing) {
+    if (c->kernel_events_used == c->kernel_events.size()) {
+      cudaEvent_t e0, e1;
+      CU(c, cudaEventCreate(&e0));
+      CU(c, cudaEventCreate(&e1));
+      c->kernel_events.push_back(std::make_pair(e0, e1));
+    }
+    evp = &c->kernel_events[c->kernel_events_used++];
+    CU(c, cudaEventRecord(evp->first, c->stream));
+  }
+  launch_eval(a, ctas, c->smem_bytes, c->stream);
+  if (evp) CU(c, cudaEventRecord(evp->second, c->stream));
+  launch_ordered(a, c->ordered_ctas, c->smem_bytes, c->stream);
+  c->launches += 3;
+  CU(c, cudaGetLastError());
+  return ASSCPP_OK;
+}
+
+int fetch_results(AsscppCtx* c, int64_t nviews) {
+  if (c->last_nviews < 0) { c->err = "no evaluation has been issued"; return ASSCPP_ESTATE; }
+  if (nviews > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
+  c->h_results.resize((size_t)std::max<int64_t>(nviews, 1));
+  if (nviews > 0)
+    CU(c, cudaMemcpyAsync(c->h_results.data(), c->d_results, (size_t)nviews * sizeof(AsscppViewResult),
+                          cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  for (int64_t v = 0; v < nviews; ++v)
+    if (c->h_results[v].status & kVsError) { c->err = "internal scratch bound violated for a view"; return ASSCPP_ERANGE; }
+  return ASSCPP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int asscpp_abi_version(void) { return ASSCPP_ABI_VERSION; }
+
+void asscpp_default_params(AsscppParams* p) {
+  if (!p) return;
+  p->leaf = 0.5f; p->hfov_deg = 58.0f; p->vfov_deg = 45.0f; p->near_dist = 0.7f; p->far_dist = 6.0f;
+  p->pcd_origin[0] = p->pcd_origin[1] = p->pcd_origin[2] = 0.0f;
+  p->cov_leaf = 0.5f;
+}
+
+const char* asscpp_last_error(const AsscppCtx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* params, AsscppCtx** out) {
+  if (!out) return ASSCPP_EINVAL;
+  *out = nullptr;
+  if ((!xyz && n > 0) || !params || n < 0 || n > 0x7fffffffLL || !(params->leaf > 0) || !(params->cov_leaf > 0) ||
+      !(params->far_dist > params->near_dist) || !(params->near_dist > 0)) {
+    g_create_error = "invalid arguments to asscpp_create";
+    return ASSCPP_EINVAL;
+  }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0 || device < 0 || device >= ndev) {
+    cudaGetLastError();
+    g_create_error = "no usable CUDA device (this library has no CPU path)";
+    return ASSCPP_ENODEVICE;
+  }
+  AsscppCtx* c = new AsscppCtx();
+  auto fail = [&](int rc) {
+    g_create_error = c->err;
+    asscpp_destroy(c);
+    return rc;
+  };
+  c->device = device;
+  c->params = *params;
+  c->fc = frustum_const(*params);
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) { c->err = cudaGetErrorString(e); return fail(ASSCPP_ENODEVICE); }
+  int major = 0, optin = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+  cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+  cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  if (major < 10) { c->err = "device is not sm_100 class; kernels are built for sm_100a only"; return fail(ASSCPP_ENODEVICE); }
+  if ((e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+    c->err = cudaGetErrorString(e);
+    return fail(ASSCPP_ECUDA);
+  }
+  cudaEventCreate(&c->ev_begin);
+  cudaEventCreate(&c->ev_end);
+
+  ModelHost h;
+  std::string perr;
+  int rc = preprocess_model(xyz, n, *params, &h, &perr);
+  if (rc) { c->err = perr; return fail(rc); }
+  ModelDev& m = c->m;
+  memset(&m, 0, sizeof(m));
+  m.n = h.n; m.n_vox = h.n_vox; m.n_cov = h.n_cov; m.n_chunks = h.n_chunks; m.n_super = h.n_super;
+  m.leaf = params->leaf; m.inv_leaf = h.inv_leaf; m.half_leaf = params->leaf * 0.5f;
+  for (int k = 0; k < 3; ++k) {
+    m.pcd_origin[k] = params->pcd_origin[k];
+    m.min_b[k] = h.min_b[k]; m.max_b[k] = h.max_b[k];
+    c->cov_min_b[k] = h.cov_min_b[k]; c->cov_div[k] = h.cov_div[k];
+  }
+  m.dist_thr_sq = h.dist_thr_sq;
+  m.cov_same = h.cov_same;
+  static_assert(sizeof(Float4) == sizeof(float4) && sizeof(Int4) == sizeof(int4), "layout");
+  if ((rc = upload(c, (const Float4**)&m.pts, h.pts))) return fail(rc);
+  if ((rc = upload(c, &m.orig, h.orig))) return fail(rc);
+  if ((rc = upload(c, &m.pos_of, h.pos_of))) return fail(rc);
+  if ((rc = upload(c, (const Int4**)&m.vox, h.vox))) return fail(rc);
+  if ((rc = upload(c, &m.vox_cov, h.vox_cov))) return fail(rc);
+  if ((rc = upload(c, &m.pt_cov, h.pt_cov))) return fail(rc);
+  if ((rc = upload(c, (const Float4**)&m.chunk_lo, h.chunk_lo))) return fail(rc);
+  if ((rc = upload(c, (const Float4**)&m.chunk_hi, h.chunk_hi))) return fail(rc);
+  if ((rc = upload(c, (const Float4**)&m.super_lo, h.super_lo))) return fail(rc);
+  if ((rc = upload(c, (const Float4**)&m.super_hi, h.super_hi))) return fail(rc);
+  {
+    const int64_t* dk;
+    if ((rc = upload(c, &dk, h.cov_keys))) return fail(rc);
+    c->d_cov_keys = const_cast<int64_t*>(dk);
+    c->cov_keys_n = (int64_t)h.cov_keys.size();
+  }
+  c->pts_words = 2 * ((m.n + 63) / 64);
+  c->vox_words = 2 * ((m.n_cov + 63) / 64);
+  if (c->pts_words == 0) c->pts_words = 2;
+  if (c->vox_words == 0) c->vox_words = 2;
+
+  // ---- launch geometry + scratch ----------------------------------------------------------------
+  c->ctas = c->sm_count;
+  size_t hdr = eval_smem_header_bytes();
+  size_t avail = (size_t)optin > hdr + 64 ? (size_t)optin - hdr - 64 : 0;
+  c->smem_grid_words = (uint32_t)(avail / 4);
+  c->smem_bytes = eval_smem_bytes(c->smem_grid_words);
+  if ((e = configure_kernels(c->smem_bytes)) != cudaSuccess) { c->err = cudaGetErrorString(e); return fail(ASSCPP_ECUDA); }
+  double ext = frustum_max_extent(*params);
+  double cells_cap = 1;
+  for (int k = 0; k < 3; ++k) {
+    double model_div = (double)h.max_b[k] - h.min_b[k] + 1;
+    double a = std::min(model_div, std::floor(ext * (double)h.inv_leaf) + 4.0);
+    cells_cap *= std::max(a, 1.0);
+  }
+  if (cells_cap > 2147483647.0) cells_cap = 2147483647.0;
+  c->grid_cap_words = (int64_t)(cells_cap / 32.0) + 2;
+  c->chunk_cap = std::max<int64_t>(m.n_chunks, 1);
+  c->list_cap = m.n_vox + m.n / 32 + m.n_chunks + 64;
+  c->cov_words = c->vox_words;
+  if ((rc = dev_alloc(c, &c->d_chunk_list, c->chunk_cap * c->ctas))) return fail(rc);
+  if ((rc = dev_alloc(c, &c->d_vox_list, c->list_cap * c->ctas))) return fail(rc);
+  if ((rc = dev_alloc(c, &c->d_grid_scratch, c->grid_cap_words * c->ctas))) return fail(rc);
+  if ((rc = dev_alloc(c, &c->d_cov_scratch, c->cov_words * c->ctas))) return fail(rc);
+  if ((rc = dev_alloc(c, &c->d_vstate, std::max<int64_t>(m.n_vox, 1) * c->ordered_ctas))) return fail(rc);
+  if ((rc = dev_alloc(c, &c->d_counters, 4))) return fail(rc);
+  if ((rc = dev_alloc(c, &c->d_pop, 2))) return fail(rc);
+  if ((rc = dev_alloc(c, &c->d_tmp_bits, c->pts_words))) return fail(rc);
+  cudaMemsetAsync(c->d_cov_scratch, 0, (size_t)c->cov_words * c->ctas * 4, c->stream);
+  launch_fill_bytes(c->d_vstate, std::max<int64_t>(m.n_vox, 1) * c->ordered_ctas, 0xff, c->stream);
+  c->launches += 1;
+  if ((rc = new_set(c, &c->tmp_set))) return fail(rc);
+  if ((e = cudaStreamSynchronize(c->stream)) != cudaSuccess) { c->err = cudaGetErrorString(e); return fail(ASSCPP_ECUDA); }
+  *out = c;
+  return ASSCPP_OK;
+}
+
+int asscpp_destroy(AsscppCtx* c) {
+  if (!c) return ASSCPP_OK;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+  for (void* p : c->allocs) cudaFree(p);
+  for (auto& s : c->sets) cudaFree(s.buf);
+  cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
+  cudaFree(c->d_idx); cudaFree(c->d_cloud); cudaFree(c->d_gather);
+  for (auto& ev : c->kernel_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+  if (c->ev_begin) cudaEventDestroy(c->ev_begin);
+  if (c->ev_end) cudaEventDestroy(c->ev_end);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+  return ASSCPP_OK;
+}
+
+int asscpp_model_info(const AsscppCtx* c, AsscppModelInfo* out) {
+  if (!c || !out) return ASSCPP_EINVAL;
+  out->n_points = c->m.n; out->n_occ_voxels = c->m.n_vox; out->n_cov_voxels = c->m.n_cov; out->n_chunks = c->m.n_chunks;
+  for (int k = 0; k < 3; ++k) { out->min_b[k] = c->m.min_b[k]; out->max_b[k] = c->m.max_b[k]; }
+  out->sm_count = c->sm_count;
+  out->reserved = 0;
+  return ASSCPP_OK;
+}
+
+int asscpp_eval_batch_device(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_set, uint32_t flags,
+                             const AsscppViewResult** d_results) {
+  if (!c || (!d_poses && nviews > 0)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = ensure_views(c, nviews);
+  if (rc) return rc;
+  rc = run_eval(c, d_poses, nviews, covered_set, -1, 0, flags);
+  if (rc) return rc;
+  if (d_results) *d_results = c->d_results;
+  return ASSCPP_OK;
+}
+
+int asscpp_eval_batch(AsscppCtx* c, const double* poses, int64_t nviews, int covered_set, uint32_t flags) {
+  if (!c || (!poses && nviews > 0) || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = ensure_views(c, nviews);
+  if (rc) return rc;
+  if (nviews > 0)
+    CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  return run_eval(c, c->d_poses, nviews, covered_set, -1, 0, flags);
+}
+
+int asscpp_get_results(AsscppCtx* c, AsscppViewResult* out, int64_t nviews) {
+  if (!c || (!out && nviews > 0) || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = fetch_results(c, nviews);
+  if (rc) return rc;
+  if (nviews > 0) memcpy(out, c->h_results.data(), (size_t)nviews * sizeof(AsscppViewResult));
+  return ASSCPP_OK;
+}
+
+int asscpp_get_counts(AsscppCtx* c, uint32_t* survivors, uint32_t* visible, uint32_t* carry, int64_t nviews) {
+  if (!c || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = fetch_results(c, nviews);
+  if (rc) return rc;
+  for (int64_t v = 0; v < nviews; ++v) {
+    if (survivors) survivors[v] = c->h_results[v].survivors;
+    if (visible) visible[v] = c->h_results[v].visible;
+    if (carry) carry[v] = c->h_results[v].carry;
+  }
+  return ASSCPP_OK;
+}
+
+int asscpp_get_gain(AsscppCtx* c, uint32_t* gain_pts, uint32_t* gain_vox, int64_t nviews) {
+  if (!c || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = fetch_results(c, nviews);
+  if (rc) return rc;
+  for (int64_t v = 0; v < nviews; ++v) {
+    if (gain_pts) gain_pts[v] = c->h_results[v].gain_pts;
+    if (gain_vox) gain_vox[v] = c->h_results[v].gain_vox;
+  }
+  return ASSCPP_OK;
+}
+
+// ---- covered sets ---------------------------------------------------------------------------------
+int asscpp_covered_new(AsscppCtx* c, int* set_out) {
+  if (!c || !set_out) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  return new_set(c, set_out);
+}
+
+int asscpp_covered_free(AsscppCtx* c, int set) {
+  if (!c || !valid_set(c, set) || set == c->tmp_set) return ASSCPP_EINVAL;
+  c->sets[set].used = false;  // buffer is kept for reuse
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_clear(AsscppCtx* c, int set) {
+  if (!c || !valid_set(c, set)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  CU(c, cudaMemsetAsync(c->sets[set].buf, 0, (size_t)set_words(c) * 4, c->stream));
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_clone(AsscppCtx* c, int src, int* set_out) {
+  if (!c || !set_out || !valid_set(c, src)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = new_set(c, set_out);
+  if (rc) return rc;
+  CU(c, cudaMemcpyAsync(c->sets[*set_out].buf, c->sets[src].buf, (size_t)set_words(c) * 4, cudaMemcpyDeviceToDevice,
+                        c->stream));
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_or_set(AsscppCtx* c, int dst, int src) {
+  if (!c || !valid_set(c, dst) || !valid_set(c, src)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  launch_or_words(c->sets[dst].buf, c->sets[src].buf, set_words(c), c->stream);
+  c->launches += 1;
+  CU(c, cudaGetLastError());
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_or_views(AsscppCtx* c, int set, const double* poses, int64_t nviews, int64_t min_visible) {
+  if (!c || !valid_set(c, set) || (!poses && nviews > 0) || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = ensure_views(c, nviews);
+  if (rc) return rc;
+  if (nviews > 0)
+    CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  return run_eval(c, c->d_poses, nviews, -1, set, min_visible, 0);
+}
+
+int asscpp_covered_or_points(AsscppCtx* c, int set, const int32_t* idx, int64_t n) {
+  if (!c || !valid_set(c, set) || (!idx && n > 0) || n < 0) return ASSCPP_EINVAL;
+  if (n == 0) return ASSCPP_OK;
+  cudaSetDevice(c->device);
+  if (n > c->idx_cap) {
+    CU(c, cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_idx);
+    c->d_idx = nullptr; c->idx_cap = 0;
+    int rc = dev_alloc(c, &c->d_idx, n, false);
+    if (rc) return rc;
+    c->idx_cap = n;
+  }
+  CU(c, cudaMemcpyAsync(c->d_idx, idx, (size_t)n * 4, cudaMemcpyHostToDevice, c->stream));
+  launch_or_points(set_dev(c, set), c->d_idx, n, c->m, c->stream);
+  c->launches += 1;
+  CU(c, cudaGetLastError());
+  CU(c, cudaStreamSynchronize(c->stream));  // idx may be pageable and reused by the caller
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_popcount(AsscppCtx* c, int set, int64_t* n_points, int64_t* n_voxels) {
+  if (!c || !valid_set(c, set)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  CoveredDev d = set_dev(c, set);
+  CU(c, cudaMemsetAsync(c->d_pop, 0, 2 * sizeof(unsigned long long), c->stream));
+  launch_popcount(d.pts, c->pts_words, c->d_pop, c->stream);
+  launch_popcount(d.vox, c->vox_words, c->d_pop + 1, c->stream);
+  c->launches += 2;
+  unsigned long long h[2];
+  CU(c, cudaMemcpyAsync(h, c->d_pop, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (n_points) *n_points = (int64_t)h[0];
+  if (n_voxels) *n_voxels = (int64_t)h[1];
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_export(AsscppCtx* c, int set, uint64_t* point_bits, uint64_t* voxel_bits) {
+  if (!c || !valid_set(c, set)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  CoveredDev d = set_dev(c, set);
+  if (point_bits) {
+    CU(c, cudaMemsetAsync(c->d_tmp_bits, 0, (size_t)c->pts_words * 4, c->stream));
+    launch_permute_bits(d.pts, c->d_tmp_bits, c->m.orig, c->m.n, c->stream);
+    c->launches += 1;
+    CU(c, cudaMemcpyAsync(point_bits, c->d_tmp_bits, (size_t)((c->m.n + 63) / 64) * 8, cudaMemcpyDeviceToHost, c->stream));
+  }
+  if (voxel_bits)
+    CU(c, cudaMemcpyAsync(voxel_bits, d.vox, (size_t)((c->m.n_cov + 63) / 64) * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_import(AsscppCtx* c, int set, const uint64_t* point_bits, const uint64_t* voxel_bits) {
+  if (!c || !valid_set(c, set)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  CoveredDev d = set_dev(c, set);
+  if (point_bits) {
+    CU(c, cudaMemcpyAsync(c->d_tmp_bits, point_bits, (size_t)((c->m.n + 63) / 64) * 8, cudaMemcpyHostToDevice, c->stream));
+    CU(c, cudaMemsetAsync(d.pts, 0, (size_t)c->pts_words * 4, c->stream));
+    launch_permute_bits(c->d_tmp_bits, d.pts, c->m.pos_of, c->m.n, c->stream);
+    c->launches += 1;
+  }
+  if (voxel_bits)
+    CU(c, cudaMemcpyAsync(d.vox, voxel_bits, (size_t)((c->m.n_cov + 63) / 64) * 8, cudaMemcpyHostToDevice, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return ASSCPP_OK;
+}
+
+static float percent_of(int64_t matched, int64_t orig) {
+  // occlusion_culling.cpp:401,431-432: float counters, float ratio, * 100
+  float m = (float)matched, o = (float)orig;
+  float ratio = m / o;
+  return ratio * 100;
+}
+
+int asscpp_coverage_percent(AsscppCtx* c, int set, float* pct) {
+  if (!c || !pct) return ASSCPP_EINVAL;
+  int64_t nv = 0;
+  int rc = asscpp_covered_popcount(c, set, nullptr, &nv);
+  if (rc) return rc;
+  *pct = percent_of(nv, c->m.n_cov);
+  return ASSCPP_OK;
+}
+
+int asscpp_coverage_percent_cloud(AsscppCtx* c, const float* xyz, int64_t n, float* pct) {
+  if (!c || !pct || (!xyz && n > 0) || n < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  if (n > c->cloud_cap) {
+    CU(c, cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_cloud);
+    c->d_cloud = nullptr; c->cloud_cap = 0;
+    int rc = dev_alloc(c, &c->d_cloud, 3 * n, false);
+    if (rc) return rc;
+    c->cloud_cap = n;
+  }
+  CoveredDev d = set_dev(c, c->tmp_set);
+  CU(c, cudaMemsetAsync(d.vox, 0, (size_t)c->vox_words * 4, c->stream));
+  if (n > 0) {
+    CU(c, cudaMemcpyAsync(c->d_cloud, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, c->stream));
+    launch_cloud_cover(c->d_cloud, n, 1.0f / c->params.cov_leaf, c->cov_min_b, c->cov_div, c->d_cov_keys, c->cov_keys_n,
+                       d.vox, c->stream);
+    c->launches += 1;
+  }
+  CU(c, cudaMemsetAsync(c->d_pop, 0, 2 * sizeof(unsigned long long), c->stream));
+  launch_popcount(d.vox, c->vox_words, c->d_pop + 1, c->stream);
+  c->launches += 1;
+  unsigned long long h[2];
+  CU(c, cudaMemcpyAsync(h, c->d_pop, sizeof(h), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  *pct = percent_of((int64_t)h[1], c->m.n_cov);
+  return ASSCPP_OK;
+}
+
+int asscpp_get_visible(AsscppCtx* c, const double pose[7], int32_t* idx_out, int64_t cap, int64_t* n_out) {
+  if (!c || !pose || !n_out || cap < 0 || (!idx_out && cap > 0)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = asscpp_covered_clear(c, c->tmp_set);
+  if (rc) return rc;
+  rc = asscpp_covered_or_views(c, c->tmp_set, pose, 1, -1);
+  if (rc) return rc;
+  std::vector<uint64_t> bits((size_t)((c->m.n + 63) / 64) + 1, 0);
+  rc = asscpp_covered_export(c, c->tmp_set, bits.data(), nullptr);
+  if (rc) return rc;
+  rc = fetch_results(c, 1);
+  if (rc) return rc;
+  int64_t k = 0;
+  for (int64_t w = 0; w < (c->m.n + 63) / 64; ++w) {
+    uint64_t b = bits[w];
+    while (b) {
+      int t = __builtin_ctzll(b);
+      b &= b - 1;
+      if (k < cap) idx_out[k] = (int32_t)(w * 64 + t);
+      ++k;
+    }
+  }
+  *n_out = k;
+  if (k > cap) { c->err = "idx_out too small"; return ASSCPP_EINVAL; }
+  return ASSCPP_OK;
+}
+
+// ---- streams / timing --------------------------------------------------------------------------------
+int asscpp_sync(AsscppCtx* c) {
+  if (!c) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  CU(c, cudaStreamSynchronize(c->stream));
+  return ASSCPP_OK;
+}
+
+void* asscpp_get_stream(AsscppCtx* c) { return c ? (void*)c->stream : nullptr; }
+
+int asscpp_timer_begin(AsscppCtx* c) {
+  if (!c) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  c->timing = true;
+  c->kernel_events_used = 0;
+  CU(c, cudaEventRecord(c->ev_begin, c->stream));
+  return ASSCPP_OK;
+}
+
+int asscpp_timer_end(AsscppCtx* c, float* ms) {
+  if (!c || !ms) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  CU(c, cudaEventRecord(c->ev_end, c->stream));
+  CU(c, cudaEventSynchronize(c->ev_end));
+  CU(c, cudaEventElapsedTime(ms, c->ev_begin, c->ev_end));
+  float total = 0;
+  for (size_t i = 0; i < c->kernel_events_used; ++i) {
+    float t = 0;
+    CU(c, cudaEventElapsedTime(&t, c->kernel_events[i].first, c->kernel_events[i].second));
+    total += t;
+  }
+  c->last_kernel_ms = total;
+  c->last_kernel_launches = (int64_t)c->kernel_events_used;
+  c->timing = false;
+  c->kernel_events_used = 0;
+  return ASSCPP_OK;
+}
+
+int64_t asscpp_launch_count(const AsscppCtx* c) { return c ? c->launches : 0; }
+
+int asscpp_eval_kernel_ms(AsscppCtx* c, float* ms, int64_t* launches) {
+  if (!c) return ASSCPP_EINVAL;
+  if (ms) *ms = c->last_kernel_ms;
+  if (launches) *launches = c->last_kernel_launches;
+  return ASSCPP_OK;
+}
+
+// ---- multi-GPU -----------------------------------------------------------------------------------------
+int asscpp_comm_unique_id(uint8_t id_out[128]) {
+  std::string err;
+  if (!id_out) return ASSCPP_EINVAL;
+  if (!g_nccl.load(&err)) { g_create_error = err; return ASSCPP_ENCCL; }
+  NcclUniqueId id;
+  int r = g_nccl.GetUniqueId(&id);
+  if (r != 0) { g_create_error = "ncclGetUniqueId failed"; return ASSCPP_ENCCL; }
+  memcpy(id_out, id.internal, 128);
+  return ASSCPP_OK;
+}
+
+int asscpp_comm_init(AsscppCtx* c, int nranks, int rank, const uint8_t id[128]) {
+  if (!c || !id || nranks < 1 || rank < 0 || rank >= nranks) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  if (!g_nccl.load(&c->err)) return ASSCPP_ENCCL;
+  NcclUniqueId uid;
+  memcpy(uid.internal, id, 128);
+  int r = g_nccl.CommInitRank(&c->comm, nranks, uid, rank);
+  if (r != 0) {
+    c->err = std::string("ncclCommInitRank: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error");
+    c->comm = nullptr;
+    return ASSCPP_ENCCL;
+  }
+  c->nranks = nranks;
+  c->rank = rank;
+  return ASSCPP_OK;
+}
+
+static int ensure_gather(AsscppCtx* c, size_t bytes) {
+  if (bytes <= c->gather_bytes) return ASSCPP_OK;
+  CU(c, cudaStreamSynchronize(c->stream));
+  cudaFree(c->d_gather);
+  c->d_gather = nullptr; c->gather_bytes = 0;
+  uint8_t* p;
+  int rc = dev_alloc(c, &p, (int64_t)bytes, false);
+  if (rc) return rc;
+  c->d_gather = p;
+  c->gather_bytes = bytes;
+  return ASSCPP_OK;
+}
+
+int asscpp_allgather_results(AsscppCtx* c, int64_t nviews_local, AsscppViewResult* out) {
+  if (!c || !out || nviews_local < 0) return ASSCPP_EINVAL;
+  if (!c->comm) { c->err = "communicator not initialised"; return ASSCPP_ESTATE; }
+  if (nviews_local > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
+  cudaSetDevice(c->device);
+  size_t bytes = (size_t)nviews_local * sizeof(AsscppViewResult);
+  int rc = ensure_gather(c, bytes * c->nranks);
+  if (rc) return rc;
+  if (bytes) {
+    int r = g_nccl.AllGather(c->d_results, c->d_gather, bytes, kNcclUint8, c->comm, c->stream);
+    if (r != 0) { c->err = "ncclAllGather failed"; return ASSCPP_ENCCL; }
+    CU(c, cudaMemcpyAsync(out, c->d_gather, bytes * c->nranks, cudaMemcpyDeviceToHost, c->stream));
+  }
+  CU(c, cudaStreamSynchronize(c->stream));
+  return ASSCPP_OK;
+}
+
+int asscpp_allreduce_or(AsscppCtx* c, int set) {
+  if (!c || !valid_set(c, set)) return ASSCPP_EINVAL;
+  if (!c->comm) { c->err = "communicator not initialised"; return ASSCPP_ESTATE; }
+  cudaSetDevice(c->device);
+  size_t bytes = (size_t)set_words(c) * 4;
+  int rc = ensure_gather(c, bytes * c->nranks);
+  if (rc) return rc;
+  // NCCL has no bitwise-OR reduction: gather every rank's bitset, then OR them locally
+  int r = g_nccl.AllGather(c->sets[set].buf, c->d_gather, bytes, kNcclUint8, c->comm, c->stream);
+  if (r != 0) { c->err = "ncclAllGather failed"; return ASSCPP_ENCCL; }
+  launch_or_reduce(c->sets[set].buf, (const uint32_t*)c->d_gather, set_words(c), c->nranks, c->stream);
+  c->launches += 1;
+  CU(c, cudaGetLastError());
+  return ASSCPP_OK;
+}
+
+int asscpp_comm_destroy(AsscppCtx* c) {
+  if (!c) return ASSCPP_EINVAL;
+  if (c->comm && g_nccl.CommDestroy) {
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    g_nccl.CommDestroy(c->comm);
+  }
+  c->comm = nullptr;
+  c->nranks = 1;
+  c->rank = 0;
+  return ASSCPP_OK;
+}
+
+int asscpp_frustum_planes(const AsscppParams* p, const double pose[7], float planes[24], float origin[3]) {
+  if (!p || !pose || !planes || !origin) return ASSCPP_EINVAL;
+  frustum_planes_host(*p, pose, planes, origin, nullptr);
+  return ASSCPP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,82 @@
+// common.h -- structures shared by the host side (abi.cu, preprocess.cpp) and the kernels.
+#pragma once
+#include <stdint.h>
+#include <vector_types.h>
+
+#include "../../include/asscpp_gpu.h"
+
+namespace asscpp {
+
+constexpr int kChunkMaxPoints = 128;  // leaf bucket of the cull hierarchy (whole voxels)
+constexpr int kSuperFanout = 32;      // chunks per super-chunk (one warp ballot)
+
+// Frustum constants that depend only on the parameters; evaluated once on the host with libm so
+// the double-precision tan() is the same one the CPU path uses (frustum_culling.cpp:88-95).
+struct FrustumConst {
+  float np_h, np_w, fp_h, fp_w;
+  float near_dist, far_dist;
+};
+
+// Device-resident model, laid out once by asscpp_create.
+struct ModelDev {
+  int64_t n;            // points
+  int64_t n_vox;        // occupied voxels (occlusion lattice)
+  int64_t n_cov;        // occupied voxels (coverage lattice)
+  int64_t n_chunks;
+  int64_t n_super;
+  const float4* pts;    // [n] x y z + voxel id bits, sorted by (morton(voxel), original index)
+  const int32_t* orig;  // [n] original index of sorted position
+  const int32_t* pos_of;  // [n] sorted position of original index
+  const int4* vox;      // [n_vox+1] {i, j, k, first point}; sentinel holds n
+  const int32_t* vox_cov;  // [n_vox] coverage id of the voxel when cov lattice == occlusion lattice
+  const int32_t* pt_cov;   // [n] coverage id per sorted position
+  const float4* chunk_lo;  // [n_chunks] aabb min + first point (bits)
+  const float4* chunk_hi;  // [n_chunks] aabb max + end point (bits)
+  const float4* super_lo;  // [n_super]
+  const float4* super_hi;  // [n_super]
+  float leaf, inv_leaf, half_leaf;
+  float pcd_origin[3];
+  float dist_thr_sq;    // largest f32 s with sqrt((double)s) <= (double)(leaf*2): occluder iff sum > this
+  int cov_same;         // coverage lattice == occlusion lattice
+  int32_t min_b[3], max_b[3];
+};
+
+struct ViewDev {  // per view, written by planes_kernel
+  float planes[24];  // l r t b f n
+  float origin[3];
+  float pad;
+};
+
+struct CoveredDev {
+  uint32_t* pts;  // bit per sorted position
+  uint32_t* vox;  // bit per compact coverage id
+};
+
+struct EvalArgs {
+  ModelDev m;
+  const ViewDev* views;
+  int64_t nviews;
+  int32_t* work_counter;     // device scalar, zeroed before launch
+  AsscppViewResult* results;
+  CoveredDev covered;        // score against (pts == nullptr: empty set)
+  CoveredDev accum;          // OR visible sets into (pts == nullptr: none)
+  int64_t accum_min_visible;
+  uint32_t flags;
+  // per-CTA scratch (global memory, L2-resident in steady state)
+  uint2* chunk_list;         // [ctas][chunk_cap] candidate chunks {first point, end point}
+  int64_t chunk_cap;
+  uint32_t* vox_list;        // [ctas][list_cap] voxels occupied for the view (bit 31: visible)
+  int64_t list_cap;
+  uint32_t* grid_scratch;    // [ctas][grid_cap_words] bit-grid when it does not fit shared memory
+  int64_t grid_cap_words;
+  uint32_t* cov_scratch;     // [ctas][cov_words] per-view coverage-voxel marks
+  int64_t cov_words;
+  uint8_t* vstate;           // [ordered ctas][n_vox] per-voxel state for the ordered (Q5) path
+  int32_t* ordered_list;     // views that saw a Q5 carry
+  int32_t* ordered_count;
+  uint32_t smem_grid_words;  // capacity of the shared-memory grid
+};
+
+constexpr uint32_t kVsError = 0x80000000u;  // internal consistency failure (scratch overflow)
+
+}  // namespace asscpp

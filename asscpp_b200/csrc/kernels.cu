@@ -1,0 +1,790 @@
+// kernels.cu -- sm_100a kernels of the coverage-evaluation path.
+//
+//   planes_kernel      pose -> camera matrix -> six frustum planes          (occlusion_culling.cpp:271-290,
+//                                                                            frustum_culling.cpp:82-141)
+//   eval_views_kernel  persistent, one CTA per viewpoint at a time:
+//       P1 bucket pre-cull (conservative AABB-vs-plane reject of super-chunks / chunks)
+//       P2 exact per-point frustum test + emission of the voxels occupied for this view
+//                                                                           (frustum_culling.cpp:150-171)
+//       P3 per-view occupancy bit-grid with PCL's dense linearisation      (voxel_grid_occlusion_estimation.cpp:43-65)
+//       P4 one 3D-DDA ray per occupied voxel + second gate + gain popcounts (...:99-128,174-238,410-582;
+//                                                                            occlusion_culling.cpp:317-370)
+//       P5 optional OR of the visible set into a covered set               (heuristic.cpp:344-346)
+//   ordered_views_kernel  exact replay of the reference's sticky `state` (quirk Q5) for the rare views in
+//                         which occlusionEstimation failed (occlusion_culling.cpp:308,332-335)
+//   set kernels        covered-set OR / popcount / permutation / coverage of an arbitrary cloud
+//
+// All float32 arithmetic that decides set membership uses the round-to-nearest intrinsics (never
+// contracted into FMA) in the operation order fixed in SURVEY.md Appendix A.
+#include <cuda_runtime.h>
+
+#include "common.h"
+#include "kernels.h"
+
+namespace asscpp {
+
+// ------------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float fmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+// frustum_culling.cpp:153-162: pt = (x, y, z, 1); inside iff pt.dot(plane) <= 0 for l r t b f n.
+// <Eigen> 4-wide dot reduced as (a0 + a2) + (a1 + a3).
+__device__ __forceinline__ bool point_in_frustum(const float* pl, float x, float y, float z) {
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    float a = fmul(x, pl[4 * k]), b = fmul(y, pl[4 * k + 1]), c = fmul(z, pl[4 * k + 2]);
+    float t = fadd(fadd(a, c), fadd(b, pl[4 * k + 3]));
+    if (!(t <= 0.0f)) return false;
+  }
+  return true;
+}
+
+// Conservative bucket reject: true only if every point of the box fails the exact test of some
+// plane.  The exact value differs from the real-valued plane function by at most a few ulps of the
+// sum of magnitudes A; the margin 1e-6*A (16 ulps) + 1e-30 (underflow) covers it.
+__device__ __forceinline__ bool box_outside(const float* pl, float lx, float ly, float lz, float hx, float hy,
+                                            float hz) {
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    float a = pl[4 * k], b = pl[4 * k + 1], c = pl[4 * k + 2], w = pl[4 * k + 3];
+    float L = (a >= 0 ? a * lx : a * hx) + (b >= 0 ? b * ly : b * hy) + (c >= 0 ? c * lz : c * hz) + w;
+    float A = fabsf(a) * fmaxf(fabsf(lx), fabsf(hx)) + fabsf(b) * fmaxf(fabsf(ly), fabsf(hy)) +
+              fabsf(c) * fmaxf(fabsf(lz), fabsf(hz)) + fabsf(w);
+    if (L > 1e-6f * A + 1e-30f) return true;
+  }
+  return false;
+}
+
+// ------------------------------------------------------------------------------------------------
+// planes_kernel: one thread per pose.  Double part = <tf Matrix3x3::setRotation>; float part =
+// frustum_culling.cpp:97-141 with the operation order of SURVEY.md A.2.
+// ------------------------------------------------------------------------------------------------
+__global__ void planes_kernel(const double* __restrict__ poses, int64_t nviews, FrustumConst fc,
+                              ViewDev* __restrict__ views) {
+  int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nviews) return;
+  const double* ps = poses + 7 * v;
+  double x = ps[3], y = ps[4], z = ps[5], w = ps[6];
+  double d = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)), __dmul_rn(w, w));
+  double s = __ddiv_rn(2.0, d);
+  double xs = __dmul_rn(x, s), ys = __dmul_rn(y, s), zs = __dmul_rn(z, s);
+  double wx = __dmul_rn(w, xs), wy = __dmul_rn(w, ys), wz = __dmul_rn(w, zs);
+  double xx = __dmul_rn(x, xs), xy = __dmul_rn(x, ys), xz = __dmul_rn(x, zs);
+  double yy = __dmul_rn(y, ys), yz = __dmul_rn(y, zs), zz = __dmul_rn(z, zs);
+  float view[3] = {(float)__dsub_rn(1.0, __dadd_rn(yy, zz)), (float)__dadd_rn(xy, wz), (float)__dsub_rn(xz, wy)};
+  float up[3] = {(float)__dsub_rn(xy, wz), (float)__dsub_rn(1.0, __dadd_rn(xx, zz)), (float)__dadd_rn(yz, wx)};
+  float right[3] = {(float)__dadd_rn(xz, wy), (float)__dsub_rn(yz, wx), (float)__dsub_rn(1.0, __dadd_rn(xx, yy))};
+  float T[3] = {(float)ps[0], (float)ps[1], (float)ps[2]};
+  float fpc[3], npc[3], c8[8][3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    fpc[c] = fadd(T[c], fmul(view[c], fc.far_dist));
+    float uh = fdiv(fmul(up[c], fc.fp_h), 2.0f), rw = fdiv(fmul(right[c], fc.fp_w), 2.0f);
+    float fu = fadd(fpc[c], uh), fd = fsub(fpc[c], uh);
+    c8[0][c] = fsub(fu, rw); c8[1][c] = fadd(fu, rw); c8[2][c] = fsub(fd, rw); c8[3][c] = fadd(fd, rw);
+    npc[c] = fadd(T[c], fmul(view[c], fc.near_dist));
+    float uhn = fdiv(fmul(up[c], fc.np_h), 2.0f), rwn = fdiv(fmul(right[c], fc.np_w), 2.0f);
+    float nu = fadd(npc[c], uhn), nd = fsub(npc[c], uhn);
+    c8[4][c] = fsub(nu, rwn); c8[5][c] = fadd(nu, rwn); c8[6][c] = fsub(nd, rwn); c8[7][c] = fadd(nd, rwn);
+  }
+  auto cross = [](const float* a, const float* b, float* o) {
+    o[0] = fsub(fmul(a[1], b[2]), fmul(a[2], b[1]));
+    o[1] = fsub(fmul(a[2], b[0]), fmul(a[0], b[2]));
+    o[2] = fsub(fmul(a[0], b[1]), fmul(a[1], b[0]));
+  };
+  auto ndot = [](const float* a, const float* b) {
+    return -fadd(fmul(a[0], b[0]), fadd(fmul(a[1], b[1]), fmul(a[2], b[2])));
+  };
+  ViewDev out;
+  float *pl_l = out.planes, *pl_r = out.planes + 4, *pl_t = out.planes + 8, *pl_b = out.planes + 12,
+        *pl_f = out.planes + 16, *pl_n = out.planes + 20;
+  float e1[3], e2[3], a[3], b[3], cc[3], dd[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { e1[c] = fsub(c8[2][c], c8[3][c]); e2[c] = fsub(c8[1][c], c8[3][c]); }
+  cross(e1, e2, pl_f); pl_f[3] = ndot(fpc, pl_f);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) { e1[c] = fsub(c8[5][c], c8[7][c]); e2[c] = fsub(c8[6][c], c8[7][c]); }
+  cross(e1, e2, pl_n); pl_n[3] = ndot(npc, pl_n);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    a[c] = fsub(c8[2][c], T[c]); b[c] = fsub(c8[3][c], T[c]); cc[c] = fsub(c8[1][c], T[c]); dd[c] = fsub(c8[0][c], T[c]);
+  }
+  cross(b, cc, pl_r); cross(dd, a, pl_l); cross(cc, dd, pl_t); cross(a, b, pl_b);
+  pl_r[3] = ndot(T, pl_r); pl_l[3] = ndot(T, pl_l); pl_t[3] = ndot(T, pl_t); pl_b[3] = ndot(T, pl_b);
+  out.origin[0] = T[0]; out.origin[1] = T[1]; out.origin[2] = T[2];
+  out.pad = 0.0f;
+  views[v] = out;
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-view state shared by the CTA
+// ------------------------------------------------------------------------------------------------
+struct GridView {  // geometry of the per-view grid (voxel_grid_occlusion_estimation.cpp:43-65)
+  float leaf, inv, half, thr_sq;
+  float base[3];  // b_min + leaf/2  (voxel_grid_occlusion_estimation.h:151-153)
+  float b_min[3], b_max[3];
+  int min_b[3], div[3];
+  int mul1, mul2;
+  unsigned cells;
+};
+
+struct ViewShared {
+  float planes[24];
+  float origin[3];
+  GridView g;
+  unsigned words;
+  int bb_min[3], bb_max[3];
+  int view;
+  int use_smem;
+  unsigned chunk_count, list_count;
+  unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
+  unsigned long long steps, vis_hash, surv_hash;
+  int seg_last[1024];  // ordered path only
+};
+
+// include/cscpp/voxel_grid_occlusion_estimation.h:143-157 with r = ijk - min_b
+__device__ __forceinline__ float centre(const GridView& g, int c, int r) {
+  return fadd(g.base[c], fmul((float)r, g.leaf));
+}
+
+// voxel_grid_occlusion_estimation.cpp:174-238
+__device__ __forceinline__ float ray_box(const GridView& g, const float o[3], const float d[3]) {
+  float tmin, tmax, tymin, tymax, tzmin, tzmax;
+  if (d[0] >= 0) { tmin = fdiv(fsub(g.b_min[0], o[0]), d[0]); tmax = fdiv(fsub(g.b_max[0], o[0]), d[0]); }
+  else           { tmin = fdiv(fsub(g.b_max[0], o[0]), d[0]); tmax = fdiv(fsub(g.b_min[0], o[0]), d[0]); }
+  if (d[1] >= 0) { tymin = fdiv(fsub(g.b_min[1], o[1]), d[1]); tymax = fdiv(fsub(g.b_max[1], o[1]), d[1]); }
+  else           { tymin = fdiv(fsub(g.b_max[1], o[1]), d[1]); tymax = fdiv(fsub(g.b_min[1], o[1]), d[1]); }
+  if ((tmin > tymax) || (tymin > tmax)) return -1.0f;
+  if (tymin > tmin) tmin = tymin;
+  if (tymax < tmax) tmax = tymax;
+  if (d[2] >= 0) { tzmin = fdiv(fsub(g.b_min[2], o[2]), d[2]); tzmax = fdiv(fsub(g.b_max[2], o[2]), d[2]); }
+  else           { tzmin = fdiv(fsub(g.b_max[2], o[2]), d[2]); tzmax = fdiv(fsub(g.b_min[2], o[2]), d[2]); }
+  if ((tmin > tzmax) || (tzmin > tmax)) return -1.0f;
+  if (tzmin > tmin) tmin = tzmin;
+  return tmin;
+}
+
+// (centre - origin).normalize() on a Vector4f whose w is 0 - 0; <Eigen> squaredNorm = (v0^2+v2^2)+(v1^2+0)
+__device__ __forceinline__ void direction(const float ctr[3], const float o[3], float d[3]) {
+  float v0 = fsub(ctr[0], o[0]), v1 = fsub(ctr[1], o[1]), v2 = fsub(ctr[2], o[2]);
+  float n2 = fadd(fadd(fmul(v0, v0), fmul(v2, v2)), fadd(fmul(v1, v1), 0.0f));
+  float nrm = __fsqrt_rn(n2);
+  d[0] = fdiv(v0, nrm); d[1] = fdiv(v1, nrm); d[2] = fdiv(v2, nrm);
+}
+
+// occlusionEstimation + rayTraversal (voxel_grid_occlusion_estimation.cpp:99-128, 410-582) for the
+// voxel at relative coordinates rt (= ijk - min_b) with cell centre tc.  Returns 0 free, 1 occluded,
+// 2 failed (tmin == -1: the caller's `state` stays untouched, quirk Q5).  The walk stops at the first
+// qualifying occluder: the reference keeps walking but its result can only stay 1 (:561-562).
+__device__ __forceinline__ int occlusion_estimation(const GridView& g, const uint32_t* grid, const float origin[3],
+                                                    const int rt[3], const float tc[3], unsigned& steps) {
+  float d[3];
+  direction(tc, origin, d);                 // :111-113
+  float tmin = ray_box(g, origin, d);       // :116
+  if (tmin == -1.0f) return 2;              // :118-122
+  float t_max[3], t_delta[3];
+  int r[3], step[3];
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    float start = fadd(origin[c], fmul(tmin, d[c]));                   // :422
+    int ijk = (int)floorf(fadd(fmul(start, g.inv), 0.5f));             // :425 (round = floor(x + 0.5f))
+    r[c] = ijk - g.min_b[c];
+    float vm = centre(g, c, r[c]);                                     // :432
+    if (d[c] >= 0) { vm = fadd(vm, g.half); step[c] = 1; }             // :436-465
+    else           { vm = fsub(vm, g.half); step[c] = -1; }
+    t_max[c] = fadd(tmin, fdiv(fsub(vm, start), d[c]));                // :513-515
+    t_delta[c] = fdiv(g.leaf, fabsf(d[c]));                            // :517-519
+  }
+  const int istep1 = step[1] * g.mul1, istep2 = step[2] * g.mul2;
+  int idx = r[0] + r[1] * g.mul1 + r[2] * g.mul2;  // <PCL getCentroidIndexAt> dense linearisation (Q3)
+  int result = 0;
+  unsigned n = 0;
+  // loop bounds :538-540: ijk <= max_b + 1 && ijk + 1 >= min_b  <=>  -1 <= r <= div
+  while ((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
+         (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1)) {
+    ++n;
+    if (r[0] == rt[0] && r[1] == rt[1] && r[2] == rt[2]) break;        // :551-552
+    if ((unsigned)idx < g.cells && ((grid[idx >> 5] >> (idx & 31)) & 1u)) {  // :555-556 (only the linear range is checked)
+      float dx = fsub(centre(g, 0, r[0]), tc[0]), dy = fsub(centre(g, 1, r[1]), tc[1]),
+            dz = fsub(centre(g, 2, r[2]), tc[2]);
+      float sum = fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz)); // :560
+      if (sum > g.thr_sq) { result = 1; break; }                        // :561 sqrt(double(sum)) > leaf*2
+    }
+    if (t_max[0] <= t_max[1] && t_max[0] <= t_max[2]) {                 // :565-569
+      t_max[0] = fadd(t_max[0], t_delta[0]); r[0] += step[0]; idx += step[0];
+    } else if (t_max[1] <= t_max[2] && t_max[1] <= t_max[0]) {          // :570-574
+      t_max[1] = fadd(t_max[1], t_delta[1]); r[1] += step[1]; idx += istep1;
+    } else {                                                            // :575-579
+      t_max[2] = fadd(t_max[2], t_delta[2]); r[2] += step[2]; idx += istep2;
+    }
+  }
+  steps += n;
+  return result;
+}
+
+// second gate, occlusion_culling.cpp:338-342: ray from the MODEL cloud's sensor origin (Q6)
+__device__ __forceinline__ bool second_gate(const GridView& g, const float pcd_origin[3], const float tc[3]) {
+  float d[3];
+  direction(tc, pcd_origin, d);
+  return ray_box(g, pcd_origin, d) != -1.0f;
+}
+
+__device__ __forceinline__ bool bit_test(const uint32_t* b, uint32_t i) { return (b[i >> 5] >> (i & 31)) & 1u; }
+
+__device__ __forceinline__ unsigned warp_sum(unsigned v) { return __reduce_add_sync(0xffffffffu, v); }
+
+// ------------------------------------------------------------------------------------------------
+// P1 + P2: cull.  Fills sh.survivors / bb_* / surv_hash and the per-CTA list of occupied voxels
+// (duplicates possible when a voxel's points straddle two 32-point loads; P3 removes them).
+// ------------------------------------------------------------------------------------------------
+__device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list) {
+  const ModelDev& m = A.m;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const bool brute = (A.flags & ASSCPP_EVAL_BRUTE) != 0;
+  const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
+  if (!brute) {
+    // P1: 32 super-chunks per warp step, then the 32 children of each surviving super-chunk
+    for (int64_t s0 = (int64_t)warp * 32; s0 < m.n_super; s0 += (int64_t)nwarps * 32) {
+      int64_t s = s0 + lane;
+      bool keep = false;
+      if (s < m.n_super) {
+        float4 lo = m.super_lo[s], hi = m.super_hi[s];
+        keep = !box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+      }
+      unsigned sb = __ballot_sync(0xffffffffu, keep);
+      while (sb) {
+        int b = __ffs(sb) - 1;
+        sb &= sb - 1;
+        int64_t c = (s0 + b) * kSuperFanout + lane;
+        bool ck = false;
+        float4 lo, hi;
+        if (c < m.n_chunks) {
+          lo = m.chunk_lo[c]; hi = m.chunk_hi[c];
+          ck = !box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+        }
+        unsigned cb = __ballot_sync(0xffffffffu, ck);
+        if (cb) {
+          unsigned base = 0;
+          if (lane == 0) base = atomicAdd(&sh.chunk_count, (unsigned)__popc(cb));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (ck) chunk_list[base + __popc(cb & ((1u << lane) - 1))] = make_uint2(__float_as_uint(lo.w), __float_as_uint(hi.w));
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // P2: exact test, 32 points per warp step
+  const int64_t nwork = brute ? m.n_chunks : (int64_t)sh.chunk_count;
+  int bmin[3] = {INT_MAX, INT_MAX, INT_MAX}, bmax[3] = {INT_MIN, INT_MIN, INT_MIN};
+  unsigned surv = 0;
+  unsigned long long shash = 0;
+  for (int64_t w = warp; w < nwork; w += nwarps) {
+    uint32_t pb, pe;
+    if (brute) { pb = __float_as_uint(m.chunk_lo[w].w); pe = __float_as_uint(m.chunk_hi[w].w); }
+    else { uint2 r = chunk_list[w]; pb = r.x; pe = r.y; }
+    for (uint32_t base = pb; base < pe; base += 32) {
+      uint32_t pos = base + lane;
+      bool pass = false;
+      uint32_t u = 0xffffffffu;
+      if (pos < pe) {
+        float4 p = m.pts[pos];
+        u = __float_as_uint(p.w);
+        pass = point_in_frustum(sh.planes, p.x, p.y, p.z);
+      }
+      unsigned pm = __ballot_sync(0xffffffffu, pass);
+      if (!pm) continue;
+      surv += (lane == 0) ? (unsigned)__popc(pm) : 0u;
+      if (want_hash && pass) shash += mix64((uint64_t)(uint32_t)m.orig[pos]);
+      // first passing lane of every run of equal voxel ids emits the voxel
+      uint32_t u_prev = __shfl_up_sync(0xffffffffu, u, 1);
+      bool head = (lane == 0) || (u != u_prev);
+      unsigned hb = __ballot_sync(0xffffffffu, head);
+      unsigned below = hb & ((2u << lane) - 1);          // heads at or below this lane
+      int my_head = 31 - __clz(below);
+      unsigned run_lower = pm & ((1u << lane) - 1) & ~((1u << my_head) - 1);  // passing lanes of my run below me
+      bool emit = pass && (run_lower == 0);
+      unsigned eb = __ballot_sync(0xffffffffu, emit);
+      unsigned slot = 0;
+      if (lane == 0) slot = atomicAdd(&sh.list_count, (unsigned)__popc(eb));
+      slot = __shfl_sync(0xffffffffu, slot, 0);
+      if (emit) {
+        unsigned at = slot + __popc(eb & ((1u << lane) - 1));
+        if (at < A.list_cap) vox_list[at] = u;
+        int4 vx = m.vox[u];
+        bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
+        bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
+      }
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    int lo = __reduce_min_sync(0xffffffffu, bmin[c]), hi = __reduce_max_sync(0xffffffffu, bmax[c]);
+    if (lane == 0 && lo <= hi) { atomicMin(&sh.bb_min[c], lo); atomicMax(&sh.bb_max[c], hi); }
+  }
+  if (lane == 0 && surv) atomicAdd(&sh.survivors, surv);
+  if (want_hash) {
+    for (int o = 16; o; o >>= 1) shash += __shfl_xor_sync(0xffffffffu, shash, o);
+    if (lane == 0 && shash) atomicAdd(&sh.surv_hash, shash);
+  }
+  __syncthreads();
+}
+
+// ------------------------------------------------------------------------------------------------
+// P3: grid geometry from the survivors' box, zero + fill the bit-grid, drop duplicate list entries.
+// Returns the grid pointer (shared or global).  Must be called by all threads.
+// ------------------------------------------------------------------------------------------------
+__device__ uint32_t* build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_grid, uint32_t* glob_grid,
+                                uint32_t* vox_list) {
+  const ModelDev& m = A.m;
+  if (threadIdx.x == 0) {
+    GridView& g = sh.g;
+    g.leaf = m.leaf; g.inv = m.inv_leaf; g.half = m.half_leaf; g.thr_sq = m.dist_thr_sq;
+    unsigned long long cells = 1;
+    for (int c = 0; c < 3; ++c) {
+      // <PCL applyFilter>: min_b = floor(min_p * inv), max_b likewise; floor(x*inv) is monotone in x, so the
+      // box of the survivors' voxel coordinates is the same box.
+      g.min_b[c] = sh.bb_min[c];
+      g.div[c] = sh.bb_max[c] - sh.bb_min[c] + 1;
+      g.b_min[c] = fmul((float)sh.bb_min[c], m.leaf);        // voxel_grid_occlusion_estimation.cpp:53-55
+      g.b_max[c] = fmul((float)(sh.bb_max[c] + 1), m.leaf);  // :56-58
+      g.base[c] = fadd(g.b_min[c], m.half_leaf);
+      cells *= (unsigned long long)g.div[c];
+    }
+    g.mul1 = g.div[0];
+    g.mul2 = g.div[0] * g.div[1];
+    g.cells = (unsigned)cells;
+    unsigned long long words = (cells + 31) / 32;
+    sh.words = (unsigned)words;
+    bool fits_smem = words <= A.smem_grid_words && !(A.flags & ASSCPP_EVAL_FORCE_GLOBAL);
+    sh.use_smem = fits_smem ? 1 : 0;
+    sh.status |= fits_smem ? ASSCPP_VS_GRID_SHARED : ASSCPP_VS_GRID_GLOBAL;
+    if ((!fits_smem && words > (unsigned long long)A.grid_cap_words) || sh.list_count > A.list_cap) {
+      sh.status |= kVsError;  // scratch bound violated: report, do not touch memory out of range
+      sh.words = 0;
+      sh.list_count = 0;
+    }
+  }
+  __syncthreads();
+  uint32_t* grid = sh.use_smem ? smem_grid : glob_grid;
+  for (unsigned w = threadIdx.x; w < sh.words; w += blockDim.x) grid[w] = 0;
+  __syncthreads();
+  const GridView& g = sh.g;
+  unsigned uniq = 0;
+  for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
+    uint32_t u = vox_list[e];
+    int4 vx = m.vox[u];
+    int idx = (vx.x - g.min_b[0]) + (vx.y - g.min_b[1]) * g.mul1 + (vx.z - g.min_b[2]) * g.mul2;
+    uint32_t bit = 1u << (idx & 31);
+    uint32_t old = atomicOr(&grid[idx >> 5], bit);
+    if (old & bit) vox_list[e] = 0xffffffffu;  // same voxel emitted by another 32-point load
+    else ++uniq;
+  }
+  uniq = warp_sum(uniq);
+  if ((threadIdx.x & 31) == 0 && uniq) atomicAdd(&sh.unique, uniq);
+  __syncthreads();
+  return grid;
+}
+
+// ------------------------------------------------------------------------------------------------
+// visit the survivors of a voxel that turned out visible: counts, gains, hash, optional OR.
+// mode 0: count/gain/hash; mode 1: OR into A.accum.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const ViewShared& sh, uint32_t u, int mode,
+                                                   uint32_t* cov_scratch, unsigned& vis, unsigned& gain_p,
+                                                   unsigned& gain_v, unsigned long long& vhash) {
+  const ModelDev& m = A.m;
+  const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
+  const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
+  bool any = false;
+  for (uint32_t pos = pb; pos < pe; ++pos) {
+    float4 p = m.pts[pos];
+    if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
+    any = true;
+    if (mode == 0) {
+      ++vis;
+      if (!A.covered.pts || !bit_test(A.covered.pts, pos)) ++gain_p;
+      if (want_hash) vhash += mix64((uint64_t)(uint32_t)m.orig[pos]);
+      if (!m.cov_same) {
+        uint32_t id = (uint32_t)m.pt_cov[pos], bit = 1u << (id & 31);
+        uint32_t old = atomicOr(&cov_scratch[id >> 5], bit);
+        if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
+      }
+    } else {
+      atomicOr(&A.accum.pts[pos >> 5], 1u << (pos & 31));
+      if (!m.cov_same) {
+        uint32_t id = (uint32_t)m.pt_cov[pos];
+        atomicOr(&A.accum.vox[id >> 5], 1u << (id & 31));
+      }
+    }
+  }
+  if (any && m.cov_same) {
+    uint32_t id = (uint32_t)m.vox_cov[u];
+    if (mode == 0) {
+      if (!A.covered.vox || !bit_test(A.covered.vox, id)) ++gain_v;
+    } else {
+      atomicOr(&A.accum.vox[id >> 5], 1u << (id & 31));
+    }
+  }
+}
+
+__device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
+  if (threadIdx.x < 24) sh.planes[threadIdx.x] = vd.planes[threadIdx.x];
+  if (threadIdx.x < 3) {
+    sh.origin[threadIdx.x] = vd.origin[threadIdx.x];
+    sh.bb_min[threadIdx.x] = INT_MAX;
+    sh.bb_max[threadIdx.x] = INT_MIN;
+  }
+  if (threadIdx.x == 0) {
+    sh.view = v;
+    sh.chunk_count = 0; sh.list_count = 0;
+    sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
+    sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
+    sh.words = 0; sh.use_smem = 1;
+    sh.g.cells = 0;
+  }
+}
+
+__device__ void write_result(const EvalArgs& A, const ViewShared& sh, int v) {
+  AsscppViewResult r;
+  r.survivors = sh.survivors; r.visible = sh.visible; r.carry = sh.carry; r.unique_rays = sh.unique;
+  r.gain_pts = sh.gain_p; r.gain_vox = sh.gain_v; r.status = sh.status; r.reserved = 0;
+  r.cells = sh.survivors ? (uint64_t)sh.g.cells : 0;
+  r.steps = sh.steps; r.vis_hash = sh.vis_hash; r.surv_hash = sh.surv_hash;
+  A.results[v] = r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// eval_views_kernel
+// ------------------------------------------------------------------------------------------------
+extern __shared__ __align__(16) unsigned char smem_raw[];
+
+__global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
+  ViewShared& sh = *reinterpret_cast<ViewShared*>(smem_raw);
+  uint32_t* smem_grid = reinterpret_cast<uint32_t*>(smem_raw + ((sizeof(ViewShared) + 15) & ~size_t(15)));
+  const ModelDev& m = A.m;
+  uint2* chunk_list = A.chunk_list + (int64_t)blockIdx.x * A.chunk_cap;
+  uint32_t* vox_list = A.vox_list + (int64_t)blockIdx.x * A.list_cap;
+  uint32_t* glob_grid = A.grid_scratch + (int64_t)blockIdx.x * A.grid_cap_words;
+  uint32_t* cov_scratch = A.cov_scratch + (int64_t)blockIdx.x * A.cov_words;
+  __shared__ int s_view;
+  for (;;) {
+    __syncthreads();
+    if (threadIdx.x == 0) s_view = atomicAdd(A.work_counter, 1);
+    __syncthreads();
+    const int v = s_view;
+    if (v >= A.nviews) break;
+    reset_view(sh, A.views[v], v);
+    __syncthreads();
+    cull_view(A, sh, chunk_list, vox_list);
+    if (sh.survivors == 0) {  // empty frustum cloud: extractVisibleSurface returns an empty cloud
+      if (threadIdx.x == 0) write_result(A, sh, v);
+      continue;
+    }
+    uint32_t* grid = build_grid(A, sh, smem_grid, glob_grid, vox_list);
+    // P4: one ray per occupied voxel
+    const GridView g = sh.g;
+    const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
+    const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
+    unsigned vis = 0, gain_p = 0, gain_v = 0, steps = 0, fails = 0;
+    unsigned long long vhash = 0;
+    for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
+      uint32_t u = vox_list[e];
+      if (u == 0xffffffffu) continue;
+      int4 vx = m.vox[u];
+      int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
+      float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
+      int state = occlusion_estimation(g, grid, origin, rt, tc, steps);
+      if (state == 2) { ++fails; continue; }
+      if (state != 1 && second_gate(g, pcd_o, tc)) {
+        vox_list[e] = u | 0x80000000u;
+        visit_voxel_points(A, sh, u, 0, cov_scratch, vis, gain_p, gain_v, vhash);
+      }
+    }
+    vis = warp_sum(vis); gain_p = warp_sum(gain_p); gain_v = warp_sum(gain_v); fails = warp_sum(fails);
+    unsigned long long st64 = steps;
+    for (int o = 16; o; o >>= 1) {
+      st64 += __shfl_xor_sync(0xffffffffu, st64, o);
+      vhash += __shfl_xor_sync(0xffffffffu, vhash, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+      if (vis) atomicAdd(&sh.visible, vis);
+      if (gain_p) atomicAdd(&sh.gain_p, gain_p);
+      if (gain_v) atomicAdd(&sh.gain_v, gain_v);
+      if (fails) atomicAdd(&sh.carry, fails);
+      if (st64) atomicAdd(&sh.steps, st64);
+      if (vhash) atomicAdd(&sh.vis_hash, vhash);
+    }
+    __syncthreads();
+    if (!m.cov_same && sh.visible) {
+      for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
+    }
+    if (sh.carry) {
+      // quirk Q5: at least one ray failed; the sticky `state` makes the result order dependent.
+      // Hand the view to ordered_views_kernel, which replays the reference loop exactly.
+      if (threadIdx.x == 0) {
+        int at = atomicAdd(A.ordered_count, 1);
+        A.ordered_list[at] = v;
+        sh.status |= ASSCPP_VS_ORDERED;
+        write_result(A, sh, v);
+      }
+      continue;
+    }
+    // P5: OR the visible set into the accumulator (heuristic.cpp:344-346)
+    if (A.accum.pts && (int64_t)sh.visible > A.accum_min_visible) {
+      unsigned d0 = 0, d1 = 0, d2 = 0;
+      unsigned long long d3 = 0;
+      for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
+        uint32_t u = vox_list[e];
+        if (u == 0xffffffffu || !(u & 0x80000000u)) continue;
+        visit_voxel_points(A, sh, u & 0x7fffffffu, 1, cov_scratch, d0, d1, d2, d3);
+      }
+    }
+    if (threadIdx.x == 0) write_result(A, sh, v);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// ordered_views_kernel: exact replay of occlusion_culling.cpp:308-370 in ORIGINAL index order for
+// the views in which occlusionEstimation failed.  Slow by design (two passes over all N points,
+// one CTA per view); such views need tmin == -1.0f exactly and are rare.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A) {
+  ViewShared& sh = *reinterpret_cast<ViewShared*>(smem_raw);
+  uint32_t* smem_grid = reinterpret_cast<uint32_t*>(smem_raw + ((sizeof(ViewShared) + 15) & ~size_t(15)));
+  const ModelDev& m = A.m;
+  uint2* chunk_list = A.chunk_list + (int64_t)blockIdx.x * A.chunk_cap;
+  uint32_t* vox_list = A.vox_list + (int64_t)blockIdx.x * A.list_cap;
+  uint32_t* glob_grid = A.grid_scratch + (int64_t)blockIdx.x * A.grid_cap_words;
+  uint32_t* cov_scratch = A.cov_scratch + (int64_t)blockIdx.x * A.cov_words;
+  uint8_t* vstate = A.vstate + (int64_t)blockIdx.x * m.n_vox;
+  const int nflag = *A.ordered_count;
+  const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
+  for (int q = blockIdx.x; q < nflag; q += gridDim.x) {
+    const int v = A.ordered_list[q];
+    __syncthreads();
+    reset_view(sh, A.views[v], v);
+    __syncthreads();
+    cull_view(A, sh, chunk_list, vox_list);
+    uint32_t* grid = build_grid(A, sh, smem_grid, glob_grid, vox_list);
+    const GridView g = sh.g;
+    const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
+    const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
+    // per-voxel state: bits 0-1 = 0 free / 1 occluded / 2 failed, bit 2 = second gate passes
+    unsigned steps = 0;
+    for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
+      uint32_t u = vox_list[e];
+      if (u == 0xffffffffu) continue;
+      int4 vx = m.vox[u];
+      int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
+      float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
+      int state = occlusion_estimation(g, grid, origin, rt, tc, steps);
+      vstate[u] = (uint8_t)(state | (second_gate(g, pcd_o, tc) ? 4 : 0));
+    }
+    unsigned long long st64 = steps;
+    for (int o = 16; o; o >>= 1) st64 += __shfl_xor_sync(0xffffffffu, st64, o);
+    if ((threadIdx.x & 31) == 0 && st64) atomicAdd(&sh.steps, st64);
+    __syncthreads();
+    // ordered scan over original indices, one contiguous segment per thread
+    const int64_t seg = (m.n + blockDim.x - 1) / blockDim.x;
+    const int64_t j0 = (int64_t)threadIdx.x * seg, j1 = min(m.n, j0 + seg);
+    int last = -1;
+    for (int64_t j = j0; j < j1; ++j) {
+      uint32_t pos = (uint32_t)m.pos_of[j];
+      float4 p = m.pts[pos];
+      uint8_t s = vstate[__float_as_uint(p.w)];
+      if (s == 0xff) continue;
+      if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
+      if ((s & 3) != 2) last = s & 3;
+    }
+    sh.seg_last[threadIdx.x] = last;
+    __syncthreads();
+    int state = 0;  // canonical initial value of the uninitialised `state` (occlusion_culling.cpp:308)
+    for (int t = (int)threadIdx.x - 1; t >= 0; --t)
+      if (sh.seg_last[t] >= 0) { state = sh.seg_last[t]; break; }
+    for (int pass = 0; pass < 2; ++pass) {
+      // pass 0 counts; pass 1 ORs into the accumulator once the visible count is known
+      if (pass == 1 && !(A.accum.pts && (int64_t)sh.visible > A.accum_min_visible)) break;
+      int st = state;
+      unsigned vis = 0, gain_p = 0, gain_v = 0, carry = 0;
+      unsigned long long vhash = 0;
+      for (int64_t j = j0; j < j1; ++j) {
+        uint32_t pos = (uint32_t)m.pos_of[j];
+        float4 p = m.pts[pos];
+        uint8_t s = vstate[__float_as_uint(p.w)];
+        if (s == 0xff) continue;
+        if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
+        if ((s & 3) != 2) st = s & 3; else ++carry;       // :332 ret = -1 leaves state untouched
+        if (st != 1 && (s & 4)) {                         // :335, :342
+          uint32_t id = (uint32_t)m.pt_cov[pos], bit = 1u << (id & 31);
+          if (pass == 0) {
+            ++vis;
+            if (!A.covered.pts || !bit_test(A.covered.pts, pos)) ++gain_p;
+            if (want_hash) vhash += mix64((uint64_t)j);
+            uint32_t old = atomicOr(&cov_scratch[id >> 5], bit);
+            if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
+          } else {
+            atomicOr(&A.accum.pts[pos >> 5], 1u << (pos & 31));
+            atomicOr(&A.accum.vox[id >> 5], bit);
+          }
+        }
+      }
+      if (pass == 0) {
+        if (vis) atomicAdd(&sh.visible, vis);
+        if (gain_p) atomicAdd(&sh.gain_p, gain_p);
+        if (gain_v) atomicAdd(&sh.gain_v, gain_v);
+        if (carry) atomicAdd(&sh.carry, carry);
+        if (vhash) atomicAdd(&sh.vis_hash, vhash);
+      }
+      __syncthreads();
+    }
+    for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
+    for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
+      uint32_t u = vox_list[e];
+      if (u != 0xffffffffu) vstate[u] = 0xff;
+    }
+    if (threadIdx.x == 0) {
+      sh.status |= ASSCPP_VS_ORDERED;
+      write_result(A, sh, v);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// covered-set kernels
+// ------------------------------------------------------------------------------------------------
+__global__ void or_words_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, int64_t words) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] |= src[i];
+}
+
+// dst |= src[0] | src[1] | ... (nsrc bitsets laid out back to back): the local half of the OR-allreduce
+__global__ void or_reduce_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ src, int64_t words,
+                                 int nsrc) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (int64_t)gridDim.x * blockDim.x) {
+    uint32_t v = dst[i];
+    for (int r = 0; r < nsrc; ++r) v |= src[(int64_t)r * words + i];
+    dst[i] = v;
+  }
+}
+
+__global__ void popcount_kernel(const uint32_t* __restrict__ bits, int64_t words, unsigned long long* out) {
+  unsigned long long c = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (int64_t)gridDim.x * blockDim.x)
+    c += __popc(bits[i]);
+  for (int o = 16; o; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+
+// point bitset in sorted-position space <-> original index space
+__global__ void permute_bits_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst,
+                                    const int32_t* __restrict__ map, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    if ((src[i >> 5] >> (i & 31)) & 1u) {
+      uint32_t j = (uint32_t)map[i];
+      atomicOr(&dst[j >> 5], 1u << (j & 31));
+    }
+}
+
+// set bits of the listed ORIGINAL indices (and their coverage voxels)
+__global__ void or_points_kernel(CoveredDev set, const int32_t* __restrict__ idx, int64_t n, ModelDev m) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int32_t j = idx[i];
+    if (j < 0 || j >= m.n) continue;
+    uint32_t pos = (uint32_t)m.pos_of[j];
+    atomicOr(&set.pts[pos >> 5], 1u << (pos & 31));
+    uint32_t id = (uint32_t)m.pt_cov[pos];
+    atomicOr(&set.vox[id >> 5], 1u << (id & 31));
+  }
+}
+
+// calcCoveragePercent of an arbitrary cloud (occlusion_culling.cpp:387-428): voxelise at the coverage
+// leaf and mark the model coverage voxels hit.  keys = sorted linear keys of the model's coverage voxels.
+__global__ void cloud_cover_kernel(const float* __restrict__ xyz, int64_t n, float inv_cov, int3 cmin, int3 cdiv,
+                                   const long long* __restrict__ keys, int64_t nkeys, uint32_t* __restrict__ marks) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float x = xyz[3 * i], y = xyz[3 * i + 1], z = xyz[3 * i + 2];
+    float qx = fmul(x, inv_cov), qy = fmul(y, inv_cov), qz = fmul(z, inv_cov);
+    if (!(fabsf(qx) < 1e9f) || !(fabsf(qy) < 1e9f) || !(fabsf(qz) < 1e9f)) continue;
+    long long a = (long long)((int)floorf(qx)) - cmin.x, b = (long long)((int)floorf(qy)) - cmin.y,
+              c = (long long)((int)floorf(qz)) - cmin.z;
+    if (a < 0 || b < 0 || c < 0 || a >= cdiv.x || b >= cdiv.y || c >= cdiv.z) continue;
+    long long key = a + (long long)cdiv.x * (b + (long long)cdiv.y * c);
+    int64_t lo = 0, hi = nkeys;
+    while (lo < hi) {
+      int64_t mid = (lo + hi) >> 1;
+      if (keys[mid] < key) lo = mid + 1; else hi = mid;
+    }
+    if (lo < nkeys && keys[lo] == key) atomicOr(&marks[lo >> 5], 1u << (lo & 31));
+  }
+}
+
+__global__ void fill_bytes_kernel(uint8_t* p, int64_t n, uint8_t v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-side launchers
+// ------------------------------------------------------------------------------------------------
+size_t eval_smem_bytes(uint32_t grid_words) { return ((sizeof(ViewShared) + 15) & ~size_t(15)) + (size_t)grid_words * 4; }
+size_t eval_smem_header_bytes() { return ((sizeof(ViewShared) + 15) & ~size_t(15)); }
+
+cudaError_t configure_kernels(size_t smem_bytes) {
+  cudaError_t e = cudaFuncSetAttribute(eval_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(ordered_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+}
+
+void launch_planes(const double* d_poses, int64_t nviews, const FrustumConst& fc, ViewDev* views, cudaStream_t s) {
+  if (nviews <= 0) return;
+  int threads = 128;
+  int blocks = (int)((nviews + threads - 1) / threads);
+  planes_kernel<<<blocks, threads, 0, s>>>(d_poses, nviews, fc, views);
+}
+void launch_eval(const EvalArgs& a, int ctas, size_t smem_bytes, cudaStream_t s) {
+  eval_views_kernel<<<ctas, 1024, smem_bytes, s>>>(a);
+}
+void launch_ordered(const EvalArgs& a, int ctas, size_t smem_bytes, cudaStream_t s) {
+  ordered_views_kernel<<<ctas, 1024, smem_bytes, s>>>(a);
+}
+static inline int blocks_for(int64_t n, int threads, int cap) {
+  int64_t b = (n + threads - 1) / threads;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+void launch_or_words(uint32_t* dst, const uint32_t* src, int64_t words, cudaStream_t s) {
+  if (words > 0) or_words_kernel<<<blocks_for(words, 256, 1184), 256, 0, s>>>(dst, src, words);
+}
+void launch_or_reduce(uint32_t* dst, const uint32_t* src, int64_t words, int nsrc, cudaStream_t s) {
+  if (words > 0) or_reduce_kernel<<<blocks_for(words, 256, 1184), 256, 0, s>>>(dst, src, words, nsrc);
+}
+void launch_popcount(const uint32_t* bits, int64_t words, unsigned long long* out, cudaStream_t s) {
+  if (words > 0) popcount_kernel<<<blocks_for(words, 256, 1184), 256, 0, s>>>(bits, words, out);
+}
+void launch_permute_bits(const uint32_t* src, uint32_t* dst, const int32_t* map, int64_t n, cudaStream_t s) {
+  if (n > 0) permute_bits_kernel<<<blocks_for(n, 256, 2368), 256, 0, s>>>(src, dst, map, n);
+}
+void launch_or_points(CoveredDev set, const int32_t* idx, int64_t n, const ModelDev& m, cudaStream_t s) {
+  if (n > 0) or_points_kernel<<<blocks_for(n, 256, 1184), 256, 0, s>>>(set, idx, n, m);
+}
+void launch_cloud_cover(const float* xyz, int64_t n, float inv_cov, const int32_t cmin[3], const int32_t cdiv[3],
+                        const int64_t* keys, int64_t nkeys, uint32_t* marks, cudaStream_t s) {
+  if (n > 0)
+    cloud_cover_kernel<<<blocks_for(n, 256, 1184), 256, 0, s>>>(xyz, n, inv_cov, make_int3(cmin[0], cmin[1], cmin[2]),
+                                                                make_int3(cdiv[0], cdiv[1], cdiv[2]),
+                                                                (const long long*)keys, nkeys, marks);
+}
+void launch_fill_bytes(uint8_t* p, int64_t n, uint8_t v, cudaStream_t s) {
+  if (n > 0) fill_bytes_kernel<<<blocks_for(n, 256, 1184), 256, 0, s>>>(p, n, v);
+}
+
+}  // namespace asscpp

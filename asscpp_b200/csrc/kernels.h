@@ -1,0 +1,25 @@
+// kernels.h -- host-callable launchers of kernels.cu
+#pragma once
+#include <cuda_runtime.h>
+
+#include "common.h"
+
+namespace asscpp {
+
+size_t eval_smem_bytes(uint32_t grid_words);
+size_t eval_smem_header_bytes();
+cudaError_t configure_kernels(size_t smem_bytes);
+
+void launch_planes(const double* d_poses, int64_t nviews, const FrustumConst& fc, ViewDev* views, cudaStream_t s);
+void launch_eval(const EvalArgs& a, int ctas, size_t smem_bytes, cudaStream_t s);
+void launch_ordered(const EvalArgs& a, int ctas, size_t smem_bytes, cudaStream_t s);
+void launch_or_words(uint32_t* dst, const uint32_t* src, int64_t words, cudaStream_t s);
+void launch_or_reduce(uint32_t* dst, const uint32_t* src, int64_t words, int nsrc, cudaStream_t s);
+void launch_popcount(const uint32_t* bits, int64_t words, unsigned long long* out, cudaStream_t s);
+void launch_permute_bits(const uint32_t* src, uint32_t* dst, const int32_t* map, int64_t n, cudaStream_t s);
+void launch_or_points(CoveredDev set, const int32_t* idx, int64_t n, const ModelDev& m, cudaStream_t s);
+void launch_cloud_cover(const float* xyz, int64_t n, float inv_cov, const int32_t cmin[3], const int32_t cdiv[3],
+                        const int64_t* keys, int64_t nkeys, uint32_t* marks, cudaStream_t s);
+void launch_fill_bytes(uint8_t* p, int64_t n, uint8_t v, cudaStream_t s);
+
+}  // namespace asscpp

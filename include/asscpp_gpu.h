@@ -1,0 +1,179 @@
+/*
+ * asscpp_gpu.h -- C ABI of the B200-native coverage-evaluation path.
+ *
+ * This is the drop-in boundary.  The reference (kucars/asscpp) has no FFI of its own: its hot
+ * path is the C++ class OcclusionCulling (cscpp/include/cscpp/occlusion_culling.h:50-95) called
+ * by SSPP::CoveragePathPlanningHeuristic (cscpp/src/coverage_path_planning_heuristic.cpp).  The
+ * functions below are what a C++ shim of that class (include/cscpp/occlusion_culling_b200.h) and
+ * the viewpoint batcher bind to.  Each entry point names the reference code it replaces.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a negative
+ * ASSCPP_E* code; no exceptions cross the boundary; one context per GPU; calls on one context
+ * must come from one host thread at a time.  There is no CPU fallback: without a CUDA device
+ * asscpp_create fails with ASSCPP_ENODEVICE.
+ */
+#ifndef ASSCPP_GPU_H_
+#define ASSCPP_GPU_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ASSCPP_ABI_VERSION 1
+
+enum {
+  ASSCPP_OK = 0,
+  ASSCPP_EINVAL = -1,     /* bad argument                                                  */
+  ASSCPP_ENODEVICE = -2,  /* no usable CUDA device (there is no CPU path)                   */
+  ASSCPP_ECUDA = -3,      /* CUDA runtime error, text in asscpp_last_error                  */
+  ASSCPP_ERANGE = -4,     /* grid too large (PCL: "Leaf size is too small") / coords not finite */
+  ASSCPP_ENOMEM = -5,
+  ASSCPP_ESTATE = -6,     /* call order (e.g. results requested before an eval)             */
+  ASSCPP_ENCCL = -7       /* NCCL unavailable or failed                                     */
+};
+
+/* Hard-coded literals of the reference turned into parameters.
+ * Defaults: occlusion_culling.cpp:41 (voxelRes 0.5f), :73-76 (VFOV 45, HFOV 58, near 0.7, far 6.0),
+ * pcd_origin = PCD VIEWPOINT translation used at occlusion_culling.cpp:338-341,
+ * cov_leaf = coverage_path_planning_heuristic.cpp:479 (0.5f). */
+typedef struct AsscppParams {
+  float leaf;
+  float hfov_deg;
+  float vfov_deg;
+  float near_dist;
+  float far_dist;
+  float pcd_origin[3];
+  float cov_leaf;
+} AsscppParams;
+
+typedef struct AsscppModelInfo {
+  int64_t n_points;
+  int64_t n_occ_voxels;  /* occupied voxels, occlusion lattice                        */
+  int64_t n_cov_voxels;  /* OriginalVoxelsSize (occlusion_culling.cpp:50-65)          */
+  int64_t n_chunks;      /* leaf buckets of the cull hierarchy                        */
+  int32_t min_b[3];      /* model box on the occlusion lattice                        */
+  int32_t max_b[3];
+  int32_t sm_count;
+  int32_t reserved;
+} AsscppModelInfo;
+
+/* Per-viewpoint result of asscpp_eval_batch (one "VE"). */
+typedef struct AsscppViewResult {
+  uint32_t survivors;   /* S_v  : points passing FrustumCullingTT::applyFilter (frustum_culling.cpp:150-171) */
+  uint32_t visible;     /* Vis_v: size of extractVisibleSurface's cloud (occlusion_culling.cpp:371)          */
+  uint32_t carry;       /* Q5 events: occlusionEstimation returned -1 (occlusion_culling.cpp:332)             */
+  uint32_t unique_rays; /* U_v  : occupied cells of the per-view grid = distinct DDA rays                     */
+  uint32_t gain_pts;    /* |visible \ covered points|                                                         */
+  uint32_t gain_vox;    /* |coverage voxels(visible) \ covered voxels| (heuristic.cpp:473-483 in bitset form) */
+  uint32_t status;      /* ASSCPP_VS_* bits                                                                   */
+  uint32_t reserved;
+  uint64_t cells;       /* G_v: cells of the per-view grid                                                    */
+  uint64_t steps;       /* DDA loop iterations over the unique rays (early exit at the first occluder)        */
+  uint64_t vis_hash;    /* sum of mix64(original index) over the visible set   (ASSCPP_EVAL_HASH)             */
+  uint64_t surv_hash;   /* same over the survivors                              (ASSCPP_EVAL_HASH)            */
+} AsscppViewResult;
+
+enum {
+  ASSCPP_VS_GRID_SHARED = 1u, /* per-view bit-grid lived in shared memory                    */
+  ASSCPP_VS_GRID_GLOBAL = 2u, /* ... in the per-CTA global (L2-resident) scratch             */
+  ASSCPP_VS_ORDERED = 4u      /* a Q5 carry happened; view re-evaluated by the ordered path  */
+};
+
+/* flags of asscpp_eval_batch */
+enum {
+  ASSCPP_EVAL_HASH = 1u,        /* also compute vis_hash / surv_hash                               */
+  ASSCPP_EVAL_BRUTE = 2u,       /* no bucket pre-cull: stream every point for every view           */
+  ASSCPP_EVAL_FORCE_GLOBAL = 4u /* keep every per-view grid in global memory (test / profiling)    */
+};
+
+typedef struct AsscppCtx AsscppCtx;
+
+/* -- lifetime ------------------------------------------------------------------------------- */
+/* Replaces OcclusionCulling::OcclusionCulling (occlusion_culling.cpp:26-79): takes the model
+ * cloud (n x {x,y,z} float32, host memory), builds the device-resident point SoA, the model
+ * voxel tables and OriginalVoxelsSize.  device = CUDA ordinal. */
+int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* params, AsscppCtx** out);
+int asscpp_destroy(AsscppCtx* ctx);
+const char* asscpp_last_error(const AsscppCtx* ctx); /* ctx may be NULL: last create error */
+int asscpp_abi_version(void);
+int asscpp_model_info(const AsscppCtx* ctx, AsscppModelInfo* out);
+void asscpp_default_params(AsscppParams* p);
+
+/* -- batched viewpoint evaluation ------------------------------------------------------------ */
+/* Replaces the per-viewpoint call OcclusionCulling::extractVisibleSurface (occlusion_culling.cpp:
+ * 265-373) as issued by calculateHeuristic (heuristic.cpp:439-445) and isFilteringConditionSatisfied
+ * (:339-354), for nviews poses at once.  poses: nviews x {x y z qx qy qz qw} doubles, host memory.
+ * covered_set: handle from asscpp_covered_new to score gains against, or -1 for the empty set.
+ * Asynchronous on the context's stream; results are fetched with asscpp_get_results. */
+int asscpp_eval_batch(AsscppCtx* ctx, const double* poses, int64_t nviews, int covered_set, uint32_t flags);
+int asscpp_get_results(AsscppCtx* ctx, AsscppViewResult* out, int64_t nviews); /* synchronises */
+int asscpp_get_counts(AsscppCtx* ctx, uint32_t* survivors, uint32_t* visible, uint32_t* carry, int64_t nviews);
+int asscpp_get_gain(AsscppCtx* ctx, uint32_t* gain_pts, uint32_t* gain_vox, int64_t nviews);
+
+/* Same evaluation with device-resident poses (nviews x 7 doubles already in HBM) and results left
+ * on the device (AsscppViewResult[nviews], device pointer returned).  Used by the batcher when
+ * poses are generated on the device and by the kernel-only benchmark leg. */
+int asscpp_eval_batch_device(AsscppCtx* ctx, const double* d_poses, int64_t nviews, int covered_set,
+                             uint32_t flags, const AsscppViewResult** d_results);
+
+/* extractVisibleSurface for one pose: ascending original point indices of the visible cloud. */
+int asscpp_get_visible(AsscppCtx* ctx, const double pose[7], int32_t* idx_out, int64_t cap, int64_t* n_out);
+
+/* -- covered sets (Node::cloud_filtered / globalCloud as bitsets) ------------------------------ */
+int asscpp_covered_new(AsscppCtx* ctx, int* set_out);
+int asscpp_covered_free(AsscppCtx* ctx, int set);
+int asscpp_covered_clear(AsscppCtx* ctx, int set);
+int asscpp_covered_clone(AsscppCtx* ctx, int src, int* set_out);
+int asscpp_covered_or_set(AsscppCtx* ctx, int dst, int src);
+/* union of the visible sets of the given views whose visible count exceeds min_visible
+ * (heuristic.cpp:344-346: "if(pts.size()>5) globalCloud += pts"; use -1 to take every view) */
+int asscpp_covered_or_views(AsscppCtx* ctx, int set, const double* poses, int64_t nviews, int64_t min_visible);
+int asscpp_covered_or_points(AsscppCtx* ctx, int set, const int32_t* idx, int64_t n); /* original indices */
+int asscpp_covered_popcount(AsscppCtx* ctx, int set, int64_t* n_points, int64_t* n_voxels);
+/* host bitsets, bit i of 64-bit word i/64: points in ORIGINAL index order; voxels by compact id
+ * (ascending k,j,i order of the model's coverage grid) */
+int asscpp_covered_export(AsscppCtx* ctx, int set, uint64_t* point_bits, uint64_t* voxel_bits);
+int asscpp_covered_import(AsscppCtx* ctx, int set, const uint64_t* point_bits, const uint64_t* voxel_bits);
+/* calcCoveragePercent (occlusion_culling.cpp:375-444) of a covered set, float32 arithmetic as :431-432 */
+int asscpp_coverage_percent(AsscppCtx* ctx, int set, float* pct);
+/* calcCoveragePercent of an arbitrary cloud (n x xyz float32, host memory) */
+int asscpp_coverage_percent_cloud(AsscppCtx* ctx, const float* xyz, int64_t n, float* pct);
+
+/* -- streams / timing -------------------------------------------------------------------------- */
+int asscpp_sync(AsscppCtx* ctx);
+void* asscpp_get_stream(AsscppCtx* ctx); /* cudaStream_t all kernels are launched on */
+int asscpp_timer_begin(AsscppCtx* ctx);           /* cudaEventRecord on that stream */
+int asscpp_timer_end(AsscppCtx* ctx, float* ms);  /* record + synchronise + elapsed  */
+/* kernels launched by this context since creation (the bench's gpu_launches claim) */
+int64_t asscpp_launch_count(const AsscppCtx* ctx);
+/* device time of the dominant kernel (eval_views) accumulated between timer_begin/timer_end */
+int asscpp_eval_kernel_ms(AsscppCtx* ctx, float* ms, int64_t* launches);
+
+/* -- multi-GPU: one context per rank, NCCL over NVLink ---------------------------------------- */
+int asscpp_comm_unique_id(uint8_t id_out[128]);
+int asscpp_comm_init(AsscppCtx* ctx, int nranks, int rank, const uint8_t id[128]);
+/* gain-score allgather: every rank contributes its nviews_local results; out (host) receives
+ * nranks * nviews_local results in rank order */
+int asscpp_allgather_results(AsscppCtx* ctx, int64_t nviews_local, AsscppViewResult* out);
+/* covered-bitset OR-allreduce (NCCL has no OR op: allgather + fused OR kernel) */
+int asscpp_allreduce_or(AsscppCtx* ctx, int set);
+int asscpp_comm_destroy(AsscppCtx* ctx);
+
+/* -- synthetic workloads of BASELINE.json configs 2/3/5 (host generators) ------- */
+/* structure_seed places the shapes (default 0xA55C0001); point_seed / view_seed drive the
+ * sampling streams (defaults 0xA55C0002 / 0xA55C0003).  Deterministic, host only. */
+int asscpp_synth_structure_v1(uint64_t structure_seed, uint64_t point_seed, int64_t n, float* xyz_out);
+int asscpp_synth_views_v1(uint64_t structure_seed, uint64_t view_seed, int64_t nviews, double* poses_out);
+
+/* sspp/src/sensors.cpp:47-90 robot pose -> sensor pose (batcher input), host, double */
+int asscpp_robot2sensor(const double robot_pose[7], const double offset[3], const double rpy[3],
+                        double sensor_pose[7]);
+/* frustum planes (l r t b f n) and camera origin of a pose: frustum_culling.cpp:75-141 */
+int asscpp_frustum_planes(const AsscppParams* p, const double pose[7], float planes[24], float origin[3]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
