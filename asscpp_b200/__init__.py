@@ -250,6 +250,9 @@ class CoverageContext:
         self._ck(self.L.asscpp_comm_init(self.h, nranks, rank, _ptr(uid, C.c_uint8)))
         self.nranks, self.rank = nranks, rank
 
+    def allgather_results_device(self, nviews_local):
+        self._ck(self.L.asscpp_allgather_results(self.h, nviews_local, None))
+
     def allgather_results(self, nviews_local):
         out = np.zeros(nviews_local * self.nranks, RESULT_DTYPE)
         self._ck(self.L.asscpp_allgather_results(self.h, nviews_local, out.ctypes.data_as(C.c_void_p)))

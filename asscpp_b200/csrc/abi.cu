@@ -740,7 +740,7 @@ static int ensure_gather(AsscppCtx* c, size_t bytes) {
 }
 
 int asscpp_allgather_results(AsscppCtx* c, int64_t nviews_local, AsscppViewResult* out) {
-  if (!c || !out || nviews_local < 0) return ASSCPP_EINVAL;
+  if (!c || nviews_local < 0) return ASSCPP_EINVAL;
   if (!c->comm) { c->err = "communicator not initialised"; return ASSCPP_ESTATE; }
   if (nviews_local > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
   cudaSetDevice(c->device);
@@ -750,9 +750,9 @@ int asscpp_allgather_results(AsscppCtx* c, int64_t nviews_local, AsscppViewResul
   if (bytes) {
     int r = g_nccl.AllGather(c->d_results, c->d_gather, bytes, kNcclUint8, c->comm, c->stream);
     if (r != 0) { c->err = "ncclAllGather failed"; return ASSCPP_ENCCL; }
-    CU(c, cudaMemcpyAsync(out, c->d_gather, bytes * c->nranks, cudaMemcpyDeviceToHost, c->stream));
+    if (out) CU(c, cudaMemcpyAsync(out, c->d_gather, bytes * c->nranks, cudaMemcpyDeviceToHost, c->stream));
   }
-  CU(c, cudaStreamSynchronize(c->stream));
+  if (out) CU(c, cudaStreamSynchronize(c->stream));  // out == NULL: gathered scores stay on the device, async
   return ASSCPP_OK;
 }
 

@@ -155,7 +155,8 @@ int asscpp_eval_kernel_ms(AsscppCtx* ctx, float* ms, int64_t* launches);
 int asscpp_comm_unique_id(uint8_t id_out[128]);
 int asscpp_comm_init(AsscppCtx* ctx, int nranks, int rank, const uint8_t id[128]);
 /* gain-score allgather: every rank contributes its nviews_local results; out (host) receives
- * nranks * nviews_local results in rank order */
+ * nranks * nviews_local results in rank order.  out == NULL keeps the gathered scores on the
+ * device and returns without synchronising. */
 int asscpp_allgather_results(AsscppCtx* ctx, int64_t nviews_local, AsscppViewResult* out);
 /* covered-bitset OR-allreduce (NCCL has no OR op: allgather + fused OR kernel) */
 int asscpp_allreduce_or(AsscppCtx* ctx, int set);
