@@ -1,0 +1,274 @@
+"""GPU parity tests (-m gpu): the sm_100a path, called through the C ABI, against the CPU oracle.
+
+Bar: bit-exact.  Every integer the path produces -- survivor / visible counts, carry events, unique
+rays, grid cells, DDA step counts, point and voxel gains, and 64-bit hashes of the survivor and visible
+index sets -- must equal the oracle's on the same inputs; visible index LISTS are compared verbatim on
+sampled views.  Epsilon classes E1-E5 are counted by the oracle and reported; no
+mismatch is tolerated inside them either.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, assert_results_equal
+
+pytestmark = pytest.mark.gpu
+
+NTHREADS = os.cpu_count() or 1
+
+
+@pytest.fixture(scope="module")
+def A(lib_built):
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    import asscpp_b200
+    return asscpp_b200
+
+
+@pytest.fixture(scope="module")
+def etihad_ctx(A, etihad):
+    ctx = A.CoverageContext(etihad[0], A.default_params())
+    yield ctx
+    ctx.close()
+
+
+@pytest.fixture(scope="module")
+def etihad_oracle(oracle_mod, etihad):
+    return oracle_mod.Oracle(etihad[0])
+
+
+def test_bundled_model_all_fixture_views(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
+    """Config 1: bundled model x the 2 x 1 225 sensor poses of cscpp/txt, reference defaults."""
+    poses = np.concatenate([space_2p5["cam0"], space_2p5["cam1"]])
+    res = etihad_ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    st = etihad_oracle.eval_batch(poses, memo=True, nthreads=NTHREADS)
+    assert_results_equal(oracle_mod, res, st, "etihad 2.5m")
+    assert int(res["visible"].sum()) > 500000
+    assert (res["status"] & 0x80000000 == 0).all()
+
+
+def test_bundled_model_large_search_space(A, oracle_mod, etihad_ctx, etihad_oracle, space_1p5):
+    """Config 1: the 2 x 17 583 poses of sspp/resources (1.5 m search space)."""
+    poses = np.concatenate([space_1p5["cam0"], space_1p5["cam1"]])
+    res = etihad_ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    st = etihad_oracle.eval_batch(poses, memo=True, nthreads=NTHREADS)
+    assert_results_equal(oracle_mod, res, st, "etihad 1.5m")
+
+
+def test_golden_fixture(A, oracle_mod, etihad_ctx, space_2p5):
+    """Committed golden vectors (tools/make_golden.py), no oracle run involved."""
+    g = np.load(os.path.join(GOLDEN, "etihad_oracle_golden.npz"))
+    poses = np.concatenate([space_2p5["cam0"], space_2p5["cam1"]])[g["view_index"]]
+    res = etihad_ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    assert_results_equal(oracle_mod, res, g["stats"], "golden")
+    vis = etihad_ctx.get_visible(poses[int(g["list_view"])])
+    assert np.array_equal(vis, g["visible_list"])
+
+
+def test_visible_lists_verbatim(A, etihad_ctx, etihad_oracle, space_2p5):
+    """extractVisibleSurface returns points in ascending original index order (occlusion_culling.cpp:317,371)."""
+    poses = np.concatenate([space_2p5["cam0"][600:700:7], space_2p5["cam1"][300:900:41]])
+    for pose in poses:
+        want = etihad_oracle.eval_view(pose)["visible"]
+        got = etihad_ctx.get_visible(pose)
+        assert np.array_equal(got, want)
+
+
+@pytest.mark.parametrize("flags_name", ["brute", "global_grid"])
+def test_alternate_paths_agree(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5, flags_name):
+    """Bucket pre-cull off (every point streamed per view) and the bit-grid kept in global memory
+    instead of shared memory: same bits."""
+    fl = A.EVAL_HASH | (A.EVAL_BRUTE if flags_name == "brute" else A.EVAL_FORCE_GLOBAL)
+    poses = np.concatenate([space_2p5["cam0"][::3], space_2p5["cam1"][1::3]])
+    res = etihad_ctx.eval_batch(poses, flags=fl)
+    st = etihad_oracle.eval_batch(poses, memo=True, nthreads=NTHREADS)
+    assert_results_equal(oracle_mod, res, st, flags_name)
+    want = A.VS_GRID_GLOBAL if flags_name == "global_grid" else A.VS_GRID_SHARED
+    assert ((res["status"] & 3 == want) | (res["survivors"] == 0)).all()
+
+
+@pytest.mark.parametrize("leaf,cov_leaf", [(0.5, 0.5), (0.05, 0.5), (0.05, 0.05), (0.2, 0.3)])
+def test_synthetic_structure(A, oracle_mod, leaf, cov_leaf):
+    """synth_structure_v1 at a size the oracle finishes in seconds; 0.05 m is the grid of configs 3/5."""
+    xyz = A.synth_structure(400_000)
+    poses = A.synth_views(600)
+    ctx = A.CoverageContext(xyz, A.default_params(leaf=leaf, cov_leaf=cov_leaf))
+    orc = oracle_mod.Oracle(xyz, oracle_mod.make_params(leaf=leaf, cov_leaf=cov_leaf))
+    assert ctx.n_cov_voxels == orc.n_cov and ctx.n_occ_voxels == orc.n_occ
+    res = ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    st = orc.eval_batch(poses, memo=True, nthreads=NTHREADS)
+    assert_results_equal(oracle_mod, res, st, "synth leaf %g cov %g" % (leaf, cov_leaf))
+    for v in np.nonzero(st[:, oracle_mod.ST_VISIBLE] > 0)[0][:3]:
+        assert np.array_equal(ctx.get_visible(poses[v]), orc.eval_view(poses[v])["visible"])
+    ctx.close()
+
+
+def test_config2_full_size_bit_exact(A, oracle_mod):
+    """Config 2: 10k candidate viewpoints vs a synthetic 1M-point structure, single B200, bit-exact
+    visible-set check (hash of every visible index set + counts) against the oracle."""
+    xyz = A.synth_structure(1_000_000)
+    poses = A.synth_views(10_000)
+    ctx = A.CoverageContext(xyz, A.default_params())
+    orc = oracle_mod.Oracle(xyz, oracle_mod.make_params())
+    res = ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    st = orc.eval_batch(poses, memo=True, nthreads=NTHREADS)
+    assert_results_equal(oracle_mod, res, st, "config 2")
+    ctx.close()
+
+
+def test_epsilon_classes_reported(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
+    """North star: points within epsilon of a frustum plane / voxel boundary are counted and reported.
+    They are compared like every other point: the visible lists still match verbatim."""
+    total = np.zeros(5, np.int64)
+    for pose in space_2p5["cam0"][600:660:6]:
+        r = etihad_oracle.eval_view(pose, want_eps=True)
+        total += r["eps"]
+        assert np.array_equal(etihad_ctx.get_visible(pose), r["visible"])
+    print("epsilon classes E1..E5 over 10 views:", total.tolist())
+    assert total[0] > 0  # some points do sit within 1e-4 of a plane
+
+
+def test_sticky_state_carry_path(A, oracle_mod):
+    """Quirk Q5 (occlusion_culling.cpp:308,332-335): same scene as tests/test_oracle.py; the GPU hands
+    such views to ordered_views_kernel, which replays the reference loop in original index order."""
+    pa = A.default_params(leaf=4.0, far_dist=60.0, cov_leaf=4.0)
+    po = oracle_mod.make_params(leaf=4.0, far=60.0, cov_leaf=4.0)
+    pose = np.array([1, 2, 2, 0, 0, 0, 1.0])
+    pts = {"A": (42, 6, 2), "B": (14, 2, 2), "C": (2.5, 2, 2), "E": (14, 3, 6)}
+    for order in ("ABCE", "BCAE", "EABC", "CEBA"):
+        xyz = np.array([pts[ch] for ch in order], np.float32)
+        ctx = A.CoverageContext(xyz, pa)
+        orc = oracle_mod.Oracle(xyz, po)
+        res = ctx.eval_batch(np.stack([pose, pose]), flags=A.EVAL_HASH)
+        st = orc.eval_batch(np.stack([pose, pose]), memo=False)
+        cols = [(n, c) for n, c in [("survivors", 0), ("visible", 1), ("carry", 2), ("unique_rays", 3), ("cells", 4),
+                                    ("gain_pts", 6), ("gain_vox", 7), ("vis_hash", 8), ("surv_hash", 9)]]
+        for name, col in cols:
+            assert np.array_equal(res[name].astype(np.uint64), st[:, col].astype(np.uint64)), (order, name)
+        assert (res["status"] & A.VS_ORDERED != 0).all() and (res["carry"] == 2).all()
+        assert np.array_equal(ctx.get_visible(pose), orc.eval_view(pose)["visible"])
+        ctx.close()
+
+
+def test_carry_inside_large_batch(A, oracle_mod, etihad):
+    """A carry view mixed into a normal batch: only that view takes the ordered path."""
+    rng = np.random.default_rng(5)
+    xyz = np.concatenate([np.array([(42, 6, 2), (14, 2, 2), (2.5, 2, 2), (14, 3, 6)], np.float32),
+                          (rng.random((5000, 3)) * np.array([60, 30, 12]) + np.array([0, -40, 0])).astype(np.float32)])
+    pa = A.default_params(leaf=4.0, far_dist=60.0, cov_leaf=2.0)
+    po = oracle_mod.make_params(leaf=4.0, far=60.0, cov_leaf=2.0)
+    poses = np.array([[1, 2, 2, 0, 0, 0, 1.0], [1, -20, 2, 0, 0, 0, 1.0], [5, -30, 6, 0, 0, 0.38268343, 0.92387953],
+                      [1, 2, 2, 0, 0, 0, 1.0]])
+    ctx = A.CoverageContext(xyz, pa)
+    orc = oracle_mod.Oracle(xyz, po)
+    res = ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    st = orc.eval_batch(poses, memo=False)
+    for name, col in [("survivors", 0), ("visible", 1), ("carry", 2), ("gain_pts", 6), ("gain_vox", 7), ("vis_hash", 8)]:
+        assert np.array_equal(res[name].astype(np.uint64), st[:, col].astype(np.uint64)), name
+    assert res["carry"][0] > 0 and res["carry"][3] > 0
+    ctx.close()
+
+
+def test_covered_sets_and_gain(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
+    """Gain = popcount of newly visible points / coverage voxels against a running covered set
+    (coverage_path_planning_heuristic.cpp:473-483 in bitset form), union with the >5 rule (:344-346)."""
+    o = etihad_oracle
+    poses = np.concatenate([space_2p5["cam0"][560:700], space_2p5["cam1"][560:700]])
+    cp = np.zeros(o.pts_words(), np.uint64)
+    cv = np.zeros(o.vox_words(), np.uint64)
+    o.accumulate(poses[:100], cp, cv, min_visible=5, nthreads=NTHREADS)
+    s = etihad_ctx.new_set()
+    s.or_views(poses[:100], min_visible=5)
+    gp, gv = s.export()
+    assert np.array_equal(gp, cp) and np.array_equal(gv, cv)
+    assert s.popcount() == (int(np.unpackbits(cp.view(np.uint8)).sum()), int(np.unpackbits(cv.view(np.uint8)).sum()))
+    assert np.float32(s.coverage_percent()) == np.float32(o.coverage_percent_vox(cv))
+    res = etihad_ctx.eval_batch(poses, covered=s, flags=A.EVAL_HASH)
+    st = o.eval_batch(poses, memo=True, nthreads=NTHREADS, covered_pts=cp, covered_vox=cv)
+    assert_results_equal(oracle_mod, res, st, "gain vs covered set")
+    # import/export round trip, clone, or_set, or_points
+    t = etihad_ctx.new_set()
+    t.load(cp, cv)
+    assert all(np.array_equal(a, b) for a, b in zip(t.export(), (cp, cv)))
+    u = s.clone()
+    u.or_set(t)
+    assert all(np.array_equal(a, b) for a, b in zip(u.export(), (cp, cv)))
+    w = etihad_ctx.new_set()
+    vis = o.eval_view(poses[120])["visible"]
+    w.or_points(vis)
+    wp, wv = w.export()
+    assert int(np.unpackbits(wp.view(np.uint8)).sum()) == len(vis)
+    assert np.float32(w.coverage_percent()) == np.float32(o.coverage_percent_idx(vis))
+    for x in (s, t, u, w):
+        x.free()
+
+
+def test_coverage_percent_of_arbitrary_cloud(A, etihad_ctx, etihad_oracle, etihad, space_2p5):
+    """calcCoveragePercent(cloud) voxelises any cloud, e.g. VoxelGrid centroids (heuristic.cpp:476-482)."""
+    xyz = etihad[0]
+    vis = etihad_oracle.eval_view(space_2p5["cam0"][610])["visible"]
+    pct = etihad_ctx.coverage_percent_cloud(xyz[vis])
+    assert np.float32(pct) == np.float32(etihad_oracle.coverage_percent_idx(vis))
+    # points outside the model grid match nothing
+    assert etihad_ctx.coverage_percent_cloud(np.array([[1e3, 1e3, 1e3]], np.float32)) == 0.0
+    assert etihad_ctx.coverage_percent_cloud(np.zeros((0, 3), np.float32)) == 0.0
+    assert np.float32(etihad_ctx.coverage_percent_cloud(xyz)) == np.float32(100.0)
+
+
+def test_edge_cases(A, oracle_mod):
+    """Empty model, single point, zero views, blind views, degenerate quaternion."""
+    ctx = A.CoverageContext(np.zeros((0, 3), np.float32), A.default_params())
+    res = ctx.eval_batch(np.array([[0, 0, 0, 0, 0, 0, 1.0]]))
+    assert res["survivors"][0] == 0 and res["visible"][0] == 0
+    assert len(ctx.eval_batch(np.zeros((0, 7)))) == 0
+    ctx.close()
+    one = np.array([[3.1, 0.2, 0.1]], np.float32)
+    ctx = A.CoverageContext(one, A.default_params())
+    orc = oracle_mod.Oracle(one)
+    poses = np.array([[0, 0, 0, 0, 0, 0, 1.0], [0, 0, 0, 0, 0, 1.0, 0.0], [0, 0, 0, 0, 0, 0, 0.0],
+                      [100, 100, 100, 0, 0, 0, 1.0]])
+    res = ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    st = orc.eval_batch(poses, memo=True)
+    assert_results_equal(oracle_mod, res, st, "single point")
+    assert list(res["visible"]) == [1, 0, 0, 0]
+    ctx.close()
+    with pytest.raises(A.AsscppError):
+        A.CoverageContext(np.array([[np.nan, 0, 0]], np.float32), A.default_params())
+    with pytest.raises(A.AsscppError):  # <PCL> "Leaf size is too small"
+        A.CoverageContext(np.array([[0, 0, 0], [4000, 4000, 4000]], np.float32), A.default_params(leaf=0.001))
+
+
+def test_idempotent_and_order_independent(A, etihad_ctx, space_2p5):
+    """Size-independent properties: re-evaluation is bit-identical; a batch is a set of independent views."""
+    poses = np.concatenate([space_2p5["cam0"][400:900], space_2p5["cam1"][400:900]])
+    a = etihad_ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    b = etihad_ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    assert a.tobytes() == b.tobytes()
+    perm = np.random.default_rng(1).permutation(len(poses))
+    c = etihad_ctx.eval_batch(poses[perm], flags=A.EVAL_HASH)
+    assert c.tobytes() == a[perm].tobytes()
+
+
+def test_full_size_properties_10m(A):
+    """BASELINE config 3 size on one GPU (10M points, 0.05 m): properties that need no oracle --
+    bucketed cull == brute-force cull, shared-memory grid == global grid, union popcount consistency."""
+    xyz = A.synth_structure(10_000_000)
+    poses = A.synth_views(100_000)[37::400]
+    ctx = A.CoverageContext(xyz, A.default_params(leaf=0.05))
+    a = ctx.eval_batch(poses, flags=A.EVAL_HASH)
+    b = ctx.eval_batch(poses, flags=A.EVAL_HASH | A.EVAL_BRUTE)
+    c = ctx.eval_batch(poses, flags=A.EVAL_HASH | A.EVAL_FORCE_GLOBAL)
+    drop = ["status"]
+    names = [n for n in a.dtype.names if n not in drop]
+    for n in names:
+        assert np.array_equal(a[n], b[n]), n
+        assert np.array_equal(a[n], c[n]), n
+    assert a["visible"].sum() > 0 and (a["visible"] <= a["survivors"]).all() and (a["gain_pts"] == a["visible"]).all()
+    s = ctx.new_set()
+    s.or_views(poses, min_visible=-1)
+    npts, nvox = s.popcount()
+    assert 0 < npts <= int(a["visible"].sum()) and npts >= int(a["visible"].max())
+    again = ctx.eval_batch(poses, covered=s)
+    assert (again["gain_pts"] == 0).all() and (again["gain_vox"] == 0).all()
+    ctx.close()
