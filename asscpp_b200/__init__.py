@@ -233,6 +233,12 @@ class CoverageContext:
         self._ck(self.L.asscpp_eval_kernel_ms(self.h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def phase_cycles(self, enable=True):
+        """Read + reset the per-phase SM-cycle counters (cull, grid, DDA, visit, views, CTA lifetime)."""
+        out = np.zeros(8, np.uint64)
+        self._ck(self.L.asscpp_debug_phase_cycles(self.h, int(enable), _ptr(out, C.c_uint64)))
+        return out
+
     def launch_count(self):
         return self.L.asscpp_launch_count(self.h)
 

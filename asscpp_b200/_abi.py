@@ -69,6 +69,7 @@ SYMBOLS = [
     "asscpp_covered_or_points", "asscpp_covered_popcount", "asscpp_covered_export", "asscpp_covered_import",
     "asscpp_coverage_percent", "asscpp_coverage_percent_cloud", "asscpp_sync", "asscpp_get_stream",
     "asscpp_timer_begin", "asscpp_timer_end", "asscpp_launch_count", "asscpp_eval_kernel_ms",
+    "asscpp_debug_phase_cycles",
     "asscpp_comm_unique_id", "asscpp_comm_init", "asscpp_allgather_results", "asscpp_allreduce_or",
     "asscpp_comm_destroy", "asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor",
     "asscpp_frustum_planes",
@@ -123,6 +124,7 @@ def load():
         "asscpp_timer_end": (i32, [vp, f32p]),
         "asscpp_launch_count": (i64, [vp]),
         "asscpp_eval_kernel_ms": (i32, [vp, f32p, i64p]),
+        "asscpp_debug_phase_cycles": (i32, [vp, i32, u64p]),
         "asscpp_comm_unique_id": (i32, [u8p]),
         "asscpp_comm_init": (i32, [vp, i32, i32, u8p]),
         "asscpp_allgather_results": (i32, [vp, i64, vp]),

@@ -77,10 +77,12 @@ struct AsscppCtx {
   uint32_t smem_grid_words = 0;
   int64_t chunk_cap = 0, list_cap = 0, grid_cap_words = 0, cov_words = 0;
   uint2* d_chunk_list = nullptr;
-  uint32_t *d_vox_list = nullptr, *d_grid_scratch = nullptr, *d_cov_scratch = nullptr;
+  uint32_t *d_vox_list = nullptr, *d_vis_list = nullptr, *d_grid_scratch = nullptr, *d_cov_scratch = nullptr;
+  int64_t vis_cap = 0;
   uint8_t* d_vstate = nullptr;
   int32_t* d_counters = nullptr;  // [0] work counter, [1] ordered count
   unsigned long long* d_pop = nullptr;  // 2 popcount cells
+  unsigned long long* d_phase = nullptr;  // per-phase cycle counters, allocated by asscpp_debug_phase_cycles
   // per-batch buffers (grown on demand)
   int64_t view_cap = 0;
   double* d_poses = nullptr;
@@ -215,12 +217,14 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.flags = flags;
   a.chunk_list = c->d_chunk_list; a.chunk_cap = c->chunk_cap;
   a.vox_list = c->d_vox_list; a.list_cap = c->list_cap;
+  a.vis_list = c->d_vis_list; a.vis_cap = c->vis_cap;
   a.grid_scratch = c->d_grid_scratch; a.grid_cap_words = c->grid_cap_words;
   a.cov_scratch = c->d_cov_scratch; a.cov_words = c->cov_words;
   a.vstate = c->d_vstate;
   a.ordered_list = c->d_ordered_list;
   a.ordered_count = c->d_counters + 1;
   a.smem_grid_words = c->smem_grid_words;
+  a.phase_cycles = c->d_phase;
   int ctas = (int)std::min<int64_t>(c->ctas, nviews);
   std::pair<cudaEvent_t, cudaEvent_t>* evp = nullptr;
   if (c->timing) {
@@ -354,7 +358,7 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   double cells_cap = 1;
   for (int k = 0; k < 3; ++k) {
     double model_div = (double)h.max_b[k] - h.min_b[k] + 1;
-    double a = std::min(model_div, std::floor(ext * (double)h.inv_leaf) + 4.0);
+    double a = std::min(model_div, std::floor(ext * (double)h.inv_leaf) + 4.0) + 4.0;  // + halo and sentinel layers
     cells_cap *= std::max(a, 1.0);
   }
   if (cells_cap > 2147483647.0) cells_cap = 2147483647.0;
@@ -364,6 +368,8 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   c->cov_words = c->vox_words;
   if ((rc = dev_alloc(c, &c->d_chunk_list, c->chunk_cap * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_vox_list, c->list_cap * c->ctas))) return fail(rc);
+  c->vis_cap = m.n_vox + 32;
+  if ((rc = dev_alloc(c, &c->d_vis_list, c->vis_cap * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_grid_scratch, c->grid_cap_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_cov_scratch, c->cov_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_vstate, std::max<int64_t>(m.n_vox, 1) * c->ordered_ctas))) return fail(rc);
@@ -689,6 +695,20 @@ int asscpp_timer_end(AsscppCtx* c, float* ms) {
 }
 
 int64_t asscpp_launch_count(const AsscppCtx* c) { return c ? c->launches : 0; }
+
+int asscpp_debug_phase_cycles(AsscppCtx* c, int enable, uint64_t out[8]) {
+  if (!c) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (c->d_phase && out) CU(c, cudaMemcpy(out, c->d_phase, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  if (enable && !c->d_phase) {
+    int rc = dev_alloc(c, &c->d_phase, 8);
+    if (rc) return rc;
+  }
+  if (c->d_phase) CU(c, cudaMemset(c->d_phase, 0, 8 * sizeof(uint64_t)));
+  if (!enable) c->d_phase = nullptr;  // buffer stays in c->allocs and is released with the context
+  return ASSCPP_OK;
+}
 
 int asscpp_eval_kernel_ms(AsscppCtx* c, float* ms, int64_t* launches) {
   if (!c) return ASSCPP_EINVAL;

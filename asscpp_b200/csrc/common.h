@@ -65,8 +65,10 @@ struct EvalArgs {
   // per-CTA scratch (global memory, L2-resident in steady state)
   uint2* chunk_list;         // [ctas][chunk_cap] candidate chunks {first point, end point}
   int64_t chunk_cap;
-  uint32_t* vox_list;        // [ctas][list_cap] voxels occupied for the view (bit 31: visible)
+  uint32_t* vox_list;        // [ctas][list_cap] voxels occupied for the view (0xffffffff: duplicate)
   int64_t list_cap;
+  uint32_t* vis_list;        // [ctas][vis_cap] voxels found visible for the view
+  int64_t vis_cap;
   uint32_t* grid_scratch;    // [ctas][grid_cap_words] bit-grid when it does not fit shared memory
   int64_t grid_cap_words;
   uint32_t* cov_scratch;     // [ctas][cov_words] per-view coverage-voxel marks
@@ -75,6 +77,7 @@ struct EvalArgs {
   int32_t* ordered_list;     // views that saw a Q5 carry
   int32_t* ordered_count;
   uint32_t smem_grid_words;  // capacity of the shared-memory grid
+  unsigned long long* phase_cycles;  // optional profiling counters (nullptr: off)
 };
 
 constexpr uint32_t kVsError = 0x80000000u;  // internal consistency failure (scratch overflow)

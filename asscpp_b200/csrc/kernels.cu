@@ -135,9 +135,26 @@ struct GridView {  // geometry of the per-view grid (voxel_grid_occlusion_estima
   float base[3];  // b_min + leaf/2  (voxel_grid_occlusion_estimation.h:151-153)
   float b_min[3], b_max[3];
   int min_b[3], div[3];
-  int mul1, mul2;
-  unsigned cells;
+  int mul1, mul2;     // PCL strides: div0, div0*div1 (linear index of quirk Q3)
+  unsigned cells;     // div0*div1*div2
+  int P0, P1, P2, P01;  // padded walk grid: P = div + 4 (one halo layer + one sentinel layer per side)
 };
+
+// Where the per-view bit-grid lives: shared memory (32-bit shared address) or the per-CTA global scratch.
+struct GridMem {
+  uint32_t* gptr;
+  uint32_t saddr;
+};
+template <bool SMEM>
+__device__ __forceinline__ uint32_t grid_load(const GridMem& gm, unsigned w) {
+  if constexpr (SMEM) {
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(gm.saddr + (w << 2)));
+    return v;
+  } else {
+    return gm.gptr[w];
+  }
+}
 
 struct ViewShared {
   float planes[24];
@@ -147,7 +164,7 @@ struct ViewShared {
   int bb_min[3], bb_max[3];
   int view;
   int use_smem;
-  unsigned chunk_count, list_count;
+  unsigned chunk_count, list_count, vis_count;
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
   int seg_last[1024];  // ordered path only
@@ -187,7 +204,17 @@ __device__ __forceinline__ void direction(const float ctr[3], const float o[3], 
 // voxel at relative coordinates rt (= ijk - min_b) with cell centre tc.  Returns 0 free, 1 occluded,
 // 2 failed (tmin == -1: the caller's `state` stays untouched, quirk Q5).  The walk stops at the first
 // qualifying occluder: the reference keeps walking but its result can only stay 1 (:561-562).
-__device__ __forceinline__ int occlusion_estimation(const GridView& g, const uint32_t* grid, const float origin[3],
+//
+// The walk runs on a PADDED copy of the grid (coordinate q = r + 2, P = div + 4 cells per axis) so the
+// hot loop needs one integer per ray: the padded linear index p.
+//   * interior cells (0 <= r < div) hold the occupancy bit,
+//   * the halo layer (r == -1 or r == div) is where the reference still walks (:538-540) and where
+//     PCL's unchecked linear index aliases into another row/slice (quirk Q3); its bits are set so the
+//     rare visit drops into the slow path, which evaluates the aliased lookup exactly,
+//   * the sentinel layer (r == -2 or r == div + 1) is set as well: arriving there is the loop exit.
+// Target test = one compare (p is unique per cell), bounds test = none in the hot loop.
+template <bool SMEM>
+__device__ __forceinline__ int occlusion_estimation(const GridView& g, const GridMem& gm, const float origin[3],
                                                     const int rt[3], const float tc[3], unsigned& steps) {
   float d[3];
   direction(tc, origin, d);                 // :111-113
@@ -206,28 +233,53 @@ __device__ __forceinline__ int occlusion_estimation(const GridView& g, const uin
     t_max[c] = fadd(tmin, fdiv(fsub(vm, start), d[c]));                // :513-515
     t_delta[c] = fdiv(g.leaf, fabsf(d[c]));                            // :517-519
   }
-  const int istep1 = step[1] * g.mul1, istep2 = step[2] * g.mul2;
-  int idx = r[0] + r[1] * g.mul1 + r[2] * g.mul2;  // <PCL getCentroidIndexAt> dense linearisation (Q3)
+  // loop entry condition :538-540: ijk <= max_b + 1 && ijk + 1 >= min_b  <=>  -1 <= r <= div
+  if (!((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
+        (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1)))
+    return 0;
+  const int P0 = g.P0, P01 = g.P01;
+  const int k0 = step[0], k1 = step[1] * P0, k2 = step[2] * P01;
+  const int pt = (rt[0] + 2) + (rt[1] + 2) * P0 + (rt[2] + 2) * P01;
+  int p = (r[0] + 2) + (r[1] + 2) * P0 + (r[2] + 2) * P01;
+  float tx = t_max[0], ty = t_max[1], tz = t_max[2];
+  const float dtx = t_delta[0], dty = t_delta[1], dtz = t_delta[2];
   int result = 0;
   unsigned n = 0;
-  // loop bounds :538-540: ijk <= max_b + 1 && ijk + 1 >= min_b  <=>  -1 <= r <= div
-  while ((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
-         (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1)) {
+  for (;;) {
     ++n;
-    if (r[0] == rt[0] && r[1] == rt[1] && r[2] == rt[2]) break;        // :551-552
-    if ((unsigned)idx < g.cells && ((grid[idx >> 5] >> (idx & 31)) & 1u)) {  // :555-556 (only the linear range is checked)
-      float dx = fsub(centre(g, 0, r[0]), tc[0]), dy = fsub(centre(g, 1, r[1]), tc[1]),
-            dz = fsub(centre(g, 2, r[2]), tc[2]);
-      float sum = fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz)); // :560
-      if (sum > g.thr_sq) { result = 1; break; }                        // :561 sqrt(double(sum)) > leaf*2
+    if (p == pt) break;                                                 // :551-552
+    const uint32_t word = grid_load<SMEM>(gm, (unsigned)p >> 5);
+    if ((word >> (p & 31)) & 1u) {
+      // rare: occupied interior cell, halo cell or sentinel
+      const int q2 = p / P01, rem = p - q2 * P01, q1 = rem / P0, q0 = rem - q1 * P0;
+      if (q0 == 0 || q0 == P0 - 1 || q1 == 0 || q1 == g.P1 - 1 || q2 == 0 || q2 == g.P2 - 1) { --n; break; }
+      const int c0 = q0 - 2, c1 = q1 - 2, c2 = q2 - 2;
+      bool occ = true;
+      if (c0 < 0 || c0 == g.div[0] || c1 < 0 || c1 == g.div[1] || c2 < 0 || c2 == g.div[2]) {
+        // <PCL getCentroidIndexAt>: idx = (ijk - min_b) . (1, div0, div0*div1), only 0 <= idx < size checked
+        const int lin = c0 + c1 * g.mul1 + c2 * g.mul2;
+        occ = false;
+        if ((unsigned)lin < g.cells) {
+          const int a2 = lin / g.mul2, ar = lin - a2 * g.mul2, a1 = ar / g.mul1, a0 = ar - a1 * g.mul1;
+          const int pa = (a0 + 2) + (a1 + 2) * P0 + (a2 + 2) * P01;
+          occ = (grid_load<SMEM>(gm, (unsigned)pa >> 5) >> (pa & 31)) & 1u;
+        }
+      }
+      if (occ) {                                                        // :555-556
+        float dx = fsub(centre(g, 0, c0), tc[0]), dy = fsub(centre(g, 1, c1), tc[1]),
+              dz = fsub(centre(g, 2, c2), tc[2]);
+        float sum = fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz)); // :560
+        if (sum > g.thr_sq) { result = 1; break; }                        // :561 sqrt(double(sum)) > leaf*2
+      }
     }
-    if (t_max[0] <= t_max[1] && t_max[0] <= t_max[2]) {                 // :565-569
-      t_max[0] = fadd(t_max[0], t_delta[0]); r[0] += step[0]; idx += step[0];
-    } else if (t_max[1] <= t_max[2] && t_max[1] <= t_max[0]) {          // :570-574
-      t_max[1] = fadd(t_max[1], t_delta[1]); r[1] += step[1]; idx += istep1;
-    } else {                                                            // :575-579
-      t_max[2] = fadd(t_max[2], t_delta[2]); r[2] += step[2]; idx += istep2;
-    }
+    // :565-579, ties x -> y -> z by <=; NaN compares false and falls through to z
+    const bool sx = (tx <= ty) & (tx <= tz);
+    const bool sy = (!sx) & (ty <= tz) & (ty <= tx);
+    const bool sz = !(sx | sy);
+    tx = sx ? fadd(tx, dtx) : tx;
+    ty = sy ? fadd(ty, dty) : ty;
+    tz = sz ? fadd(tz, dtz) : tz;
+    p += sx ? k0 : (sy ? k1 : k2);
   }
   steps += n;
   return result;
@@ -341,16 +393,28 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
 }
 
 // ------------------------------------------------------------------------------------------------
-// P3: grid geometry from the survivors' box, zero + fill the bit-grid, drop duplicate list entries.
-// Returns the grid pointer (shared or global).  Must be called by all threads.
+// P3: grid geometry from the survivors' box, zero + fill the padded bit-grid, drop duplicate list
+// entries.  Returns where the grid lives (shared or global).  Must be called by all threads.
 // ------------------------------------------------------------------------------------------------
-__device__ uint32_t* build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_grid, uint32_t* glob_grid,
-                                uint32_t* vox_list) {
+template <class F>
+__device__ __forceinline__ void or_bit_range(F&& or_word, unsigned lo, unsigned hi) {  // bits [lo, hi)
+  if (hi <= lo) return;
+  unsigned w0 = lo >> 5, w1 = (hi - 1) >> 5;
+  for (unsigned w = w0; w <= w1; ++w) {
+    uint32_t mask = 0xffffffffu;
+    if (w == w0) mask &= 0xffffffffu << (lo & 31);
+    if (w == w1) mask &= 0xffffffffu >> (31 - ((hi - 1) & 31));
+    or_word(w, mask);
+  }
+}
+
+__device__ bool build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_grid, uint32_t* glob_grid,
+                           uint32_t* vox_list, GridMem* gm_out) {
   const ModelDev& m = A.m;
   if (threadIdx.x == 0) {
     GridView& g = sh.g;
     g.leaf = m.leaf; g.inv = m.inv_leaf; g.half = m.half_leaf; g.thr_sq = m.dist_thr_sq;
-    unsigned long long cells = 1;
+    unsigned long long cells = 1, pcells = 1;
     for (int c = 0; c < 3; ++c) {
       // <PCL applyFilter>: min_b = floor(min_p * inv), max_b likewise; floor(x*inv) is monotone in x, so the
       // box of the survivors' voxel coordinates is the same box.
@@ -360,40 +424,69 @@ __device__ uint32_t* build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* sme
       g.b_max[c] = fmul((float)(sh.bb_max[c] + 1), m.leaf);  // :56-58
       g.base[c] = fadd(g.b_min[c], m.half_leaf);
       cells *= (unsigned long long)g.div[c];
+      pcells *= (unsigned long long)(g.div[c] + 4);
     }
     g.mul1 = g.div[0];
     g.mul2 = g.div[0] * g.div[1];
     g.cells = (unsigned)cells;
-    unsigned long long words = (cells + 31) / 32;
+    g.P0 = g.div[0] + 4; g.P1 = g.div[1] + 4; g.P2 = g.div[2] + 4; g.P01 = g.P0 * g.P1;
+    unsigned long long words = (pcells + 31) / 32;
     sh.words = (unsigned)words;
     bool fits_smem = words <= A.smem_grid_words && !(A.flags & ASSCPP_EVAL_FORCE_GLOBAL);
     sh.use_smem = fits_smem ? 1 : 0;
     sh.status |= fits_smem ? ASSCPP_VS_GRID_SHARED : ASSCPP_VS_GRID_GLOBAL;
-    if ((!fits_smem && words > (unsigned long long)A.grid_cap_words) || sh.list_count > A.list_cap) {
+    if ((!fits_smem && words > (unsigned long long)A.grid_cap_words) || sh.list_count > A.list_cap ||
+        pcells > 0x7fffffffULL) {
       sh.status |= kVsError;  // scratch bound violated: report, do not touch memory out of range
       sh.words = 0;
       sh.list_count = 0;
     }
   }
   __syncthreads();
-  uint32_t* grid = sh.use_smem ? smem_grid : glob_grid;
+  const bool use_smem = sh.use_smem != 0;
+  uint32_t* grid = use_smem ? smem_grid : glob_grid;
+  gm_out->gptr = grid;
+  gm_out->saddr = (uint32_t)__cvta_generic_to_shared(smem_grid);
   for (unsigned w = threadIdx.x; w < sh.words; w += blockDim.x) grid[w] = 0;
   __syncthreads();
+  if (sh.words == 0) return use_smem;
   const GridView& g = sh.g;
+  const int P0 = g.P0, P1 = g.P1, P2 = g.P2, P01 = g.P01;
+  // interior: occupancy of the survivors' voxels
   unsigned uniq = 0;
   for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
     uint32_t u = vox_list[e];
     int4 vx = m.vox[u];
-    int idx = (vx.x - g.min_b[0]) + (vx.y - g.min_b[1]) * g.mul1 + (vx.z - g.min_b[2]) * g.mul2;
-    uint32_t bit = 1u << (idx & 31);
-    uint32_t old = atomicOr(&grid[idx >> 5], bit);
+    int p = (vx.x - g.min_b[0] + 2) + (vx.y - g.min_b[1] + 2) * P0 + (vx.z - g.min_b[2] + 2) * P01;
+    uint32_t bit = 1u << (p & 31);
+    uint32_t old = atomicOr(&grid[p >> 5], bit);
     if (old & bit) vox_list[e] = 0xffffffffu;  // same voxel emitted by another 32-point load
     else ++uniq;
+  }
+  // halo + sentinel layers: every cell with a padded coordinate in {0, 1, P-2, P-1}
+  auto orw = [&](unsigned w, uint32_t mask) { atomicOr(&grid[w], mask); };
+  {  // the two bottom and two top z-slabs, word-parallel
+    const unsigned slab = 2u * (unsigned)P01, top = (unsigned)(P2 - 2) * (unsigned)P01, end = (unsigned)P2 * (unsigned)P01;
+    for (unsigned w = threadIdx.x; w <= ((slab - 1) >> 5); w += blockDim.x)
+      or_bit_range(orw, max(w << 5, 0u), min((w + 1) << 5, slab));
+    for (unsigned w = (top >> 5) + threadIdx.x; w <= ((end - 1) >> 5); w += blockDim.x)
+      or_bit_range(orw, max(w << 5, top), min((w + 1) << 5, end));
+  }
+  const int rows = P1 * (P2 - 4);
+  for (int t = threadIdx.x; t < rows; t += blockDim.x) {
+    const int q2 = 2 + t / P1, q1 = t - (q2 - 2) * P1;
+    const unsigned base = (unsigned)q2 * (unsigned)P01 + (unsigned)q1 * (unsigned)P0;
+    if (q1 < 2 || q1 >= P1 - 2) {
+      or_bit_range(orw, base, base + (unsigned)P0);
+    } else {
+      or_bit_range(orw, base, base + 2u);
+      or_bit_range(orw, base + (unsigned)P0 - 2u, base + (unsigned)P0);
+    }
   }
   uniq = warp_sum(uniq);
   if ((threadIdx.x & 31) == 0 && uniq) atomicAdd(&sh.unique, uniq);
   __syncthreads();
-  return grid;
+  return use_smem;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -438,6 +531,57 @@ __device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const View
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// P4a: one DDA ray per voxel occupied for this view (quirk Q1: every survivor of a voxel shares the
+// ray to its cell centre).  Fast path (vstate == nullptr): visible voxels (state != 1 and second gate)
+// are appended to vis_list, failed rays (quirk Q5) are counted in sh.carry.  Ordered path: the state
+// of every voxel is stored in vstate for the replay in original index order.
+// ------------------------------------------------------------------------------------------------
+template <bool SMEM>
+__device__ __forceinline__ void trace_rays(const EvalArgs& A, ViewShared& sh, const GridMem& gm,
+                                           const uint32_t* vox_list, uint32_t* vis_list, uint8_t* vstate = nullptr) {
+  const ModelDev& m = A.m;
+  const GridView g = sh.g;
+  const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
+  const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
+  const int lane = threadIdx.x & 31;
+  unsigned steps = 0, fails = 0;
+  const unsigned count = sh.list_count;
+  for (unsigned e0 = (threadIdx.x & ~31u); e0 < count; e0 += blockDim.x) {
+    const unsigned e = e0 + lane;
+    uint32_t u = e < count ? vox_list[e] : 0xffffffffu;
+    bool visible = false;
+    if (u != 0xffffffffu) {
+      int4 vx = m.vox[u];
+      int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
+      float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
+      int state = occlusion_estimation<SMEM>(g, gm, origin, rt, tc, steps);
+      if (vstate) {
+        vstate[u] = (uint8_t)(state | (second_gate(g, pcd_o, tc) ? 4 : 0));
+      } else {
+        if (state == 2) ++fails;
+        visible = (state == 0) && second_gate(g, pcd_o, tc);  // occlusion_culling.cpp:335-342
+      }
+    }
+    if (!vstate) {
+      unsigned vb = __ballot_sync(0xffffffffu, visible);
+      if (vb) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(&sh.vis_count, (unsigned)__popc(vb));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (visible) vis_list[base + __popc(vb & ((1u << lane) - 1))] = u;
+      }
+    }
+  }
+  fails = warp_sum(fails);
+  unsigned long long st64 = steps;
+  for (int o = 16; o; o >>= 1) st64 += __shfl_xor_sync(0xffffffffu, st64, o);
+  if (lane == 0) {
+    if (fails) atomicAdd(&sh.carry, fails);
+    if (st64) atomicAdd(&sh.steps, st64);
+  }
+}
+
 __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   if (threadIdx.x < 24) sh.planes[threadIdx.x] = vd.planes[threadIdx.x];
   if (threadIdx.x < 3) {
@@ -447,7 +591,7 @@ __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   }
   if (threadIdx.x == 0) {
     sh.view = v;
-    sh.chunk_count = 0; sh.list_count = 0;
+    sh.chunk_count = 0; sh.list_count = 0; sh.vis_count = 0;
     sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
     sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
     sh.words = 0; sh.use_smem = 1;
@@ -477,53 +621,50 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
   uint32_t* vox_list = A.vox_list + (int64_t)blockIdx.x * A.list_cap;
   uint32_t* glob_grid = A.grid_scratch + (int64_t)blockIdx.x * A.grid_cap_words;
   uint32_t* cov_scratch = A.cov_scratch + (int64_t)blockIdx.x * A.cov_words;
+  uint32_t* vis_list = A.vis_list + (int64_t)blockIdx.x * A.vis_cap;
   __shared__ int s_view;
+  const long long k_start = clock64();
   for (;;) {
     __syncthreads();
     if (threadIdx.x == 0) s_view = atomicAdd(A.work_counter, 1);
     __syncthreads();
     const int v = s_view;
     if (v >= A.nviews) break;
+    long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    const bool prof = A.phase_cycles != nullptr && threadIdx.x == 0;
+    if (prof) t0 = clock64();
     reset_view(sh, A.views[v], v);
     __syncthreads();
     cull_view(A, sh, chunk_list, vox_list);
+    if (prof) t1 = clock64();
     if (sh.survivors == 0) {  // empty frustum cloud: extractVisibleSurface returns an empty cloud
       if (threadIdx.x == 0) write_result(A, sh, v);
+      if (prof) atomicAdd(&A.phase_cycles[0], (unsigned long long)(t1 - t0));
       continue;
     }
-    uint32_t* grid = build_grid(A, sh, smem_grid, glob_grid, vox_list);
-    // P4: one ray per occupied voxel
-    const GridView g = sh.g;
-    const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
-    const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
-    unsigned vis = 0, gain_p = 0, gain_v = 0, steps = 0, fails = 0;
-    unsigned long long vhash = 0;
-    for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
-      uint32_t u = vox_list[e];
-      if (u == 0xffffffffu) continue;
-      int4 vx = m.vox[u];
-      int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
-      float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
-      int state = occlusion_estimation(g, grid, origin, rt, tc, steps);
-      if (state == 2) { ++fails; continue; }
-      if (state != 1 && second_gate(g, pcd_o, tc)) {
-        vox_list[e] = u | 0x80000000u;
-        visit_voxel_points(A, sh, u, 0, cov_scratch, vis, gain_p, gain_v, vhash);
+    GridMem gm;
+    const bool in_smem = build_grid(A, sh, smem_grid, glob_grid, vox_list, &gm);
+    if (prof) t2 = clock64();
+    // P4a: one ray per occupied voxel; visible voxels are compacted into vis_list
+    if (in_smem) trace_rays<true>(A, sh, gm, vox_list, vis_list);
+    else trace_rays<false>(A, sh, gm, vox_list, vis_list);
+    __syncthreads();
+    if (prof) t3 = clock64();
+    // P4b: survivors of the visible voxels -> counts, gains, hash
+    {
+      unsigned vis = 0, gain_p = 0, gain_v = 0;
+      unsigned long long vhash = 0;
+      const unsigned nvis = sh.vis_count;
+      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x)
+        visit_voxel_points(A, sh, vis_list[e], 0, cov_scratch, vis, gain_p, gain_v, vhash);
+      vis = warp_sum(vis); gain_p = warp_sum(gain_p); gain_v = warp_sum(gain_v);
+      for (int o = 16; o; o >>= 1) vhash += __shfl_xor_sync(0xffffffffu, vhash, o);
+      if ((threadIdx.x & 31) == 0) {
+        if (vis) atomicAdd(&sh.visible, vis);
+        if (gain_p) atomicAdd(&sh.gain_p, gain_p);
+        if (gain_v) atomicAdd(&sh.gain_v, gain_v);
+        if (vhash) atomicAdd(&sh.vis_hash, vhash);
       }
-    }
-    vis = warp_sum(vis); gain_p = warp_sum(gain_p); gain_v = warp_sum(gain_v); fails = warp_sum(fails);
-    unsigned long long st64 = steps;
-    for (int o = 16; o; o >>= 1) {
-      st64 += __shfl_xor_sync(0xffffffffu, st64, o);
-      vhash += __shfl_xor_sync(0xffffffffu, vhash, o);
-    }
-    if ((threadIdx.x & 31) == 0) {
-      if (vis) atomicAdd(&sh.visible, vis);
-      if (gain_p) atomicAdd(&sh.gain_p, gain_p);
-      if (gain_v) atomicAdd(&sh.gain_v, gain_v);
-      if (fails) atomicAdd(&sh.carry, fails);
-      if (st64) atomicAdd(&sh.steps, st64);
-      if (vhash) atomicAdd(&sh.vis_hash, vhash);
     }
     __syncthreads();
     if (!m.cov_same && sh.visible) {
@@ -544,14 +685,21 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     if (A.accum.pts && (int64_t)sh.visible > A.accum_min_visible) {
       unsigned d0 = 0, d1 = 0, d2 = 0;
       unsigned long long d3 = 0;
-      for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
-        uint32_t u = vox_list[e];
-        if (u == 0xffffffffu || !(u & 0x80000000u)) continue;
-        visit_voxel_points(A, sh, u & 0x7fffffffu, 1, cov_scratch, d0, d1, d2, d3);
-      }
+      const unsigned nvis = sh.vis_count;
+      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x)
+        visit_voxel_points(A, sh, vis_list[e], 1, cov_scratch, d0, d1, d2, d3);
     }
     if (threadIdx.x == 0) write_result(A, sh, v);
+    if (prof) {
+      long long t4 = clock64();
+      atomicAdd(&A.phase_cycles[0], (unsigned long long)(t1 - t0));  // cull (P1 + P2)
+      atomicAdd(&A.phase_cycles[1], (unsigned long long)(t2 - t1));  // grid build (P3)
+      atomicAdd(&A.phase_cycles[2], (unsigned long long)(t3 - t2));  // DDA (P4a)
+      atomicAdd(&A.phase_cycles[3], (unsigned long long)(t4 - t3));  // point visit + OR (P4b, P5)
+      atomicAdd(&A.phase_cycles[4], 1ull);
+    }
   }
+  if (A.phase_cycles != nullptr && threadIdx.x == 0) atomicAdd(&A.phase_cycles[5], (unsigned long long)clock64() - (unsigned long long)k_start);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -576,24 +724,11 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
     reset_view(sh, A.views[v], v);
     __syncthreads();
     cull_view(A, sh, chunk_list, vox_list);
-    uint32_t* grid = build_grid(A, sh, smem_grid, glob_grid, vox_list);
-    const GridView g = sh.g;
-    const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
-    const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
+    GridMem gm;
+    const bool in_smem = build_grid(A, sh, smem_grid, glob_grid, vox_list, &gm);
     // per-voxel state: bits 0-1 = 0 free / 1 occluded / 2 failed, bit 2 = second gate passes
-    unsigned steps = 0;
-    for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
-      uint32_t u = vox_list[e];
-      if (u == 0xffffffffu) continue;
-      int4 vx = m.vox[u];
-      int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
-      float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
-      int state = occlusion_estimation(g, grid, origin, rt, tc, steps);
-      vstate[u] = (uint8_t)(state | (second_gate(g, pcd_o, tc) ? 4 : 0));
-    }
-    unsigned long long st64 = steps;
-    for (int o = 16; o; o >>= 1) st64 += __shfl_xor_sync(0xffffffffu, st64, o);
-    if ((threadIdx.x & 31) == 0 && st64) atomicAdd(&sh.steps, st64);
+    if (in_smem) trace_rays<true>(A, sh, gm, vox_list, nullptr, vstate);
+    else trace_rays<false>(A, sh, gm, vox_list, nullptr, vstate);
     __syncthreads();
     // ordered scan over original indices, one contiguous segment per thread
     const int64_t seg = (m.n + blockDim.x - 1) / blockDim.x;
