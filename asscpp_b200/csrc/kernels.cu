@@ -138,7 +138,14 @@ struct GridView {  // geometry of the per-view grid (voxel_grid_occlusion_estima
   int mul1, mul2;     // PCL strides: div0, div0*div1 (linear index of quirk Q3)
   unsigned cells;     // div0*div1*div2
   int P0, P1, P2, P01;  // padded walk grid: P = div + 4 (one halo layer + one sentinel layer per side)
+  unsigned mP0, mP01, mD0, mD01;  // floor(2^32 / d) for d = P0, P01, div0, div0*div1 (division by multiply-high)
 };
+
+// n / d for n < 2^31 with m = floor(2^32 / d): the multiply-high estimate is at most one too small.
+__device__ __forceinline__ int fast_div(int n, int d, unsigned m) {
+  int q = (int)__umulhi((unsigned)n, m);
+  return q + ((n - q * d) >= d ? 1 : 0);
+}
 
 // Where the per-view bit-grid lives: shared memory (32-bit shared address) or the per-CTA global scratch.
 struct GridMem {
@@ -251,7 +258,7 @@ __device__ __forceinline__ int occlusion_estimation(const GridView& g, const Gri
     const uint32_t word = grid_load<SMEM>(gm, (unsigned)p >> 5);
     if ((word >> (p & 31)) & 1u) {
       // rare: occupied interior cell, halo cell or sentinel
-      const int q2 = p / P01, rem = p - q2 * P01, q1 = rem / P0, q0 = rem - q1 * P0;
+      const int q2 = fast_div(p, P01, g.mP01), rem = p - q2 * P01, q1 = fast_div(rem, P0, g.mP0), q0 = rem - q1 * P0;
       if (q0 == 0 || q0 == P0 - 1 || q1 == 0 || q1 == g.P1 - 1 || q2 == 0 || q2 == g.P2 - 1) { --n; break; }
       const int c0 = q0 - 2, c1 = q1 - 2, c2 = q2 - 2;
       bool occ = true;
@@ -260,7 +267,8 @@ __device__ __forceinline__ int occlusion_estimation(const GridView& g, const Gri
         const int lin = c0 + c1 * g.mul1 + c2 * g.mul2;
         occ = false;
         if ((unsigned)lin < g.cells) {
-          const int a2 = lin / g.mul2, ar = lin - a2 * g.mul2, a1 = ar / g.mul1, a0 = ar - a1 * g.mul1;
+          const int a2 = fast_div(lin, g.mul2, g.mD01), ar = lin - a2 * g.mul2, a1 = fast_div(ar, g.mul1, g.mD0),
+                    a0 = ar - a1 * g.mul1;
           const int pa = (a0 + 2) + (a1 + 2) * P0 + (a2 + 2) * P01;
           occ = (grid_load<SMEM>(gm, (unsigned)pa >> 5) >> (pa & 31)) & 1u;
         }
@@ -430,6 +438,10 @@ __device__ bool build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_gri
     g.mul2 = g.div[0] * g.div[1];
     g.cells = (unsigned)cells;
     g.P0 = g.div[0] + 4; g.P1 = g.div[1] + 4; g.P2 = g.div[2] + 4; g.P01 = g.P0 * g.P1;
+    g.mP0 = (unsigned)(0x100000000ull / (unsigned long long)g.P0);
+    g.mP01 = (unsigned)(0x100000000ull / (unsigned long long)g.P01);
+    g.mD0 = g.mul1 > 1 ? (unsigned)(0x100000000ull / (unsigned long long)g.mul1) : 0xffffffffu;
+    g.mD01 = g.mul2 > 1 ? (unsigned)(0x100000000ull / (unsigned long long)g.mul2) : 0xffffffffu;
     unsigned long long words = (pcells + 31) / 32;
     sh.words = (unsigned)words;
     bool fits_smem = words <= A.smem_grid_words && !(A.flags & ASSCPP_EVAL_FORCE_GLOBAL);
