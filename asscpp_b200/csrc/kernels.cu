@@ -171,7 +171,7 @@ struct ViewShared {
   int bb_min[3], bb_max[3];
   int view;
   int use_smem;
-  unsigned chunk_count, list_count, vis_count;
+  unsigned chunk_count, list_count, vis_count, ray_next;
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
   int seg_last[1024];  // ordered path only
@@ -353,37 +353,48 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
     uint32_t pb, pe;
     if (brute) { pb = __float_as_uint(m.chunk_lo[w].w); pe = __float_as_uint(m.chunk_hi[w].w); }
     else { uint2 r = chunk_list[w]; pb = r.x; pe = r.y; }
-    for (uint32_t base = pb; base < pe; base += 32) {
-      uint32_t pos = base + lane;
-      bool pass = false;
-      uint32_t u = 0xffffffffu;
-      if (pos < pe) {
-        float4 p = m.pts[pos];
-        u = __float_as_uint(p.w);
-        pass = point_in_frustum(sh.planes, p.x, p.y, p.z);
+    for (uint32_t base0 = pb; base0 < pe; base0 += 128) {
+      // four independent 512-byte loads in flight per warp before any is consumed (latency, not bandwidth,
+      // bounds this phase: a chunk holds at most kChunkMaxPoints = 128 points unless it is one big voxel)
+      float4 pt[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint32_t pos = base0 + 32 * k + lane;
+        pt[k] = pos < pe ? m.pts[pos] : make_float4(0.f, 0.f, 0.f, __uint_as_float(0xffffffffu));
       }
-      unsigned pm = __ballot_sync(0xffffffffu, pass);
-      if (!pm) continue;
-      surv += (lane == 0) ? (unsigned)__popc(pm) : 0u;
-      if (want_hash && pass) shash += mix64((uint64_t)(uint32_t)m.orig[pos]);
-      // first passing lane of every run of equal voxel ids emits the voxel
-      uint32_t u_prev = __shfl_up_sync(0xffffffffu, u, 1);
-      bool head = (lane == 0) || (u != u_prev);
-      unsigned hb = __ballot_sync(0xffffffffu, head);
-      unsigned below = hb & ((2u << lane) - 1);          // heads at or below this lane
-      int my_head = 31 - __clz(below);
-      unsigned run_lower = pm & ((1u << lane) - 1) & ~((1u << my_head) - 1);  // passing lanes of my run below me
-      bool emit = pass && (run_lower == 0);
-      unsigned eb = __ballot_sync(0xffffffffu, emit);
-      unsigned slot = 0;
-      if (lane == 0) slot = atomicAdd(&sh.list_count, (unsigned)__popc(eb));
-      slot = __shfl_sync(0xffffffffu, slot, 0);
-      if (emit) {
-        unsigned at = slot + __popc(eb & ((1u << lane) - 1));
-        if (at < A.list_cap) vox_list[at] = u;
-        int4 vx = m.vox[u];
-        bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
-        bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint32_t base = base0 + 32 * k;
+        if (base >= pe) break;
+        const uint32_t pos = base + lane;
+        const float4 p = pt[k];
+        const uint32_t u = __float_as_uint(p.w);
+        const bool pass = pos < pe && point_in_frustum(sh.planes, p.x, p.y, p.z);
+        unsigned pm = __ballot_sync(0xffffffffu, pass);
+        if (!pm) continue;
+        surv += (lane == 0) ? (unsigned)__popc(pm) : 0u;
+        if (want_hash && pass) shash += mix64((uint64_t)(uint32_t)m.orig[pos]);
+        // first passing lane of every run of equal voxel ids emits the voxel
+        uint32_t u_prev = __shfl_up_sync(0xffffffffu, u, 1);
+        bool head = (lane == 0) || (u != u_prev);
+        unsigned hb = __ballot_sync(0xffffffffu, head);
+        unsigned below = hb & ((2u << lane) - 1);          // heads at or below this lane
+        int my_head = 31 - __clz(below);
+        unsigned run_lower = pm & ((1u << lane) - 1) & ~((1u << my_head) - 1);  // passing lanes of my run below me
+        bool emit = pass && (run_lower == 0);
+        unsigned eb = __ballot_sync(0xffffffffu, emit);
+        unsigned slot = 0;
+        if (lane == 0) slot = atomicAdd(&sh.list_count, (unsigned)__popc(eb));
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (emit) {
+          unsigned at = slot + __popc(eb & ((1u << lane) - 1));
+          if (at < A.list_cap) vox_list[at] = u;
+          // voxel coordinates as <PCL getGridCoordinates>: floor(x * inverse_leaf) (same value as m.vox[u])
+          int vi = (int)floorf(fmul(p.x, m.inv_leaf)), vj = (int)floorf(fmul(p.y, m.inv_leaf)),
+              vk = (int)floorf(fmul(p.z, m.inv_leaf));
+          bmin[0] = min(bmin[0], vi); bmin[1] = min(bmin[1], vj); bmin[2] = min(bmin[2], vk);
+          bmax[0] = max(bmax[0], vi); bmax[1] = max(bmax[1], vj); bmax[2] = max(bmax[2], vk);
+        }
       }
     }
   }
@@ -559,7 +570,12 @@ __device__ __forceinline__ void trace_rays(const EvalArgs& A, ViewShared& sh, co
   const int lane = threadIdx.x & 31;
   unsigned steps = 0, fails = 0;
   const unsigned count = sh.list_count;
-  for (unsigned e0 = (threadIdx.x & ~31u); e0 < count; e0 += blockDim.x) {
+  for (;;) {
+    // warps take 32-ray tiles from a shared counter: ray lengths vary, static striding leaves a long tail
+    unsigned e0 = 0;
+    if (lane == 0) e0 = atomicAdd(&sh.ray_next, 32u);
+    e0 = __shfl_sync(0xffffffffu, e0, 0);
+    if (e0 >= count) break;
     const unsigned e = e0 + lane;
     uint32_t u = e < count ? vox_list[e] : 0xffffffffu;
     bool visible = false;
@@ -603,7 +619,7 @@ __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   }
   if (threadIdx.x == 0) {
     sh.view = v;
-    sh.chunk_count = 0; sh.list_count = 0; sh.vis_count = 0;
+    sh.chunk_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0;
     sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
     sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
     sh.words = 0; sh.use_smem = 1;
