@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libasscpp_b200.so")
+LIB_PATH = os.environ.get("ASSCPP_LIB") or os.path.join(_HERE, "lib", "libasscpp_b200.so")
 
 OK, EINVAL, ENODEVICE, ECUDA, ERANGE, ENOMEM, ESTATE, ENCCL = 0, -1, -2, -3, -4, -5, -6, -7
 EVAL_HASH, EVAL_BRUTE, EVAL_FORCE_GLOBAL = 1, 2, 4

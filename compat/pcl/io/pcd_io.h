@@ -1,0 +1,55 @@
+// Stand-in for pcl::io::loadPCDFile<pcl::PointXYZ> (occlusion_culling.cpp:39): PCD v0.7, FIELDS x y z,
+// float32, DATA ascii | binary.  Sets sensor_origin_ from VIEWPOINT like PCL does.
+#pragma once
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include "../point_types.h"
+namespace pcl {
+namespace io {
+inline int loadPCDFile(const std::string& path, PointCloud<PointXYZ>& cloud) {
+  std::ifstream f(path.c_str(), std::ios::binary);
+  if (!f) return -1;
+  std::string line, data;
+  size_t npts = 0;
+  while (std::getline(f, line)) {
+    if (!line.empty() && line[line.size() - 1] == '\r') line.erase(line.size() - 1);
+    std::istringstream ss(line);
+    std::string key;
+    ss >> key;
+    if (key == "FIELDS") {
+      std::string a, b, c;
+      ss >> a >> b >> c;
+      if (a != "x" || b != "y" || c != "z") return -2;
+    } else if (key == "POINTS") {
+      ss >> npts;
+    } else if (key == "VIEWPOINT") {
+      ss >> cloud.sensor_origin_[0] >> cloud.sensor_origin_[1] >> cloud.sensor_origin_[2];
+      cloud.sensor_origin_[3] = 0;
+    } else if (key == "DATA") {
+      ss >> data;
+      break;
+    }
+  }
+  cloud.points.resize(npts);
+  if (data == "binary") {
+    std::vector<float> raw(3 * npts);
+    f.read(reinterpret_cast<char*>(raw.data()), (std::streamsize)(raw.size() * sizeof(float)));
+    if ((size_t)f.gcount() != raw.size() * sizeof(float)) return -3;
+    for (size_t i = 0; i < npts; ++i) cloud.points[i] = PointXYZ(raw[3 * i], raw[3 * i + 1], raw[3 * i + 2]);
+  } else if (data == "ascii") {
+    for (size_t i = 0; i < npts; ++i) {
+      float x, y, z;
+      if (!(f >> x >> y >> z)) return -3;
+      cloud.points[i] = PointXYZ(x, y, z);
+    }
+  } else {
+    return -4;
+  }
+  cloud.width = (unsigned)npts;
+  return 0;
+}
+}  // namespace io
+}  // namespace pcl

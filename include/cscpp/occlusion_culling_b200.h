@@ -1,0 +1,149 @@
+// occlusion_culling_b200.h -- drop-in shim of the reference's OcclusionCulling class
+// (cscpp/include/cscpp/occlusion_culling.h:50-95) on top of the C ABI (include/asscpp_gpu.h).
+//
+// Same class name, same public data members the callers touch (cloud, cloudCopy, filtered_cloud,
+// occlusionFreeCloud, FrustumCloud, freeCloud, voxelRes, OriginalVoxelsSize, maxAccuracyError, ...),
+// same method signatures on the hot path:
+//     pcl::PointCloud<pcl::PointXYZ> extractVisibleSurface(geometry_msgs::Pose)   (:82,  .cpp:265-373)
+//     float calcCoveragePercent(pcl::PointCloud<pcl::PointXYZ>::Ptr)              (:84,  .cpp:375-444)
+// plus non-breaking batched entry points used by the viewpoint batcher.  With real ROS/PCL headers on
+// the include path the same source builds against them; otherwise the stand-ins under compat/ are used
+// and the two ros::NodeHandle constructors are not declared.
+//
+// There is no CPU fallback: construction throws std::runtime_error when no sm_100 GPU is usable.
+#pragma once
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include <geometry_msgs/Pose.h>
+#include <pcl/io/pcd_io.h>
+#include <pcl/point_types.h>
+
+#include "../asscpp_gpu.h"
+
+class OcclusionCulling {
+ public:
+  // attributes kept from the reference (occlusion_culling.h:54-74)
+  std::string model;
+  pcl::PointCloud<pcl::PointXYZ>::Ptr cloud;
+  pcl::PointCloud<pcl::PointXYZ>::Ptr cloudCopy;
+  pcl::PointCloud<pcl::PointXYZ>::Ptr filtered_cloud;
+  pcl::PointCloud<pcl::PointXYZ>::Ptr occlusionFreeCloud;
+  pcl::PointCloud<pcl::PointXYZ>::Ptr FrustumCloud;
+  pcl::PointCloud<pcl::PointXYZ> freeCloud;
+  float voxelRes, OriginalVoxelsSize, viewEntropy;
+  double id;
+  double maxAccuracyError, minAccuracyError;
+  bool AccuracyMaxSet;
+  std::string frame_id;
+  // The reference appends every visible point of every call to occlusionFreeCloud forever
+  // (occlusion_culling.cpp:363).  Kept on by default for fidelity; the batcher turns it off.
+  bool accumulateOcclusionFreeCloud;
+
+  explicit OcclusionCulling(std::string modelName, int device = 0) : model(modelName) {
+    init_members();
+    pcl::io::loadPCDFile(model, *cloud);  // occlusion_culling.cpp:39 (a missing file yields an empty cloud)
+    finish_init(device);
+  }
+  explicit OcclusionCulling(pcl::PointCloud<pcl::PointXYZ>::Ptr& cloudPtr, int device = 0) {
+    init_members();
+    cloud->points = cloudPtr->points;  // occlusion_culling.cpp:94
+    std::memcpy(cloud->sensor_origin_, cloudPtr->sensor_origin_, sizeof(cloud->sensor_origin_));
+    finish_init(device);
+  }
+  ~OcclusionCulling() { asscpp_destroy(ctx_); }
+  OcclusionCulling(const OcclusionCulling&) = delete;
+  OcclusionCulling& operator=(const OcclusionCulling&) = delete;
+
+  // occlusion_culling.cpp:265-373
+  pcl::PointCloud<pcl::PointXYZ> extractVisibleSurface(geometry_msgs::Pose location) {
+    std::vector<int32_t> idx;
+    visibleIndices(location, idx);
+    freeCloud.points.resize(idx.size());
+    for (size_t k = 0; k < idx.size(); ++k) freeCloud.points[k] = cloudCopy->points[(size_t)idx[k]];
+    freeCloud.width = (unsigned)idx.size();
+    if (accumulateOcclusionFreeCloud)
+      occlusionFreeCloud->points.insert(occlusionFreeCloud->points.end(), freeCloud.points.begin(),
+                                        freeCloud.points.end());
+    return freeCloud;
+  }
+
+  // occlusion_culling.cpp:375-444: any cloud (e.g. VoxelGrid centroids, heuristic.cpp:476-482)
+  float calcCoveragePercent(pcl::PointCloud<pcl::PointXYZ>::Ptr cloud_filtered) {
+    std::vector<float> xyz(3 * cloud_filtered->points.size());
+    for (size_t i = 0; i < cloud_filtered->points.size(); ++i) {
+      xyz[3 * i] = cloud_filtered->points[i].x;
+      xyz[3 * i + 1] = cloud_filtered->points[i].y;
+      xyz[3 * i + 2] = cloud_filtered->points[i].z;
+    }
+    float pct = 0;
+    check(asscpp_coverage_percent_cloud(ctx_, xyz.data(), (int64_t)cloud_filtered->points.size(), &pct));
+    return pct;
+  }
+
+  // ---- additions (non-breaking) -----------------------------------------------------------------
+  // ascending original indices of extractVisibleSurface's cloud
+  void visibleIndices(const geometry_msgs::Pose& location, std::vector<int32_t>& idx) {
+    double p[7];
+    pack(location, p);
+    idx.resize(cloudCopy->points.size());
+    int64_t n = 0;
+    check(asscpp_get_visible(ctx_, p, idx.data(), (int64_t)idx.size(), &n));
+    idx.resize((size_t)n);
+  }
+  // one launch for a whole batch of viewpoints; covered_set = -1 scores against the empty set
+  void evalBatch(const std::vector<geometry_msgs::Pose>& poses, std::vector<AsscppViewResult>& out,
+                 int covered_set = -1, uint32_t flags = 0) {
+    std::vector<double> p(7 * poses.size());
+    for (size_t i = 0; i < poses.size(); ++i) pack(poses[i], &p[7 * i]);
+    out.resize(poses.size());
+    check(asscpp_eval_batch(ctx_, p.data(), (int64_t)poses.size(), covered_set, flags));
+    check(asscpp_get_results(ctx_, out.data(), (int64_t)poses.size()));
+  }
+  AsscppCtx* context() { return ctx_; }
+  static void pack(const geometry_msgs::Pose& q, double p[7]) {
+    p[0] = q.position.x; p[1] = q.position.y; p[2] = q.position.z;
+    p[3] = q.orientation.x; p[4] = q.orientation.y; p[5] = q.orientation.z; p[6] = q.orientation.w;
+  }
+  void check(int rc) const {
+    if (rc != ASSCPP_OK) throw std::runtime_error(std::string("asscpp: ") + asscpp_last_error(ctx_));
+  }
+
+ private:
+  AsscppCtx* ctx_ = nullptr;
+  void init_members() {
+    typedef pcl::PointCloud<pcl::PointXYZ> Cloud;
+    cloud = Cloud::Ptr(new Cloud);
+    cloudCopy = Cloud::Ptr(new Cloud);
+    filtered_cloud = Cloud::Ptr(new Cloud);
+    occlusionFreeCloud = Cloud::Ptr(new Cloud);
+    FrustumCloud = Cloud::Ptr(new Cloud);
+    voxelRes = 0.5f;  // occlusion_culling.cpp:41
+    OriginalVoxelsSize = 0.0f;
+    viewEntropy = 0.0f;
+    id = 0.0;
+    maxAccuracyError = minAccuracyError = 0.0;
+    AccuracyMaxSet = false;
+    frame_id = "world";
+    accumulateOcclusionFreeCloud = true;
+  }
+  void finish_init(int device) {
+    cloudCopy->points = cloud->points;  // occlusion_culling.cpp:40
+    AsscppParams prm;
+    asscpp_default_params(&prm);  // VFOV 45, HFOV 58, near 0.7, far 6.0 (occlusion_culling.cpp:73-76)
+    prm.leaf = voxelRes;
+    prm.cov_leaf = voxelRes;      // calcCoveragePercent voxelises at voxelRes (occlusion_culling.cpp:390)
+    for (int k = 0; k < 3; ++k) prm.pcd_origin[k] = cloud->sensor_origin_[k];  // used at :338-341
+    std::vector<float> xyz(3 * cloud->points.size());
+    for (size_t i = 0; i < cloud->points.size(); ++i) {
+      xyz[3 * i] = cloud->points[i].x; xyz[3 * i + 1] = cloud->points[i].y; xyz[3 * i + 2] = cloud->points[i].z;
+    }
+    int rc = asscpp_create(device, xyz.data(), (int64_t)cloud->points.size(), &prm, &ctx_);
+    if (rc != ASSCPP_OK) throw std::runtime_error(std::string("asscpp_create: ") + asscpp_last_error(nullptr));
+    AsscppModelInfo info;
+    asscpp_model_info(ctx_, &info);
+    OriginalVoxelsSize = (float)info.n_cov_voxels;  // occlusion_culling.cpp:50-65
+  }
+};

@@ -1,0 +1,145 @@
+// coverage_heuristic_b200.h -- the node-scoring side of the boundary: SurfaceCoverageH of
+// SSPP::CoveragePathPlanningHeuristic (cscpp/src/coverage_path_planning_heuristic.cpp:425-488, root
+// :1227-1240), the acceptance rule of isFilteringConditionSatisfied (:339-357) and pointCloudDiff's
+// uncovered percentage (:88-145), all in covered-bitset form on top of the C ABI.
+//
+// What changes against the reference: Node::cloud_filtered (a re-voxelised point cloud per node) becomes
+// a device-resident covered set handle; the per-child call pattern of Astar (sspp/src/astar.cpp:311-357)
+// is fed by ViewpointBatcher::prefetch(), which pushes the sensor poses of ALL children of an expansion
+// through one asscpp_eval_batch launch and caches the per-view results by node id.
+#pragma once
+#include <cmath>
+#include <map>
+#include <vector>
+
+#include "../cscpp/occlusion_culling_b200.h"
+
+namespace SSPP {
+
+// Minimal stand-in of SSPP::Node (sspp/include/sspp/node.h:48-71) with the fields the coverage
+// heuristic reads and writes.  cloud_filtered is replaced by covered_set.
+struct NodeB200 {
+  int id = 0;
+  NodeB200* parent = nullptr;
+  geometry_msgs::Pose pose;                   // robot pose (Node::pose.p)
+  std::vector<geometry_msgs::Pose> senPoses;  // one per sensor (Node::senPoses[i].p)
+  double f_value = 0, g_value = 0, h_value = 0, distance = 0, coverage = 0;
+  int covered_set = -1;                       // replaces Node::cloud_filtered
+};
+
+class ViewpointBatcher {
+ public:
+  explicit ViewpointBatcher(OcclusionCulling* oc) : oc_(oc) {}
+  // One launch for every sensor pose of every child; scored against the parent's covered set.
+  void prefetch(NodeB200* const* children, int n, int parent_set) {
+    std::vector<geometry_msgs::Pose> poses;
+    std::vector<std::pair<int, int> > owner;  // (node id, sensor)
+    for (int i = 0; i < n; ++i)
+      for (size_t s = 0; s < children[i]->senPoses.size(); ++s) {
+        poses.push_back(children[i]->senPoses[s]);
+        owner.push_back(std::make_pair(children[i]->id, (int)s));
+      }
+    std::vector<AsscppViewResult> res;
+    oc_->evalBatch(poses, res, parent_set, 0);
+    for (size_t k = 0; k < res.size(); ++k) cache_[owner[k]] = res[k];
+    launches_++;
+  }
+  bool lookup(int node_id, int sensor, AsscppViewResult* out) const {
+    std::map<std::pair<int, int>, AsscppViewResult>::const_iterator it = cache_.find(std::make_pair(node_id, sensor));
+    if (it == cache_.end()) return false;
+    *out = it->second;
+    return true;
+  }
+  void clear() { cache_.clear(); }
+  int launches() const { return launches_; }
+
+ private:
+  OcclusionCulling* oc_;
+  std::map<std::pair<int, int>, AsscppViewResult> cache_;
+  int launches_ = 0;
+};
+
+class CoverageHeuristicB200 {
+ public:
+  CoverageHeuristicB200(OcclusionCulling* oc, double coverageTarget, double coverageTolerance)
+      : oc_(oc), batcher_(oc), target_(coverageTarget), tol_(coverageTolerance) {}
+
+  ViewpointBatcher& batcher() { return batcher_; }
+
+  // coverage_path_planning_heuristic.cpp:425-488 (SurfaceCoverageH) / :1227-1240 (root)
+  void calculateHeuristic(NodeB200* node) {
+    if (!node) return;
+    AsscppCtx* c = oc_->context();
+    if (node->covered_set < 0) {
+      if (node->parent && node->parent->covered_set >= 0)
+        oc_->check(asscpp_covered_clone(c, node->parent->covered_set, &node->covered_set));  // :473 parent's cloud
+      else
+        oc_->check(asscpp_covered_new(c, &node->covered_set));
+    }
+    std::vector<double> p(7 * node->senPoses.size());
+    for (size_t s = 0; s < node->senPoses.size(); ++s) OcclusionCulling::pack(node->senPoses[s], &p[7 * s]);
+    // visibleCloud += extractVisibleSurface(senPoses[i]) for every sensor (:439-445); union into the set (:474-480)
+    oc_->check(asscpp_covered_or_views(c, node->covered_set, p.data(), (int64_t)node->senPoses.size(), -1));
+    float pct = 0;
+    oc_->check(asscpp_coverage_percent(c, node->covered_set, &pct));  // :482
+    node->coverage = pct;
+    if (node->parent) {
+      double dx = node->pose.position.x - node->parent->pose.position.x,
+             dy = node->pose.position.y - node->parent->pose.position.y,
+             dz = node->pose.position.z - node->parent->pose.position.z;
+      double d = std::sqrt(dx * dx + dy * dy + dz * dz);  // Dist(), sspp/include/sspp/utils.h
+      node->distance = node->parent->distance + d;         // :452
+      double cgain = node->coverage - node->parent->coverage;  // :483
+      node->h_value = 0; node->g_value = 0;
+      node->f_value = d != 0.0 ? node->parent->f_value + (1 / d) * cgain  // :487
+                               : node->parent->f_value + cgain;            // :780
+    } else {
+      node->distance = 0; node->h_value = 0; node->g_value = 0;
+      node->f_value = node->coverage;  // root: :1232-1238
+    }
+  }
+
+  // coverage_path_planning_heuristic.cpp:253-283
+  bool terminateConditionReached(const NodeB200* node) const {
+    double delta = target_ - node->coverage;
+    return delta <= tol_;
+  }
+
+  // acceptance rule of isFilteringConditionSatisfied (:339-357) for candidates whose geometric filters
+  // (CGAL inside test / stand-off distance, :320-335) passed on the host: accept iff the sensors see more
+  // than 5 points in total; each sensor cloud with more than 5 points joins the global covered set.
+  // One batched launch for all candidates; accepted[i] is written per candidate.
+  void filterCandidates(const std::vector<std::vector<geometry_msgs::Pose> >& sensorPoses, int global_set,
+                        std::vector<char>& accepted) {
+    std::vector<geometry_msgs::Pose> flat;
+    for (size_t i = 0; i < sensorPoses.size(); ++i) flat.insert(flat.end(), sensorPoses[i].begin(), sensorPoses[i].end());
+    std::vector<AsscppViewResult> res;
+    oc_->evalBatch(flat, res, -1, 0);
+    std::vector<double> p(7 * flat.size());
+    for (size_t k = 0; k < flat.size(); ++k) OcclusionCulling::pack(flat[k], &p[7 * k]);
+    oc_->check(asscpp_covered_or_views(oc_->context(), global_set, p.data(), (int64_t)flat.size(), 5));  // :344-346
+    accepted.assign(sensorPoses.size(), 0);
+    size_t k = 0;
+    for (size_t i = 0; i < sensorPoses.size(); ++i) {
+      unsigned long long total = 0;
+      for (size_t s = 0; s < sensorPoses[i].size(); ++s) total += res[k++].visible;
+      accepted[i] = total > 5;  // :357
+    }
+  }
+
+  // pointCloudDiff (:88-145): uncovered model voxels / model voxels * 100 (double arithmetic, :143)
+  double uncoveredPercent(int global_set) {
+    int64_t npts = 0, nvox = 0;
+    oc_->check(asscpp_covered_popcount(oc_->context(), global_set, &npts, &nvox));
+    AsscppModelInfo info;
+    asscpp_model_info(oc_->context(), &info);
+    return ((double)(info.n_cov_voxels - nvox) / (double)info.n_cov_voxels) * 100;
+  }
+
+ private:
+  OcclusionCulling* oc_;
+  ViewpointBatcher batcher_;
+  double target_, tol_;
+};
+
+}  // namespace SSPP

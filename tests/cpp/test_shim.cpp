@@ -1,0 +1,94 @@
+// Exercises the C++ class surface the reference's callers use (OcclusionCulling::extractVisibleSurface /
+// calcCoveragePercent, the SurfaceCoverageH node scoring and the ASSCPP acceptance rule) through the
+// shim headers, and prints results for tests/test_cpp_shim.py to compare with the oracle.
+//   test_shim <model.pcd> <poses.txt (x y z qx qy qz qw per line, two consecutive lines = one waypoint)>
+#include <cstdio>
+#include <fstream>
+#include <sstream>
+
+#include <cscpp/occlusion_culling_b200.h>
+#include <sspp/coverage_heuristic_b200.h>
+
+static unsigned long long mix64(unsigned long long x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+int main(int argc, char** argv) {
+  if (argc < 3) return 2;
+  OcclusionCulling oc{std::string(argv[1])};
+  std::vector<geometry_msgs::Pose> poses;
+  std::ifstream f(argv[2]);
+  std::string line;
+  while (std::getline(f, line)) {
+    std::istringstream ss(line);
+    geometry_msgs::Pose p;
+    if (ss >> p.position.x >> p.position.y >> p.position.z >> p.orientation.x >> p.orientation.y >> p.orientation.z >>
+        p.orientation.w)
+      poses.push_back(p);
+  }
+  std::printf("model %zu points OriginalVoxelsSize %.0f\n", oc.cloud->points.size(), oc.OriginalVoxelsSize);
+  // 1. extractVisibleSurface + calcCoveragePercent, one call per pose like the reference's loops
+  for (size_t k = 0; k < poses.size(); ++k) {
+    pcl::PointCloud<pcl::PointXYZ> vis = oc.extractVisibleSurface(poses[k]);
+    std::vector<int32_t> idx;
+    oc.visibleIndices(poses[k], idx);
+    unsigned long long h = 0;
+    bool same = idx.size() == vis.points.size();
+    for (size_t i = 0; i < idx.size(); ++i) {
+      h += mix64((unsigned long long)idx[i]);
+      const pcl::PointXYZ& a = vis.points[i];
+      const pcl::PointXYZ& b = oc.cloudCopy->points[(size_t)idx[i]];
+      same = same && a.x == b.x && a.y == b.y && a.z == b.z;
+    }
+    pcl::PointCloud<pcl::PointXYZ>::Ptr vp(new pcl::PointCloud<pcl::PointXYZ>(vis));
+    float pct = oc.calcCoveragePercent(vp);
+    std::printf("view %zu visible %zu hash %llu cloud_matches %d coverage %.9g\n", k, vis.points.size(), h, (int)same,
+                (double)pct);
+  }
+  // 2. SurfaceCoverageH greedy walk: waypoints = consecutive pose pairs (two sensors each)
+  std::vector<SSPP::NodeB200> nodes(poses.size() / 2);
+  for (size_t i = 0; i < nodes.size(); ++i) {
+    nodes[i].id = (int)i;
+    nodes[i].pose = poses[2 * i];
+    nodes[i].senPoses.push_back(poses[2 * i]);
+    nodes[i].senPoses.push_back(poses[2 * i + 1]);
+  }
+  SSPP::CoverageHeuristicB200 heur(&oc, 100.0, 1.0);
+  std::vector<SSPP::NodeB200> path;
+  path.reserve(16);
+  SSPP::NodeB200 root = nodes[0];
+  heur.calculateHeuristic(&root);
+  path.push_back(root);
+  std::printf("root coverage %.9g f %.9g\n", root.coverage, root.f_value);
+  for (int step = 0; step < 4; ++step) {
+    SSPP::NodeB200* parent = &path.back();
+    std::vector<SSPP::NodeB200> kids(nodes.begin() + 1, nodes.end());
+    std::vector<SSPP::NodeB200*> ptrs;
+    for (size_t i = 0; i < kids.size(); ++i) { kids[i].parent = parent; ptrs.push_back(&kids[i]); }
+    heur.batcher().prefetch(ptrs.data(), (int)ptrs.size(), parent->covered_set);
+    int best = -1;
+    for (size_t i = 0; i < kids.size(); ++i) {
+      heur.calculateHeuristic(&kids[i]);  // astar.cpp:318, one child at a time
+      if (best < 0 || kids[i].f_value > kids[(size_t)best].f_value) best = (int)i;
+    }
+    std::printf("step %d best %d coverage %.9g f %.9g\n", step, kids[(size_t)best].id, kids[(size_t)best].coverage,
+                kids[(size_t)best].f_value);
+    path.push_back(kids[(size_t)best]);
+    path.back().parent = nullptr;  // the walk keeps only coverage / f / set of the chosen node
+    path.back().distance = 0;
+  }
+  // 3. ASSCPP acceptance rule + uncovered percentage
+  int global_set = -1;
+  oc.check(asscpp_covered_new(oc.context(), &global_set));
+  std::vector<std::vector<geometry_msgs::Pose> > cand;
+  for (size_t i = 0; i < nodes.size(); ++i) cand.push_back(nodes[i].senPoses);
+  std::vector<char> accepted;
+  heur.filterCandidates(cand, global_set, accepted);
+  int nacc = 0;
+  for (size_t i = 0; i < accepted.size(); ++i) nacc += accepted[i];
+  std::printf("accepted %d of %zu uncovered %.9g\n", nacc, accepted.size(), heur.uncoveredPercent(global_set));
+  return 0;
+}

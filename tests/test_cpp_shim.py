@@ -1,0 +1,95 @@
+"""The C++ drop-in surface (include/cscpp/occlusion_culling_b200.h, include/sspp/coverage_heuristic_b200.h):
+it compiles against the compat/ stand-ins (CPU test) and, on a GPU, reproduces the oracle's visible sets,
+coverage percentages, SurfaceCoverageH walk and ASSCPP acceptance counts (gpu test)."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+MOUNTS = (((0.0, 0.022, 0.065), (0.0, -0.349, 0.0)), ((0.0, 0.022, -0.065), (0.0, 0.349, 0.0)))
+
+
+def build_shim(tmp_path, lib_built):
+    exe = str(tmp_path / "test_shim")
+    libdir = os.path.dirname(lib_built)
+    subprocess.check_call(["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(ROOT, "compat"),
+                           "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "cpp", "test_shim.cpp"),
+                           "-L" + libdir, "-lasscpp_b200", "-Wl,-rpath," + libdir, "-o", exe])
+    return exe
+
+
+def test_shim_compiles_and_links(tmp_path, lib_built):
+    exe = build_shim(tmp_path, lib_built)
+    assert os.path.exists(exe)
+
+
+def write_pcd(path, xyz):
+    with open(path, "wb") as f:
+        f.write(("# .PCD v0.7\nVERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nCOUNT 1 1 1\nWIDTH %d\nHEIGHT 1\n"
+                 "VIEWPOINT 0 0 0 0 0.5 0 0\nPOINTS %d\nDATA binary\n" % (len(xyz), len(xyz))).encode())
+        f.write(np.ascontiguousarray(xyz, "<f4").tobytes())
+
+
+@pytest.mark.gpu
+def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5):
+    O = oracle_mod
+    xyz, _ = etihad
+    exe = build_shim(tmp_path, lib_built)
+    pcd = str(tmp_path / "model.pcd")
+    write_pcd(pcd, xyz)
+    rows = [600, 610, 633, 700, 742, 815, 900, 1010]
+    poses = np.stack([space_2p5[c][k] for k in rows for c in ("cam0", "cam1")])
+    np.savetxt(str(tmp_path / "poses.txt"), poses, fmt="%.17g")
+    out = subprocess.check_output([exe, pcd, str(tmp_path / "poses.txt")], text=True)
+    o = O.Oracle(xyz)
+    assert re.search(r"model %d points OriginalVoxelsSize 2759" % len(xyz), out)
+    # 1. per-view visible set and calcCoveragePercent
+    views = re.findall(r"view (\d+) visible (\d+) hash (\d+) cloud_matches (\d) coverage (\S+)", out)
+    assert len(views) == len(poses)
+    for k, nvis, h, same, pct in views:
+        r = o.eval_view(poses[int(k)])
+        assert int(nvis) == len(r["visible"]) and int(same) == 1
+        assert int(h) == O.set_hash(r["visible"])
+        assert np.float32(float(pct)) == np.float32(o.coverage_percent_idx(r["visible"]))
+    # 2. SurfaceCoverageH walk (coverage_path_planning_heuristic.cpp:470-488) restated with the oracle
+    ids = o.cov_ids()
+    vox = [np.unique(ids[np.concatenate([o.eval_view(poses[2 * i])["visible"], o.eval_view(poses[2 * i + 1])["visible"]])])
+           for i in range(len(rows))]
+    pos = [poses[2 * i][:3] for i in range(len(rows))]
+
+    def pct(s):
+        return float(np.float32(np.float32(np.float32(len(s)) / np.float32(o.n_cov)) * np.float32(100)))
+
+    covered = set(vox[0].tolist())
+    cov, fval, cur = pct(covered), pct(covered), 0
+    m = re.search(r"root coverage (\S+) f (\S+)", out)
+    assert float(m.group(1)) == pytest.approx(cov, abs=0) and float(m.group(2)) == pytest.approx(fval, abs=0)
+    steps = re.findall(r"step (\d+) best (\d+) coverage (\S+) f (\S+)", out)
+    assert len(steps) == 4
+    for s, best, c_s, f_s in steps:
+        cand = []
+        for i in range(1, len(rows)):
+            u = covered | set(vox[i].tolist())
+            c = pct(u)
+            d = float(np.linalg.norm(pos[i] - pos[cur]))
+            gain = c - cov
+            cand.append((fval + ((1 / d) * gain if d != 0 else gain), i, c, u))
+        bi = max(range(len(cand)), key=lambda j: (cand[j][0], -j))
+        fbest, ibest, cbest, ubest = cand[bi]
+        assert int(best) == ibest, (s, best, ibest)
+        assert float(c_s) == pytest.approx(cbest, abs=1e-6) and float(f_s) == pytest.approx(fbest, rel=1e-12, abs=1e-9)
+        covered, cov, fval, cur = ubest, cbest, fbest, ibest
+    # 3. acceptance rule (:339-357) and uncovered percentage (:143)
+    st = o.eval_batch(poses, memo=True)
+    vis = st[:, O.ST_VISIBLE].reshape(-1, 2)
+    cv = np.zeros(o.vox_words(), np.uint64)
+    cp = np.zeros(o.pts_words(), np.uint64)
+    o.accumulate(poses, cp, cv, min_visible=5)
+    nvox = int(np.unpackbits(cv.view(np.uint8)).sum())
+    m = re.search(r"accepted (\d+) of (\d+) uncovered (\S+)", out)
+    assert int(m.group(1)) == int((vis.sum(1) > 5).sum()) and int(m.group(2)) == len(rows)
+    assert float(m.group(3)) == pytest.approx((o.n_cov - nvox) / o.n_cov * 100, rel=1e-12)
