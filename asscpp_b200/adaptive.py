@@ -1,0 +1,185 @@
+"""Host side of the ASSCPP adaptive sampling loop (BASELINE.json config 4) and the viewpoint sharding
+used by every multi-GPU entry point.
+
+Restates the skeleton of PathPlanner::dynamicNodesGenerationAndConnection (sspp/src/pathplanner.cpp:
+729-850) around the hot path:
+  * generate_grid()      = generateRegularGrid's z, x, y, yaw loops (pathplanner.cpp:122-147) and the two
+                           sensor poses per robot pose (sensors.cpp:47-90, mounts coverage_heuristic_test.cpp:94-95)
+  * evaluate + accept    = isFilteringConditionSatisfied's coverage part (heuristic.cpp:339-357), batched
+  * uncovered percentage = pointCloudDiff (heuristic.cpp:88-145) on the covered voxel bitset
+  * clusters + boxes     = clusteringPointCloud / findClusterBB (heuristic.cpp:147-246)
+Deviations (stated in DESIGN.md): the CGAL inside-mesh / distance filters are replaced by a stand-off test
+against the model's voxel grid, PCL's Euclidean clustering (tolerance 0.8 m on 0.5 m voxel centres) by
+18-connected components of the uncovered voxels.  Both run on the host; only the viewpoint evaluation and
+the covered-set union run on the GPUs, sharded over ranks with ONE covered-bitset OR-allreduce per iteration.
+
+The `backend` is duck-typed (GpuBackend here, OracleBackend in tests/): the same loop drives the CUDA
+path and the CPU oracle, which is how the per-iteration parity of config 4 is asserted.
+"""
+import numpy as np
+
+MOUNTS = (((0.0, 0.022, 0.065), (0.0, -0.349, 0.0)), ((0.0, 0.022, -0.065), (0.0, 0.349, 0.0)))
+
+
+def shard_range(n, world, rank):
+    """Contiguous block of [0, n) owned by `rank`."""
+    base, extra = divmod(n, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def generate_grid(center, size, res, robot2sensor, yaws=8, mounts=MOUNTS):
+    """pathplanner.cpp:122-147: z, x, y loops with `<=` bounds and += res, 8 yaws of 45 degrees.
+    Returns robot poses [n, 7] and sensor poses [n, len(mounts), 7]."""
+    def axis(c, s):
+        out, v = [], c - s / 2.0
+        while v <= c + s / 2.0:
+            out.append(v)
+            v += res
+        return out
+    robots, sensors = [], []
+    for z in axis(center[2], size[2]):
+        for x in axis(center[0], size[0]):
+            for y in axis(center[1], size[1]):
+                yaw = 0.0
+                for _ in range(yaws):
+                    rp = np.array([x, y, z, 0.0, 0.0, np.sin(yaw * 0.5), np.cos(yaw * 0.5)])  # tf createQuaternionFromYaw
+                    yaw += 45.0 * np.pi / 180.0
+                    robots.append(rp)
+                    sensors.append([robot2sensor(rp, off, rpy) for off, rpy in mounts])
+    if not robots:
+        return np.zeros((0, 7)), np.zeros((0, len(mounts), 7))
+    return np.array(robots), np.array(sensors)
+
+
+class VoxelModel:
+    """Host view of the model's coverage lattice: occupied voxel coordinates in compact-id order."""
+
+    def __init__(self, xyz, cov_leaf):
+        inv = np.float32(1.0) / np.float32(cov_leaf)
+        ijk = np.floor(xyz.astype(np.float32) * inv).astype(np.int64)
+        self.lo = ijk.min(0)
+        self.div = ijk.max(0) - self.lo + 1
+        rel = ijk - self.lo
+        key = rel[:, 0] + self.div[0] * (rel[:, 1] + self.div[1] * rel[:, 2])
+        self.keys = np.unique(key)  # ascending (k, j, i): the compact ids of the C ABI and the oracle
+        k = self.keys
+        self.ijk = np.stack([k % self.div[0], (k // self.div[0]) % self.div[1], k // (self.div[0] * self.div[1])], 1) + self.lo
+        self.leaf = float(cov_leaf)
+        self.centres = (self.ijk + 0.5) * self.leaf
+        self.n = len(k)
+
+    def standoff_ok(self, positions, dmin=1.0, dmax=4.0):
+        """Stand-in for the CGAL distance filter (heuristic.cpp:328-331): distance from the waypoint to the
+        nearest occupied voxel centre within [dmin, dmax]."""
+        ok = np.zeros(len(positions), bool)
+        for s in range(0, len(positions), 512):
+            d = np.sqrt(((positions[s:s + 512, None, :] - self.centres[None, :, :]) ** 2).sum(-1)).min(1)
+            ok[s:s + 512] = (d >= dmin) & (d <= dmax)
+        return ok
+
+    def clusters(self, uncovered_ids, min_size=5):
+        """18-connected components of the uncovered voxels (centres within 0.8 m at a 0.5 m lattice)."""
+        pts = {tuple(self.ijk[i]): i for i in uncovered_ids}
+        offs = [(a, b, c) for a in (-1, 0, 1) for b in (-1, 0, 1) for c in (-1, 0, 1) if 0 < abs(a) + abs(b) + abs(c) <= 2]
+        seen, out = set(), []
+        for start in sorted(pts):
+            if start in seen:
+                continue
+            comp, stack = [], [start]
+            seen.add(start)
+            while stack:
+                v = stack.pop()
+                comp.append(pts[v])
+                for o in offs:
+                    w = (v[0] + o[0], v[1] + o[1], v[2] + o[2])
+                    if w in pts and w not in seen:
+                        seen.add(w)
+                        stack.append(w)
+            if len(comp) >= min_size:
+                out.append(np.array(sorted(comp)))
+        return out
+
+    def cluster_box(self, ids):
+        """findClusterBB (heuristic.cpp:218-246): centre of the min / max voxel, +5 m in x, y, +3 m in z."""
+        lo, hi = self.centres[ids].min(0), self.centres[ids].max(0)
+        size = np.array([abs(hi[0] - lo[0]) + 5.0, abs(hi[1] - lo[1]) + 5.0, abs(hi[2] - lo[2]) + 3.0])
+        start = np.array([lo[0] - 2.5, lo[1] - 2.5, lo[2]])
+        return start, size
+
+
+def bits_to_ids(bits, n):
+    return np.nonzero(np.unpackbits(bits.view(np.uint8), bitorder="little")[:n])[0]
+
+
+class GpuBackend:
+    """CUDA path: evaluation, union and reduction all through the C ABI."""
+
+    def __init__(self, ctx, comm=False):
+        self.ctx, self.comm = ctx, comm
+        self.set = ctx.new_set()
+        self.n_cov = ctx.n_cov_voxels
+
+    def robot2sensor(self, rp, off, rpy):
+        from . import robot2sensor
+        return robot2sensor(rp, off, rpy)
+
+    def evaluate_and_accumulate(self, poses, min_visible=5):
+        """visible count per pose; every view with more than min_visible points joins the covered set."""
+        if len(poses) == 0:
+            return np.zeros(0, np.int64)
+        self.set.or_views(poses, min_visible)          # heuristic.cpp:344-346
+        return self.ctx.results(len(poses))["visible"].astype(np.int64)
+
+    def reduce(self):
+        if self.comm:
+            self.ctx.allreduce_or(self.set)            # covered-bitset OR-allreduce between iterations
+
+    def covered_voxels(self):
+        return self.set.export()[1]
+
+
+def adaptive_loop(backend, model, grid_center, grid_size, start_res=4.5, res_dec=1.5, world=1, rank=0,
+                  gather_counts=None, max_iters=8, log=None):
+    """dynamicNodesGenerationAndConnection (pathplanner.cpp:729-850) around the hot path.
+
+    Every rank generates the same candidate list, evaluates its contiguous shard, and the covered bitsets
+    are OR-reduced once per iteration; acceptance counts are summed through `gather_counts` (identity for
+    one rank).  Returns the per-iteration trace used by the parity tests.
+    """
+    trace = []
+    res = start_res
+    boxes = [(np.asarray(grid_center, float), np.asarray(grid_size, float))]
+    for it in range(max_iters):
+        accepted_total, cand_total = 0, 0
+        for center, size in boxes:
+            robots, sensors = generate_grid(center, size, res, backend.robot2sensor)
+            if len(robots) == 0:
+                continue
+            keep = model.standoff_ok(robots[:, :3])  # stand-in for heuristic.cpp:320-335
+            robots, sensors = robots[keep], sensors[keep]
+            lo, hi = shard_range(len(robots), world, rank)
+            flat = sensors[lo:hi].reshape(-1, 7)
+            vis = backend.evaluate_and_accumulate(flat, 5).reshape(-1, sensors.shape[1]) if hi > lo else np.zeros((0, 2), np.int64)
+            accepted_total += int((vis.sum(1) > 5).sum())  # heuristic.cpp:357
+            cand_total += len(robots)
+        backend.reduce()
+        if gather_counts is not None:
+            accepted_total = gather_counts(accepted_total)
+        bits = backend.covered_voxels()
+        covered = bits_to_ids(bits, model.n)
+        uncovered = np.setdiff1d(np.arange(model.n), covered)
+        pct = (len(uncovered) / float(model.n)) * 100.0  # heuristic.cpp:143
+        trace.append({"iter": it, "res": res, "candidates": cand_total, "accepted": accepted_total,
+                      "covered_voxels": int(len(covered)), "uncovered_pct": pct, "bits": bits.copy()})
+        if log:
+            log("iter %d res %.2f candidates %d accepted %d covered %d uncovered %.3f%%"
+                % (it, res, cand_total, accepted_total, len(covered), pct))
+        if pct <= 0.01:          # pathplanner.cpp:776
+            break
+        clusters = model.clusters(uncovered)
+        res -= res_dec           # pathplanner.cpp:792
+        if res <= 0 or not clusters:
+            break
+        boxes = [model.cluster_box(c) for c in clusters]
+    return trace

@@ -272,3 +272,25 @@ def test_full_size_properties_10m(A):
     again = ctx.eval_batch(poses, covered=s)
     assert (again["gain_pts"] == 0).all() and (again["gain_vox"] == 0).all()
     ctx.close()
+
+
+def test_config4_adaptive_loop(A, oracle_mod, etihad):
+    """Config 4: the ASSCPP adaptive loop (pathplanner.cpp:729-850 skeleton) driven by the CUDA path and by
+    the oracle: identical candidate lists, identical covered bitset and acceptance count per iteration."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from asscpp_b200 import adaptive as AD
+    from backends import OracleBackend
+    xyz, _ = etihad
+    model = AD.VoxelModel(xyz, 0.5)
+    ctx = A.CoverageContext(xyz, A.default_params())
+    assert model.n == ctx.n_cov_voxels
+    tg = AD.adaptive_loop(AD.GpuBackend(ctx), model, (0, 0, 4.5), (36, 50, 9))
+    to = AD.adaptive_loop(OracleBackend(oracle_mod.Oracle(xyz), oracle_mod, NTHREADS), model, (0, 0, 4.5), (36, 50, 9))
+    assert len(tg) == len(to) >= 3
+    for a, b in zip(tg, to):
+        assert a["candidates"] == b["candidates"] and a["accepted"] == b["accepted"]
+        assert np.array_equal(a["bits"], b["bits"])
+        assert a["uncovered_pct"] == b["uncovered_pct"]
+    assert tg[-1]["uncovered_pct"] < 1.0
+    ctx.close()
