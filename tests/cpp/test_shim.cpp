@@ -62,7 +62,7 @@ int main(int argc, char** argv) {
   SSPP::NodeB200 root = nodes[0];
   heur.calculateHeuristic(&root);
   path.push_back(root);
-  std::printf("root coverage %.9g f %.9g\n", root.coverage, root.f_value);
+  std::printf("root coverage %.17g f %.17g\n", root.coverage, root.f_value);
   for (int step = 0; step < 4; ++step) {
     SSPP::NodeB200* parent = &path.back();
     std::vector<SSPP::NodeB200> kids(nodes.begin() + 1, nodes.end());
@@ -74,7 +74,7 @@ int main(int argc, char** argv) {
       heur.calculateHeuristic(&kids[i]);  // astar.cpp:318, one child at a time
       if (best < 0 || kids[i].f_value > kids[(size_t)best].f_value) best = (int)i;
     }
-    std::printf("step %d best %d coverage %.9g f %.9g\n", step, kids[(size_t)best].id, kids[(size_t)best].coverage,
+    std::printf("step %d best %d coverage %.17g f %.17g\n", step, kids[(size_t)best].id, kids[(size_t)best].coverage,
                 kids[(size_t)best].f_value);
     path.push_back(kids[(size_t)best]);
     path.back().parent = nullptr;  // the walk keeps only coverage / f / set of the chosen node
@@ -89,6 +89,6 @@ int main(int argc, char** argv) {
   heur.filterCandidates(cand, global_set, accepted);
   int nacc = 0;
   for (size_t i = 0; i < accepted.size(); ++i) nacc += accepted[i];
-  std::printf("accepted %d of %zu uncovered %.9g\n", nacc, accepted.size(), heur.uncoveredPercent(global_set));
+  std::printf("accepted %d of %zu uncovered %.17g\n", nacc, accepted.size(), heur.uncoveredPercent(global_set));
   return 0;
 }
