@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -79,6 +80,9 @@ struct AsscppCtx {
   uint2* d_chunk_list = nullptr;
   uint32_t *d_vox_list = nullptr, *d_vis_list = nullptr, *d_grid_scratch = nullptr, *d_cov_scratch = nullptr;
   int64_t vis_cap = 0;
+  uint4* d_ray_buf = nullptr;
+  int64_t ray_cap = 0;
+  int walk_thresh = 24;
   uint8_t* d_vstate = nullptr;
   int32_t* d_counters = nullptr;  // [0] work counter, [1] ordered count
   unsigned long long* d_pop = nullptr;  // 2 popcount cells
@@ -218,6 +222,8 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.chunk_list = c->d_chunk_list; a.chunk_cap = c->chunk_cap;
   a.vox_list = c->d_vox_list; a.list_cap = c->list_cap;
   a.vis_list = c->d_vis_list; a.vis_cap = c->vis_cap;
+  a.ray_buf = c->d_ray_buf; a.ray_cap = c->ray_cap;
+  a.walk_thresh = c->walk_thresh;
   a.grid_scratch = c->d_grid_scratch; a.grid_cap_words = c->grid_cap_words;
   a.cov_scratch = c->d_cov_scratch; a.cov_words = c->cov_words;
   a.vstate = c->d_vstate;
@@ -370,6 +376,9 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = dev_alloc(c, &c->d_vox_list, c->list_cap * c->ctas))) return fail(rc);
   c->vis_cap = m.n_vox + 32;
   if ((rc = dev_alloc(c, &c->d_vis_list, c->vis_cap * c->ctas))) return fail(rc);
+  c->ray_cap = std::min<int64_t>(65536, ((m.n_vox + 31) / 32) * 32 + 32);  // rays prepared per setup/walk round
+  if ((rc = dev_alloc(c, &c->d_ray_buf, 3 * c->ray_cap * c->ctas))) return fail(rc);
+  if (const char* wt = getenv("ASSCPP_WALK_THRESH")) c->walk_thresh = std::max(1, std::min(32, atoi(wt)));
   if ((rc = dev_alloc(c, &c->d_grid_scratch, c->grid_cap_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_cov_scratch, c->cov_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_vstate, std::max<int64_t>(m.n_vox, 1) * c->ordered_ctas))) return fail(rc);

@@ -67,8 +67,11 @@ struct EvalArgs {
   int64_t chunk_cap;
   uint32_t* vox_list;        // [ctas][list_cap] voxels occupied for the view (0xffffffff: duplicate)
   int64_t list_cap;
-  uint32_t* vis_list;        // [ctas][vis_cap] voxels found visible for the view
+  uint32_t* vis_list;        // [ctas][vis_cap] voxels whose ray came back free (second gate applied in P4b)
   int64_t vis_cap;
+  uint4* ray_buf;            // [ctas][3][ray_cap] prepared ray records (SoA of three 16-byte planes)
+  int64_t ray_cap;
+  int32_t walk_thresh;       // leave the DDA burst loop for service/refill when fewer lanes than this still walk
   uint32_t* grid_scratch;    // [ctas][grid_cap_words] bit-grid when it does not fit shared memory
   int64_t grid_cap_words;
   uint32_t* cov_scratch;     // [ctas][cov_words] per-view coverage-voxel marks

@@ -171,7 +171,7 @@ struct ViewShared {
   int bb_min[3], bb_max[3];
   int view;
   int use_smem;
-  unsigned chunk_count, list_count, vis_count, ray_next;
+  unsigned chunk_count, list_count, vis_count, ray_next, ray_count;
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
   int seg_last[1024];  // ordered path only
@@ -619,7 +619,7 @@ __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   }
   if (threadIdx.x == 0) {
     sh.view = v;
-    sh.chunk_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0;
+    sh.chunk_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.ray_count = 0;
     sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
     sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
     sh.words = 0; sh.use_smem = 1;

@@ -294,3 +294,18 @@ def test_config4_adaptive_loop(A, oracle_mod, etihad):
         assert a["uncovered_pct"] == b["uncovered_pct"]
     assert tg[-1]["uncovered_pct"] < 1.0
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_nccl_legs_two_gpus():
+    """asscpp_allgather_results / asscpp_allreduce_or over real NCCL (needs >= 2 GPUs; skipped on a 1-GPU box)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29617",
+                          os.path.join(root, "tools", "nccl_check.py")], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "OK" in out.stdout, out.stdout + out.stderr
