@@ -82,7 +82,7 @@ struct AsscppCtx {
   int64_t vis_cap = 0;
   uint4* d_ray_buf = nullptr;
   int64_t ray_cap = 0;
-  int walk_thresh = 24;
+  int walk_thresh = 16;
   uint8_t* d_vstate = nullptr;
   int32_t* d_counters = nullptr;  // [0] work counter, [1] ordered count
   unsigned long long* d_pop = nullptr;  // 2 popcount cells

@@ -610,6 +610,332 @@ __device__ __forceinline__ void trace_rays(const EvalArgs& A, ViewShared& sh, co
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// P4a, fast path: the same rays as trace_rays, reorganised so that lanes stay busy.
+//
+//   setup_rays   one thread per occupied voxel, fully converged: direction, slab test, start cell, t_max /
+//                t_delta (:99-128, :410-519) and the FIRST loop iteration (:538-579) on the start cell, whose
+//                coordinates are still at hand (it is the cell that most often lies in the halo layer).
+//                Rays that are already decided leave here (failed / free / occluded); the others are written
+//                as 48-byte records to the per-CTA ray buffer (L2-resident).
+//   walk_rays    warps pull records from the buffer; a lane that finishes its ray takes the next record instead
+//                of idling until the slowest ray of a 32-ray tile is done.  The step loop holds nothing but
+//                the bit test and the t_max update: a set bit is first classified on the linear index
+//                difference to the target (the 3x3x3 neighbourhood of the target can never occlude, quirk Q4:
+//                d^2 <= 3 < 4) and everything else (target reached, occluder, halo alias, sentinel) is parked
+//                and resolved for all parked lanes together.  DDA step counts come from the Manhattan
+//                distance between start and end cell (every iteration moves one cell along one axis).
+//
+// Record: a = {p, u, qs0 | qs1 << 16, qs2 | qt2 << 16}   p = padded linear index after the first step,
+//         b = {t_max x y z, qt0 | qt1 << 16}              qs / qt = padded start / target coordinates,
+//         c = {t_delta x y z with the step sign in the (otherwise unused) sign bit, 0}
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void dda_step(float& tx, float& ty, float& tz, int& p, float dtx, float dty, float dtz,
+                                         int k0, int k1, int k2) {
+  // :565-579, ties x -> y -> z by <=; NaN compares false and falls through to z
+  const bool sx = (tx <= ty) & (tx <= tz);
+  const bool sy = (!sx) & (ty <= tz) & (ty <= tx);
+  const bool sz = !(sx | sy);
+  tx = sx ? fadd(tx, dtx) : tx;
+  ty = sy ? fadd(ty, dty) : ty;
+  tz = sz ? fadd(tz, dtz) : tz;
+  p += sx ? k0 : (sy ? k1 : k2);
+}
+
+// occupancy of the cell at relative coordinates c (halo cells: <PCL getCentroidIndexAt> aliasing, quirk Q3)
+template <bool SMEM>
+__device__ __forceinline__ bool cell_occupied(const GridView& g, const GridMem& gm, int c0, int c1, int c2) {
+  int a0 = c0, a1 = c1, a2 = c2;
+  if (c0 < 0 || c0 == g.div[0] || c1 < 0 || c1 == g.div[1] || c2 < 0 || c2 == g.div[2]) {
+    const int lin = c0 + c1 * g.mul1 + c2 * g.mul2;
+    if ((unsigned)lin >= g.cells) return false;
+    a2 = fast_div(lin, g.mul2, g.mD01);
+    const int ar = lin - a2 * g.mul2;
+    a1 = fast_div(ar, g.mul1, g.mD0);
+    a0 = ar - a1 * g.mul1;
+  }
+  const int pa = (a0 + 2) + (a1 + 2) * g.P0 + (a2 + 2) * g.P01;
+  return (grid_load<SMEM>(gm, (unsigned)pa >> 5) >> (pa & 31)) & 1u;
+}
+
+// :558-562 for the occupied cell c against the target cell t (relative coordinates)
+__device__ __forceinline__ bool is_occluder(const GridView& g, int c0, int c1, int c2, int t0, int t1, int t2) {
+  const int o0 = abs(c0 - t0), o1 = abs(c1 - t1), o2 = abs(c2 - t2);
+  if (max(o0, max(o1, o2)) >= 3) return true;  // d^2 >= 9 leaf^2: no float32 rounding can bring it under 4 leaf^2
+  float dx = fsub(centre(g, 0, c0), centre(g, 0, t0)), dy = fsub(centre(g, 1, c1), centre(g, 1, t1)),
+        dz = fsub(centre(g, 2, c2), centre(g, 2, t2));
+  float sum = fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz));  // :560
+  return sum > g.thr_sq;                                             // :561
+}
+
+template <bool SMEM>
+__device__ __forceinline__ void setup_rays(const EvalArgs& A, ViewShared& sh, const GridMem& gm,
+                                           const uint32_t* vox_list, unsigned e_begin, unsigned e_end, uint4* ray_buf,
+                                           uint32_t* cand_list) {
+  const ModelDev& m = A.m;
+  const GridView& g = sh.g;
+  const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const unsigned lt = (1u << lane) - 1;
+  unsigned steps = 0, fails = 0;
+  for (unsigned e0 = e_begin + warp * 32; e0 < e_end; e0 += nwarps * 32) {
+    const unsigned e = e0 + lane;
+    const uint32_t u = e < e_end ? vox_list[e] : 0xffffffffu;
+    int kind = 0;  // 0 nothing to emit, 1 free (candidate for the second gate), 2 walk
+    uint4 ra = make_uint4(0, 0, 0, 0);
+    float4 rb = make_float4(0, 0, 0, 0), rc = make_float4(0, 0, 0, 0);
+    if (u != 0xffffffffu) {
+      const int4 vx = m.vox[u];
+      const int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
+      const float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
+      float d[3];
+      direction(tc, origin, d);                 // :111-113
+      const float tmin = ray_box(g, origin, d); // :116
+      if (tmin == -1.0f) {
+        ++fails;                                // :118-122, quirk Q5
+      } else {
+        float t_max[3], t_delta[3];
+        int r[3], step[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          float start = fadd(origin[c], fmul(tmin, d[c]));                   // :422
+          int ijk = (int)floorf(fadd(fmul(start, g.inv), 0.5f));             // :425
+          r[c] = ijk - g.min_b[c];
+          float vm = centre(g, c, r[c]);                                     // :432
+          if (d[c] >= 0) { vm = fadd(vm, g.half); step[c] = 1; }             // :436-465
+          else           { vm = fsub(vm, g.half); step[c] = -1; }
+          t_max[c] = fadd(tmin, fdiv(fsub(vm, start), d[c]));                // :513-515
+          t_delta[c] = fdiv(g.leaf, fabsf(d[c]));                            // :517-519
+        }
+        if (!((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
+              (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1))) {
+          kind = 1;                             // :538-540 false on entry: result 0, no iteration
+        } else {
+          // first iteration; rays that go on are counted in walk_rays from their start cell
+          if (r[0] == rt[0] && r[1] == rt[1] && r[2] == rt[2]) {
+            kind = 1;                           // :551-552
+            ++steps;
+          } else if (cell_occupied<SMEM>(g, gm, r[0], r[1], r[2]) &&
+                     is_occluder(g, r[0], r[1], r[2], rt[0], rt[1], rt[2])) {
+            kind = 0;                           // occluded by its start cell
+            ++steps;
+          } else {
+            kind = 2;
+            const int P0 = g.P0, P01 = g.P01;
+            int p = (r[0] + 2) + (r[1] + 2) * P0 + (r[2] + 2) * P01;
+            float tx = t_max[0], ty = t_max[1], tz = t_max[2];
+            dda_step(tx, ty, tz, p, t_delta[0], t_delta[1], t_delta[2], step[0], step[1] * P0, step[2] * P01);
+            ra = make_uint4((unsigned)p, u, (unsigned)(r[0] + 2) | ((unsigned)(r[1] + 2) << 16),
+                            (unsigned)(r[2] + 2) | ((unsigned)(rt[2] + 2) << 16));
+            rb = make_float4(tx, ty, tz, __uint_as_float((unsigned)(rt[0] + 2) | ((unsigned)(rt[1] + 2) << 16)));
+            rc = make_float4(__uint_as_float(__float_as_uint(t_delta[0]) & 0x7fffffffu | (step[0] < 0 ? 0x80000000u : 0u)),
+                             __uint_as_float(__float_as_uint(t_delta[1]) & 0x7fffffffu | (step[1] < 0 ? 0x80000000u : 0u)),
+                             __uint_as_float(__float_as_uint(t_delta[2]) & 0x7fffffffu | (step[2] < 0 ? 0x80000000u : 0u)),
+                             0.0f);
+          }
+        }
+      }
+    }
+    const unsigned cb = __ballot_sync(0xffffffffu, kind == 1);
+    if (cb) {
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&sh.vis_count, (unsigned)__popc(cb));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (kind == 1) cand_list[base + __popc(cb & lt)] = u;
+    }
+    const unsigned wb = __ballot_sync(0xffffffffu, kind == 2);
+    if (wb) {
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&sh.ray_count, (unsigned)__popc(wb));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (kind == 2) {
+        const unsigned at = base + __popc(wb & lt);
+        ray_buf[at] = ra;
+        reinterpret_cast<float4*>(ray_buf)[A.ray_cap + at] = rb;
+        reinterpret_cast<float4*>(ray_buf)[2 * A.ray_cap + at] = rc;
+      }
+    }
+  }
+  fails = warp_sum(fails);
+  steps = warp_sum(steps);
+  if (lane == 0) {
+    if (fails) atomicAdd(&sh.carry, fails);
+    if (steps) atomicAdd(&sh.steps, (unsigned long long)steps);
+  }
+}
+
+// The burst loop in PTX: two DDA iterations per lane, then a warp vote; leaves when fewer than `thresh`
+// lanes are still walking.  A lane stops walking at the first set bit (pbit then addresses that cell).
+// Branch-free per iteration: bit test, the x -> y -> z `<=` cascade of :565-579 as predicates (sy and sz
+// use pw ^ px = pw & !px, valid because px implies pw), predicated FADD (add.rn: never fused) and index
+// updates.  pbit = padded linear index (+ 8 * shared byte address of the grid in the SMEM variant, which
+// is a multiple of 32 bits, so pbit & 31 is still the bit number).
+#define ASSCPP_DDA_ITER(LOAD)                          \
+  " shr.u32 a, %0, 3;\n"                               \
+  " and.b32 a, a, 0xfffffffc;\n" LOAD                  \
+  " shf.r.wrap.b32 b, word, word, %0;\n"               \
+  " and.b32 b, b, 1;\n"                                \
+  " setp.eq.and.u32 pw, b, 0, pw;\n"                   \
+  " setp.le.and.f32 q1, %1, %2, pw;\n"                 \
+  " setp.le.and.f32 px, %1, %3, q1;\n"                 \
+  " xor.pred pn, pw, px;\n"                            \
+  " setp.le.and.f32 q2, %2, %3, pn;\n"                 \
+  " setp.le.and.f32 py, %2, %1, q2;\n"                 \
+  " xor.pred pz, pn, py;\n"                            \
+  " @px add.rn.f32 %1, %1, %5;\n"                      \
+  " @py add.rn.f32 %2, %2, %6;\n"                      \
+  " @pz add.rn.f32 %3, %3, %7;\n"                      \
+  " @px add.s32 %0, %0, %8;\n"                         \
+  " @py add.s32 %0, %0, %9;\n"                         \
+  " @pz add.s32 %0, %0, %10;\n"
+
+template <bool SMEM>
+__device__ __forceinline__ void dda_burst(unsigned& pbit, float& tx, float& ty, float& tz, unsigned& walking,
+                                          float dtx, float dty, float dtz, int k0, int k1, int k2, unsigned thresh,
+                                          const uint32_t* gptr) {
+  if constexpr (SMEM) {
+    asm volatile(
+        "{\n"
+        " .reg .pred pw, px, py, pz, pn, q1, q2, pc;\n"
+        " .reg .u32 a, word, b, bal, cnt;\n"
+        " setp.ne.u32 pw, %4, 0;\n"
+        "LB_%=:\n"
+        ASSCPP_DDA_ITER(" ld.shared.u32 word, [a];\n")
+        ASSCPP_DDA_ITER(" ld.shared.u32 word, [a];\n")
+        " vote.sync.ballot.b32 bal, pw, 0xffffffff;\n"
+        " popc.b32 cnt, bal;\n"
+        " setp.ge.u32 pc, cnt, %11;\n"
+        " @pc bra.uni LB_%=;\n"
+        " selp.u32 %4, 1, 0, pw;\n"
+        "}\n"
+        : "+r"(pbit), "+f"(tx), "+f"(ty), "+f"(tz), "+r"(walking)
+        : "f"(dtx), "f"(dty), "f"(dtz), "r"(k0), "r"(k1), "r"(k2), "r"(thresh)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        " .reg .pred pw, px, py, pz, pn, q1, q2, pc;\n"
+        " .reg .u32 a, word, b, bal, cnt;\n"
+        " .reg .u64 ga;\n"
+        " setp.ne.u32 pw, %4, 0;\n"
+        "LB_%=:\n"
+        ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u32 word, [ga];\n")
+        ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u32 word, [ga];\n")
+        " vote.sync.ballot.b32 bal, pw, 0xffffffff;\n"
+        " popc.b32 cnt, bal;\n"
+        " setp.ge.u32 pc, cnt, %11;\n"
+        " @pc bra.uni LB_%=;\n"
+        " selp.u32 %4, 1, 0, pw;\n"
+        "}\n"
+        : "+r"(pbit), "+f"(tx), "+f"(ty), "+f"(tz), "+r"(walking)
+        : "f"(dtx), "f"(dty), "f"(dtz), "r"(k0), "r"(k1), "r"(k2), "r"(thresh), "l"(gptr)
+        : "memory");
+  }
+}
+
+template <bool SMEM>
+__device__ __forceinline__ void walk_rays(const EvalArgs& A, ViewShared& sh, const GridMem& gm, const uint4* ray_buf,
+                                          uint32_t* cand_list) {
+  const GridView& g = sh.g;
+  const int lane = threadIdx.x & 31;
+  const unsigned lt = (1u << lane) - 1;
+  const unsigned count = sh.ray_count;
+  const int P0 = g.P0, P01 = g.P01;
+  const int h0 = P0 >> 1, h01 = P01 >> 1, near_max = P01 + P0 + 1;
+  const unsigned bit_base = SMEM ? (gm.saddr << 3) : 0u;  // see dda_burst
+  unsigned pbit = bit_base;
+  int pt = 0, k0 = 0, k1 = 0, k2 = 0;
+  float tx = 0, ty = 0, tz = 0, dtx = 0, dty = 0, dtz = 0;
+  uint32_t u = 0, w_s01 = 0, w_s2t2 = 0, w_t01 = 0;
+  unsigned walking = 0, have = 0, drained = 0;  // have: the lane owns an unfinished ray (walking or parked)
+  unsigned long long steps = 0;
+  for (;;) {
+    // ---- service: resolve parked lanes, emit free rays, refill idle lanes (converged) ----------------
+    unsigned freed = 0;
+    if (have && !walking) {
+      // parked on a set bit: target, occupied cell, halo or sentinel
+      const int p = (int)(pbit - bit_base);
+      const int delta = p - pt;
+      // cells of the target's 3x3x3 neighbourhood (delta = a + b P0 + c P01, |a|,|b|,|c| <= 1) never occlude
+      // (quirk Q4: d^2 <= 3 < 4), whatever their occupancy: step over them
+      const int c = (delta > h01) - (delta < -h01);
+      const int rem = delta - c * P01;
+      const int b = (rem > h0) - (rem < -h0);
+      const int a = rem - b * P0;
+      const bool near27 = (abs(delta) <= near_max) & (abs(rem) <= P0 + 1) & (abs(a) <= 1);
+      bool go_on = near27 & (delta != 0);
+      if (!go_on) {
+        const int qs0 = w_s01 & 0xffff, qs1 = w_s01 >> 16, qs2 = w_s2t2 & 0xffff;
+        const int qt0 = w_t01 & 0xffff, qt1 = w_t01 >> 16, qt2 = w_s2t2 >> 16;
+        if (delta == 0) {                                                  // :551-552
+          steps += (unsigned)(abs(qt0 - qs0) + abs(qt1 - qs1) + abs(qt2 - qs2) + 1);
+          freed = 1;
+        } else {
+          const int q2 = fast_div(p, P01, g.mP01), rm = p - q2 * P01, q1 = fast_div(rm, P0, g.mP0), q0 = rm - q1 * P0;
+          const unsigned walked = (unsigned)(abs(q0 - qs0) + abs(q1 - qs1) + abs(q2 - qs2));
+          if (q0 == 0 || q0 == P0 - 1 || q1 == 0 || q1 == g.P1 - 1 || q2 == 0 || q2 == g.P2 - 1) {
+            steps += walked;                                               // left the expanded box (:538-540): result 0
+            freed = 1;
+          } else if (cell_occupied<SMEM>(g, gm, q0 - 2, q1 - 2, q2 - 2) &&
+                     is_occluder(g, q0 - 2, q1 - 2, q2 - 2, qt0 - 2, qt1 - 2, qt2 - 2)) {
+            steps += walked + 1;                                           // :561-562 result 1
+          } else {
+            go_on = true;
+          }
+        }
+      }
+      if (go_on) {
+        int pp = p;
+        dda_step(tx, ty, tz, pp, dtx, dty, dtz, k0, k1, k2);
+        pbit = (unsigned)pp + bit_base;
+        walking = 1;
+      } else {
+        have = 0;
+      }
+    }
+    const unsigned fb = __ballot_sync(0xffffffffu, freed != 0);
+    if (fb) {
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(&sh.vis_count, (unsigned)__popc(fb));
+      base = __shfl_sync(0xffffffffu, base, 0);
+      if (freed) cand_list[base + __popc(fb & lt)] = u;
+    }
+    if (!drained) {
+      const unsigned idle = __ballot_sync(0xffffffffu, have == 0);
+      if (idle) {
+        unsigned base = 0;
+        const unsigned want = (unsigned)__popc(idle);
+        if (lane == 0) base = atomicAdd(&sh.ray_next, want);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (!have) {
+          const unsigned at = base + __popc(idle & lt);
+          if (at < count) {
+            const uint4 ra = ray_buf[at];
+            const float4 rb = reinterpret_cast<const float4*>(ray_buf)[A.ray_cap + at];
+            const float4 rc = reinterpret_cast<const float4*>(ray_buf)[2 * A.ray_cap + at];
+            pbit = ra.x + bit_base; u = ra.y; w_s01 = ra.z; w_s2t2 = ra.w;
+            tx = rb.x; ty = rb.y; tz = rb.z; w_t01 = __float_as_uint(rb.w);
+            dtx = fabsf(rc.x); dty = fabsf(rc.y); dtz = fabsf(rc.z);
+            k0 = (__float_as_uint(rc.x) >> 31) ? -1 : 1;
+            k1 = (__float_as_uint(rc.y) >> 31) ? -P0 : P0;
+            k2 = (__float_as_uint(rc.z) >> 31) ? -P01 : P01;
+            pt = (int)(w_t01 & 0xffff) + (int)(w_t01 >> 16) * P0 + (int)(w_s2t2 >> 16) * P01;
+            walking = 1; have = 1;
+          }
+        }
+        if (base + want >= count) drained = 1;
+      }
+    }
+    if (!__any_sync(0xffffffffu, have != 0)) break;
+    // ---- burst: step until too few lanes are still walking -----------------------------------------
+    if (__any_sync(0xffffffffu, walking != 0))
+      dda_burst<SMEM>(pbit, tx, ty, tz, walking, dtx, dty, dtz, k0, k1, k2, drained ? 1u : (unsigned)A.walk_thresh,
+                      gm.gptr);
+  }
+  for (int o = 16; o; o >>= 1) steps += __shfl_xor_sync(0xffffffffu, steps, o);
+  if (lane == 0 && steps) atomicAdd(&sh.steps, steps);
+}
+
 __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   if (threadIdx.x < 24) sh.planes[threadIdx.x] = vd.planes[threadIdx.x];
   if (threadIdx.x < 3) {
@@ -673,18 +999,42 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     GridMem gm;
     const bool in_smem = build_grid(A, sh, smem_grid, glob_grid, vox_list, &gm);
     if (prof) t2 = clock64();
-    // P4a: one ray per occupied voxel; visible voxels are compacted into vis_list
-    if (in_smem) trace_rays<true>(A, sh, gm, vox_list, vis_list);
-    else trace_rays<false>(A, sh, gm, vox_list, vis_list);
+    // P4a: one ray per occupied voxel, prepared and walked in rounds of at most ray_cap rays; voxels whose ray
+    // comes back free are collected in vis_list
+    {
+      uint4* ray_buf = A.ray_buf + (int64_t)blockIdx.x * 3 * A.ray_cap;
+      const unsigned total = sh.list_count;
+      for (unsigned e0 = 0; e0 < total; e0 += (unsigned)A.ray_cap) {
+        const unsigned e1 = min(total, e0 + (unsigned)A.ray_cap);
+        if (e0) {
+          __syncthreads();
+          if (threadIdx.x == 0) { sh.ray_count = 0; sh.ray_next = 0; }
+          __syncthreads();
+        }
+        if (in_smem) setup_rays<true>(A, sh, gm, vox_list, e0, e1, ray_buf, vis_list);
+        else setup_rays<false>(A, sh, gm, vox_list, e0, e1, ray_buf, vis_list);
+        __syncthreads();
+        if (in_smem) walk_rays<true>(A, sh, gm, ray_buf, vis_list);
+        else walk_rays<false>(A, sh, gm, ray_buf, vis_list);
+      }
+    }
     __syncthreads();
     if (prof) t3 = clock64();
-    // P4b: survivors of the visible voxels -> counts, gains, hash
+    // P4b: second gate (occlusion_culling.cpp:338-342) per free voxel, then its survivors -> counts, gains, hash
     {
       unsigned vis = 0, gain_p = 0, gain_v = 0;
       unsigned long long vhash = 0;
       const unsigned nvis = sh.vis_count;
-      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x)
-        visit_voxel_points(A, sh, vis_list[e], 0, cov_scratch, vis, gain_p, gain_v, vhash);
+      const GridView& g = sh.g;
+      const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
+      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x) {
+        const uint32_t u = vis_list[e];
+        const int4 vx = m.vox[u];
+        const float tc[3] = {centre(g, 0, vx.x - g.min_b[0]), centre(g, 1, vx.y - g.min_b[1]),
+                             centre(g, 2, vx.z - g.min_b[2])};
+        if (!second_gate(g, pcd_o, tc)) { vis_list[e] = 0xffffffffu; continue; }
+        visit_voxel_points(A, sh, u, 0, cov_scratch, vis, gain_p, gain_v, vhash);
+      }
       vis = warp_sum(vis); gain_p = warp_sum(gain_p); gain_v = warp_sum(gain_v);
       for (int o = 16; o; o >>= 1) vhash += __shfl_xor_sync(0xffffffffu, vhash, o);
       if ((threadIdx.x & 31) == 0) {
@@ -715,7 +1065,7 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
       unsigned long long d3 = 0;
       const unsigned nvis = sh.vis_count;
       for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x)
-        visit_voxel_points(A, sh, vis_list[e], 1, cov_scratch, d0, d1, d2, d3);
+        if (vis_list[e] != 0xffffffffu) visit_voxel_points(A, sh, vis_list[e], 1, cov_scratch, d0, d1, d2, d3);
     }
     if (threadIdx.x == 0) write_result(A, sh, v);
     if (prof) {
