@@ -376,8 +376,8 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = dev_alloc(c, &c->d_vox_list, c->list_cap * c->ctas))) return fail(rc);
   c->vis_cap = m.n_vox + 32;
   if ((rc = dev_alloc(c, &c->d_vis_list, c->vis_cap * c->ctas))) return fail(rc);
-  c->ray_cap = std::min<int64_t>(65536, ((m.n_vox + 31) / 32) * 32 + 32);  // rays prepared per setup/walk round
-  if ((rc = dev_alloc(c, &c->d_ray_buf, 3 * c->ray_cap * c->ctas))) return fail(rc);
+  c->ray_cap = ray_queue_cap();  // records per warp queue; 32 warps per CTA
+  if ((rc = dev_alloc(c, &c->d_ray_buf, 3 * c->ray_cap * 32 * c->ctas))) return fail(rc);
   if (const char* wt = getenv("ASSCPP_WALK_THRESH")) c->walk_thresh = std::max(1, std::min(32, atoi(wt)));
   if ((rc = dev_alloc(c, &c->d_grid_scratch, c->grid_cap_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_cov_scratch, c->cov_words * c->ctas))) return fail(rc);

@@ -613,13 +613,15 @@ __device__ __forceinline__ void trace_rays(const EvalArgs& A, ViewShared& sh, co
 // ------------------------------------------------------------------------------------------------
 // P4a, fast path: the same rays as trace_rays, reorganised so that lanes stay busy.
 //
-//   setup_rays   one thread per occupied voxel, fully converged: direction, slab test, start cell, t_max /
+//   setup_ray    one thread per occupied voxel, fully converged (a warp prepares kRayBatch list entries at a time): direction, slab test, start cell, t_max /
 //                t_delta (:99-128, :410-519) and the FIRST loop iteration (:538-579) on the start cell, whose
 //                coordinates are still at hand (it is the cell that most often lies in the halo layer).
 //                Rays that are already decided leave here (failed / free / occluded); the others are written
-//                as 48-byte records to the per-CTA ray buffer (L2-resident).
-//   walk_rays    warps pull records from the buffer; a lane that finishes its ray takes the next record instead
-//                of idling until the slowest ray of a 32-ray tile is done.  The step loop holds nothing but
+//                as 48-byte records to the warp's private queue (7.5 KB per warp, L2-resident).
+//   walk         lanes pull records from the queue; a lane that finishes its ray takes the next record instead
+//                of idling until the slowest ray of a 32-ray tile is done.  When the queue runs dry the rays still
+//                in flight are checkpointed as records (the record format is resumable) and the next batch is
+//                prepared, so the setup code never runs with walk state live in registers.  The step loop holds nothing but
 //                the bit test and the t_max update: a set bit is first classified on the linear index
 //                difference to the target (the 3x3x3 neighbourhood of the target can never occlude, quirk Q4:
 //                d^2 <= 3 < 4) and everything else (target reached, occluder, halo alias, sentinel) is parked
@@ -668,100 +670,61 @@ __device__ __forceinline__ bool is_occluder(const GridView& g, int c0, int c1, i
   return sum > g.thr_sq;                                             // :561
 }
 
+// Record planes of one warp's private queue
+struct RayQueue {
+  uint4* a;
+  float4* b;
+  float4* c;
+};
+
+// Ray setup for one list entry (u = voxel id or 0xffffffff).  Returns 0 nothing to emit (duplicate entry, failed
+// or occluded by its start cell), 1 free (candidate for the second gate), 2 walk (record in ra / rb / rc).
 template <bool SMEM>
-__device__ __forceinline__ void setup_rays(const EvalArgs& A, ViewShared& sh, const GridMem& gm,
-                                           const uint32_t* vox_list, unsigned e_begin, unsigned e_end, uint4* ray_buf,
-                                           uint32_t* cand_list) {
-  const ModelDev& m = A.m;
-  const GridView& g = sh.g;
-  const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-  const unsigned lt = (1u << lane) - 1;
-  unsigned steps = 0, fails = 0;
-  for (unsigned e0 = e_begin + warp * 32; e0 < e_end; e0 += nwarps * 32) {
-    const unsigned e = e0 + lane;
-    const uint32_t u = e < e_end ? vox_list[e] : 0xffffffffu;
-    int kind = 0;  // 0 nothing to emit, 1 free (candidate for the second gate), 2 walk
-    uint4 ra = make_uint4(0, 0, 0, 0);
-    float4 rb = make_float4(0, 0, 0, 0), rc = make_float4(0, 0, 0, 0);
-    if (u != 0xffffffffu) {
-      const int4 vx = m.vox[u];
-      const int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
-      const float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
-      float d[3];
-      direction(tc, origin, d);                 // :111-113
-      const float tmin = ray_box(g, origin, d); // :116
-      if (tmin == -1.0f) {
-        ++fails;                                // :118-122, quirk Q5
-      } else {
-        float t_max[3], t_delta[3];
-        int r[3], step[3];
+__device__ __forceinline__ int setup_ray(const ModelDev& m, const GridView& g, const GridMem& gm, const float origin[3],
+                                         uint32_t u, uint4& ra, float4& rb, float4& rc, unsigned& steps,
+                                         unsigned& fails) {
+  if (u == 0xffffffffu) return 0;
+  const int4 vx = m.vox[u];
+  const int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
+  const float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
+  float d[3];
+  direction(tc, origin, d);                  // :111-113
+  const float tmin = ray_box(g, origin, d);  // :116
+  if (tmin == -1.0f) { ++fails; return 0; }  // :118-122, quirk Q5
+  float t_max[3], t_delta[3];
+  int r[3], step[3];
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-          float start = fadd(origin[c], fmul(tmin, d[c]));                   // :422
-          int ijk = (int)floorf(fadd(fmul(start, g.inv), 0.5f));             // :425
-          r[c] = ijk - g.min_b[c];
-          float vm = centre(g, c, r[c]);                                     // :432
-          if (d[c] >= 0) { vm = fadd(vm, g.half); step[c] = 1; }             // :436-465
-          else           { vm = fsub(vm, g.half); step[c] = -1; }
-          t_max[c] = fadd(tmin, fdiv(fsub(vm, start), d[c]));                // :513-515
-          t_delta[c] = fdiv(g.leaf, fabsf(d[c]));                            // :517-519
-        }
-        if (!((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
-              (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1))) {
-          kind = 1;                             // :538-540 false on entry: result 0, no iteration
-        } else {
-          // first iteration; rays that go on are counted in walk_rays from their start cell
-          if (r[0] == rt[0] && r[1] == rt[1] && r[2] == rt[2]) {
-            kind = 1;                           // :551-552
-            ++steps;
-          } else if (cell_occupied<SMEM>(g, gm, r[0], r[1], r[2]) &&
-                     is_occluder(g, r[0], r[1], r[2], rt[0], rt[1], rt[2])) {
-            kind = 0;                           // occluded by its start cell
-            ++steps;
-          } else {
-            kind = 2;
-            const int P0 = g.P0, P01 = g.P01;
-            int p = (r[0] + 2) + (r[1] + 2) * P0 + (r[2] + 2) * P01;
-            float tx = t_max[0], ty = t_max[1], tz = t_max[2];
-            dda_step(tx, ty, tz, p, t_delta[0], t_delta[1], t_delta[2], step[0], step[1] * P0, step[2] * P01);
-            ra = make_uint4((unsigned)p, u, (unsigned)(r[0] + 2) | ((unsigned)(r[1] + 2) << 16),
-                            (unsigned)(r[2] + 2) | ((unsigned)(rt[2] + 2) << 16));
-            rb = make_float4(tx, ty, tz, __uint_as_float((unsigned)(rt[0] + 2) | ((unsigned)(rt[1] + 2) << 16)));
-            rc = make_float4(__uint_as_float(__float_as_uint(t_delta[0]) & 0x7fffffffu | (step[0] < 0 ? 0x80000000u : 0u)),
-                             __uint_as_float(__float_as_uint(t_delta[1]) & 0x7fffffffu | (step[1] < 0 ? 0x80000000u : 0u)),
-                             __uint_as_float(__float_as_uint(t_delta[2]) & 0x7fffffffu | (step[2] < 0 ? 0x80000000u : 0u)),
-                             0.0f);
-          }
-        }
-      }
-    }
-    const unsigned cb = __ballot_sync(0xffffffffu, kind == 1);
-    if (cb) {
-      unsigned base = 0;
-      if (lane == 0) base = atomicAdd(&sh.vis_count, (unsigned)__popc(cb));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (kind == 1) cand_list[base + __popc(cb & lt)] = u;
-    }
-    const unsigned wb = __ballot_sync(0xffffffffu, kind == 2);
-    if (wb) {
-      unsigned base = 0;
-      if (lane == 0) base = atomicAdd(&sh.ray_count, (unsigned)__popc(wb));
-      base = __shfl_sync(0xffffffffu, base, 0);
-      if (kind == 2) {
-        const unsigned at = base + __popc(wb & lt);
-        ray_buf[at] = ra;
-        reinterpret_cast<float4*>(ray_buf)[A.ray_cap + at] = rb;
-        reinterpret_cast<float4*>(ray_buf)[2 * A.ray_cap + at] = rc;
-      }
-    }
+  for (int c = 0; c < 3; ++c) {
+    float start = fadd(origin[c], fmul(tmin, d[c]));                   // :422
+    int ijk = (int)floorf(fadd(fmul(start, g.inv), 0.5f));             // :425
+    r[c] = ijk - g.min_b[c];
+    float vm = centre(g, c, r[c]);                                     // :432
+    if (d[c] >= 0) { vm = fadd(vm, g.half); step[c] = 1; }             // :436-465
+    else           { vm = fsub(vm, g.half); step[c] = -1; }
+    t_max[c] = fadd(tmin, fdiv(fsub(vm, start), d[c]));                // :513-515
+    t_delta[c] = fdiv(g.leaf, fabsf(d[c]));                            // :517-519
   }
-  fails = warp_sum(fails);
-  steps = warp_sum(steps);
-  if (lane == 0) {
-    if (fails) atomicAdd(&sh.carry, fails);
-    if (steps) atomicAdd(&sh.steps, (unsigned long long)steps);
+  if (!((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
+        (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1)))
+    return 1;                                // :538-540 false on entry: result 0, no iteration
+  // first iteration; rays that go on are counted in the walk from their start cell
+  if (r[0] == rt[0] && r[1] == rt[1] && r[2] == rt[2]) { ++steps; return 1; }  // :551-552
+  if (cell_occupied<SMEM>(g, gm, r[0], r[1], r[2]) && is_occluder(g, r[0], r[1], r[2], rt[0], rt[1], rt[2])) {
+    ++steps;                                 // occluded by its start cell
+    return 0;
   }
+  const int P0 = g.P0, P01 = g.P01;
+  int p = (r[0] + 2) + (r[1] + 2) * P0 + (r[2] + 2) * P01;
+  float tx = t_max[0], ty = t_max[1], tz = t_max[2];
+  dda_step(tx, ty, tz, p, t_delta[0], t_delta[1], t_delta[2], step[0], step[1] * P0, step[2] * P01);
+  ra = make_uint4((unsigned)p, u, (unsigned)(r[0] + 2) | ((unsigned)(r[1] + 2) << 16),
+                  (unsigned)(r[2] + 2) | ((unsigned)(rt[2] + 2) << 16));
+  rb = make_float4(tx, ty, tz, __uint_as_float((unsigned)(rt[0] + 2) | ((unsigned)(rt[1] + 2) << 16)));
+  rc = make_float4(__uint_as_float(__float_as_uint(t_delta[0]) & 0x7fffffffu | (step[0] < 0 ? 0x80000000u : 0u)),
+                   __uint_as_float(__float_as_uint(t_delta[1]) & 0x7fffffffu | (step[1] < 0 ? 0x80000000u : 0u)),
+                   __uint_as_float(__float_as_uint(t_delta[2]) & 0x7fffffffu | (step[2] < 0 ? 0x80000000u : 0u)),
+                   0.0f);
+  return 2;
 }
 
 // The burst loop in PTX: two DDA iterations per lane, then a warp vote; leaves when fewer than `thresh`
@@ -833,21 +796,31 @@ __device__ __forceinline__ void dda_burst(unsigned& pbit, float& tx, float& ty, 
   }
 }
 
+constexpr int kRayBatch = 128;              // list entries a warp claims and prepares at a time
+constexpr int kRayQueueCap = kRayBatch + 32;  // + at most 32 checkpointed rays
+
+// One warp: alternate between preparing a batch of rays into its private queue and walking them.
 template <bool SMEM>
-__device__ __forceinline__ void walk_rays(const EvalArgs& A, ViewShared& sh, const GridMem& gm, const uint4* ray_buf,
-                                          uint32_t* cand_list) {
+__device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& sh, const GridMem& gm,
+                                                const uint32_t* vox_list, RayQueue q, uint32_t* cand_list) {
+  const ModelDev& m = A.m;
   const GridView& g = sh.g;
+  const float origin[3] = {sh.origin[0], sh.origin[1], sh.origin[2]};
   const int lane = threadIdx.x & 31;
   const unsigned lt = (1u << lane) - 1;
-  const unsigned count = sh.ray_count;
+  const unsigned total = sh.list_count;
   const int P0 = g.P0, P01 = g.P01;
   const int h0 = P0 >> 1, h01 = P01 >> 1, near_max = P01 + P0 + 1;
   const unsigned bit_base = SMEM ? (gm.saddr << 3) : 0u;  // see dda_burst
+  const unsigned T = (unsigned)A.walk_thresh;
   unsigned pbit = bit_base;
   int pt = 0, k0 = 0, k1 = 0, k2 = 0;
   float tx = 0, ty = 0, tz = 0, dtx = 0, dty = 0, dtz = 0;
   uint32_t u = 0, w_s01 = 0, w_s2t2 = 0, w_t01 = 0;
-  unsigned walking = 0, have = 0, drained = 0;  // have: the lane owns an unfinished ray (walking or parked)
+  unsigned walking = 0, have = 0;  // have: the lane owns an unfinished ray (walking or parked)
+  unsigned qhead = 0, qtail = 0;   // private queue, warp-uniform
+  bool more = true;                // list entries not yet claimed by any warp (warp-uniform)
+  unsigned steps_lo = 0, fails = 0;
   unsigned long long steps = 0;
   for (;;) {
     // ---- service: resolve parked lanes, emit free rays, refill idle lanes (converged) ----------------
@@ -868,17 +841,17 @@ __device__ __forceinline__ void walk_rays(const EvalArgs& A, ViewShared& sh, con
         const int qs0 = w_s01 & 0xffff, qs1 = w_s01 >> 16, qs2 = w_s2t2 & 0xffff;
         const int qt0 = w_t01 & 0xffff, qt1 = w_t01 >> 16, qt2 = w_s2t2 >> 16;
         if (delta == 0) {                                                  // :551-552
-          steps += (unsigned)(abs(qt0 - qs0) + abs(qt1 - qs1) + abs(qt2 - qs2) + 1);
+          steps_lo += (unsigned)(abs(qt0 - qs0) + abs(qt1 - qs1) + abs(qt2 - qs2) + 1);
           freed = 1;
         } else {
           const int q2 = fast_div(p, P01, g.mP01), rm = p - q2 * P01, q1 = fast_div(rm, P0, g.mP0), q0 = rm - q1 * P0;
           const unsigned walked = (unsigned)(abs(q0 - qs0) + abs(q1 - qs1) + abs(q2 - qs2));
           if (q0 == 0 || q0 == P0 - 1 || q1 == 0 || q1 == g.P1 - 1 || q2 == 0 || q2 == g.P2 - 1) {
-            steps += walked;                                               // left the expanded box (:538-540): result 0
+            steps_lo += walked;                                            // left the expanded box (:538-540): result 0
             freed = 1;
           } else if (cell_occupied<SMEM>(g, gm, q0 - 2, q1 - 2, q2 - 2) &&
                      is_occluder(g, q0 - 2, q1 - 2, q2 - 2, qt0 - 2, qt1 - 2, qt2 - 2)) {
-            steps += walked + 1;                                           // :561-562 result 1
+            steps_lo += walked + 1;                                        // :561-562 result 1
           } else {
             go_on = true;
           }
@@ -900,40 +873,89 @@ __device__ __forceinline__ void walk_rays(const EvalArgs& A, ViewShared& sh, con
       base = __shfl_sync(0xffffffffu, base, 0);
       if (freed) cand_list[base + __popc(fb & lt)] = u;
     }
-    if (!drained) {
-      const unsigned idle = __ballot_sync(0xffffffffu, have == 0);
-      if (idle) {
-        unsigned base = 0;
-        const unsigned want = (unsigned)__popc(idle);
-        if (lane == 0) base = atomicAdd(&sh.ray_next, want);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (!have) {
-          const unsigned at = base + __popc(idle & lt);
-          if (at < count) {
-            const uint4 ra = ray_buf[at];
-            const float4 rb = reinterpret_cast<const float4*>(ray_buf)[A.ray_cap + at];
-            const float4 rc = reinterpret_cast<const float4*>(ray_buf)[2 * A.ray_cap + at];
-            pbit = ra.x + bit_base; u = ra.y; w_s01 = ra.z; w_s2t2 = ra.w;
-            tx = rb.x; ty = rb.y; tz = rb.z; w_t01 = __float_as_uint(rb.w);
-            dtx = fabsf(rc.x); dty = fabsf(rc.y); dtz = fabsf(rc.z);
-            k0 = (__float_as_uint(rc.x) >> 31) ? -1 : 1;
-            k1 = (__float_as_uint(rc.y) >> 31) ? -P0 : P0;
-            k2 = (__float_as_uint(rc.z) >> 31) ? -P01 : P01;
-            pt = (int)(w_t01 & 0xffff) + (int)(w_t01 >> 16) * P0 + (int)(w_s2t2 >> 16) * P01;
-            walking = 1; have = 1;
-          }
+    unsigned idle = __ballot_sync(0xffffffffu, have == 0);
+    if (idle && qhead < qtail) {
+      if (!have) {
+        const unsigned at = qhead + __popc(idle & lt);
+        if (at < qtail) {
+          const uint4 ra = __ldcg(q.a + at);
+          const float4 rb = __ldcg(q.b + at);
+          const float4 rc = __ldcg(q.c + at);
+          pbit = ra.x + bit_base; u = ra.y; w_s01 = ra.z; w_s2t2 = ra.w;
+          tx = rb.x; ty = rb.y; tz = rb.z; w_t01 = __float_as_uint(rb.w);
+          dtx = fabsf(rc.x); dty = fabsf(rc.y); dtz = fabsf(rc.z);
+          k0 = (__float_as_uint(rc.x) >> 31) ? -1 : 1;
+          k1 = (__float_as_uint(rc.y) >> 31) ? -P0 : P0;
+          k2 = (__float_as_uint(rc.z) >> 31) ? -P01 : P01;
+          pt = (int)(w_t01 & 0xffff) + (int)(w_t01 >> 16) * P0 + (int)(w_s2t2 >> 16) * P01;
+          walking = 1; have = 1;
         }
-        if (base + want >= count) drained = 1;
       }
+      qhead = min(qtail, qhead + (unsigned)__popc(idle));
+      idle = __ballot_sync(0xffffffffu, have == 0);
     }
-    if (!__any_sync(0xffffffffu, have != 0)) break;
+    const unsigned nhave = 32u - (unsigned)__popc(idle);
+    if (qhead == qtail && more && nhave < T) {
+      // queue empty and too few rays in flight: checkpoint them as records, then prepare the next batch
+      const unsigned hb = ~idle;
+      if (have) {
+        const unsigned at = (unsigned)__popc(hb & lt);
+        __stcg(q.a + at, make_uint4(pbit - bit_base, u, w_s01, w_s2t2));
+        __stcg(q.b + at, make_float4(tx, ty, tz, __uint_as_float(w_t01)));
+        __stcg(q.c + at, make_float4(__uint_as_float(__float_as_uint(dtx) | (k0 < 0 ? 0x80000000u : 0u)),
+                                     __uint_as_float(__float_as_uint(dty) | (k1 < 0 ? 0x80000000u : 0u)),
+                                     __uint_as_float(__float_as_uint(dtz) | (k2 < 0 ? 0x80000000u : 0u)), 0.0f));
+      }
+      qhead = 0;
+      qtail = nhave;
+      have = 0; walking = 0;  // nothing of the walk state is live across the setup code below
+      pbit = bit_base; pt = 0; k0 = k1 = k2 = 0; tx = ty = tz = dtx = dty = dtz = 0; u = w_s01 = w_s2t2 = w_t01 = 0;
+      unsigned e0 = 0;
+      if (lane == 0) e0 = atomicAdd(&sh.ray_next, (unsigned)kRayBatch);
+      e0 = __shfl_sync(0xffffffffu, e0, 0);
+      if (e0 >= total) {
+        more = false;
+      } else {
+        const unsigned e1 = min(total, e0 + (unsigned)kRayBatch);
+        for (unsigned eb = e0; eb < e1; eb += 32) {
+          const unsigned e = eb + lane;
+          const uint32_t uu = e < e1 ? vox_list[e] : 0xffffffffu;
+          uint4 ra = make_uint4(0, 0, 0, 0);
+          float4 rb = make_float4(0, 0, 0, 0), rc = make_float4(0, 0, 0, 0);
+          const int kind = setup_ray<SMEM>(m, g, gm, origin, uu, ra, rb, rc, steps_lo, fails);
+          const unsigned cb = __ballot_sync(0xffffffffu, kind == 1);
+          if (cb) {
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(&sh.vis_count, (unsigned)__popc(cb));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (kind == 1) cand_list[base + __popc(cb & lt)] = uu;
+          }
+          const unsigned wb = __ballot_sync(0xffffffffu, kind == 2);
+          if (kind == 2) {
+            const unsigned at = qtail + __popc(wb & lt);
+            __stcg(q.a + at, ra);
+            __stcg(q.b + at, rb);
+            __stcg(q.c + at, rc);
+          }
+          qtail += (unsigned)__popc(wb);
+        }
+      }
+      __syncwarp();
+      steps += steps_lo; steps_lo = 0;
+      continue;
+    }
+    if (nhave == 0) break;  // nothing in flight, queue empty, no entries left
     // ---- burst: step until too few lanes are still walking -----------------------------------------
     if (__any_sync(0xffffffffu, walking != 0))
-      dda_burst<SMEM>(pbit, tx, ty, tz, walking, dtx, dty, dtz, k0, k1, k2, drained ? 1u : (unsigned)A.walk_thresh,
-                      gm.gptr);
+      dda_burst<SMEM>(pbit, tx, ty, tz, walking, dtx, dty, dtz, k0, k1, k2, (qhead == qtail && !more) ? 1u : T, gm.gptr);
   }
+  steps += steps_lo;
+  fails = warp_sum(fails);
   for (int o = 16; o; o >>= 1) steps += __shfl_xor_sync(0xffffffffu, steps, o);
-  if (lane == 0 && steps) atomicAdd(&sh.steps, steps);
+  if (lane == 0) {
+    if (fails) atomicAdd(&sh.carry, fails);
+    if (steps) atomicAdd(&sh.steps, steps);
+  }
 }
 
 __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
@@ -999,24 +1021,16 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     GridMem gm;
     const bool in_smem = build_grid(A, sh, smem_grid, glob_grid, vox_list, &gm);
     if (prof) t2 = clock64();
-    // P4a: one ray per occupied voxel, prepared and walked in rounds of at most ray_cap rays; voxels whose ray
-    // comes back free are collected in vis_list
+    // P4a: one ray per occupied voxel; every warp prepares batches of rays into its private queue and walks
+    // them; voxels whose ray comes back free are collected in vis_list
     {
-      uint4* ray_buf = A.ray_buf + (int64_t)blockIdx.x * 3 * A.ray_cap;
-      const unsigned total = sh.list_count;
-      for (unsigned e0 = 0; e0 < total; e0 += (unsigned)A.ray_cap) {
-        const unsigned e1 = min(total, e0 + (unsigned)A.ray_cap);
-        if (e0) {
-          __syncthreads();
-          if (threadIdx.x == 0) { sh.ray_count = 0; sh.ray_next = 0; }
-          __syncthreads();
-        }
-        if (in_smem) setup_rays<true>(A, sh, gm, vox_list, e0, e1, ray_buf, vis_list);
-        else setup_rays<false>(A, sh, gm, vox_list, e0, e1, ray_buf, vis_list);
-        __syncthreads();
-        if (in_smem) walk_rays<true>(A, sh, gm, ray_buf, vis_list);
-        else walk_rays<false>(A, sh, gm, ray_buf, vis_list);
-      }
+      uint4* qb = A.ray_buf + ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 3 * kRayQueueCap;
+      RayQueue q;
+      q.a = qb;
+      q.b = reinterpret_cast<float4*>(qb + kRayQueueCap);
+      q.c = reinterpret_cast<float4*>(qb + 2 * kRayQueueCap);
+      if (in_smem) trace_rays_fast<true>(A, sh, gm, vox_list, q, vis_list);
+      else trace_rays_fast<false>(A, sh, gm, vox_list, q, vis_list);
     }
     __syncthreads();
     if (prof) t3 = clock64();
@@ -1250,6 +1264,7 @@ __global__ void fill_bytes_kernel(uint8_t* p, int64_t n, uint8_t v) {
 // host-side launchers
 // ------------------------------------------------------------------------------------------------
 size_t eval_smem_bytes(uint32_t grid_words) { return ((sizeof(ViewShared) + 15) & ~size_t(15)) + (size_t)grid_words * 4; }
+int ray_queue_cap() { return kRayQueueCap; }
 size_t eval_smem_header_bytes() { return ((sizeof(ViewShared) + 15) & ~size_t(15)); }
 
 cudaError_t configure_kernels(size_t smem_bytes) {

@@ -8,6 +8,7 @@ namespace asscpp {
 
 size_t eval_smem_bytes(uint32_t grid_words);
 size_t eval_smem_header_bytes();
+int ray_queue_cap();
 cudaError_t configure_kernels(size_t smem_bytes);
 
 void launch_planes(const double* d_poses, int64_t nviews, const FrustumConst& fc, ViewDev* views, cudaStream_t s);
