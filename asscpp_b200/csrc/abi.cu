@@ -74,8 +74,10 @@ struct AsscppCtx {
   // sizes
   int64_t pts_words = 0, vox_words = 0;  // uint32 words, even counts
   int ctas = 0, ordered_ctas = 8;
+  int cta_threads = 1024;   // eval_views_kernel: 1024 -> one CTA per SM, 512 -> two (half the shared-memory grid each)
+  size_t eval_smem_bytes_ = 0;
   size_t smem_bytes = 0;
-  uint32_t smem_grid_words = 0;
+  uint32_t smem_grid_words = 0, eval_grid_words = 0;
   int64_t chunk_cap = 0, list_cap = 0, grid_cap_words = 0, cov_words = 0;
   uint2* d_chunk_list = nullptr;
   uint32_t *d_vox_list = nullptr, *d_vis_list = nullptr, *d_grid_scratch = nullptr, *d_cov_scratch = nullptr;
@@ -243,7 +245,9 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
     evp = &c->kernel_events[c->kernel_events_used++];
     CU(c, cudaEventRecord(evp->first, c->stream));
   }
-  launch_eval(a, ctas, c->smem_bytes, c->stream);
+  a.smem_grid_words = c->eval_grid_words;
+  launch_eval(a, ctas, c->cta_threads, c->eval_smem_bytes_, c->stream);
+  a.smem_grid_words = c->smem_grid_words;
   if (evp) CU(c, cudaEventRecord(evp->second, c->stream));
   launch_ordered(a, c->ordered_ctas, c->smem_bytes, c->stream);
   c->launches += 3;
@@ -340,6 +344,7 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = upload(c, &m.pt_cov, h.pt_cov))) return fail(rc);
   if ((rc = upload(c, (const Float4**)&m.chunk_lo, h.chunk_lo))) return fail(rc);
   if ((rc = upload(c, (const Float4**)&m.chunk_hi, h.chunk_hi))) return fail(rc);
+  if ((rc = upload(c, &m.chunk_vox, h.chunk_vox))) return fail(rc);
   if ((rc = upload(c, (const Float4**)&m.super_lo, h.super_lo))) return fail(rc);
   if ((rc = upload(c, (const Float4**)&m.super_hi, h.super_hi))) return fail(rc);
   {
@@ -354,11 +359,27 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if (c->vox_words == 0) c->vox_words = 2;
 
   // ---- launch geometry + scratch ----------------------------------------------------------------
-  c->ctas = c->sm_count;
+  if (const char* ct = getenv("ASSCPP_CTA_THREADS")) {
+    int v = atoi(ct);
+    if (v == 256 || v == 512 || v == 1024) c->cta_threads = v;
+  }
+  const int per_sm = 1024 / c->cta_threads;
+  c->ctas = c->sm_count * per_sm;
   size_t hdr = eval_smem_header_bytes();
   size_t avail = (size_t)optin > hdr + 64 ? (size_t)optin - hdr - 64 : 0;
   c->smem_grid_words = (uint32_t)(avail / 4);
-  c->smem_bytes = eval_smem_bytes(c->smem_grid_words);
+  c->smem_bytes = eval_smem_bytes(c->smem_grid_words);  // ordered_views_kernel (always 1024 threads)
+  {
+    // per-CTA share of the SM's shared memory (1 KB per CTA is reserved by the system)
+    size_t sm_total = 0;
+    int v = 0;
+    cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device);
+    sm_total = (size_t)v;
+    size_t share = per_sm == 1 ? (size_t)optin : std::min<size_t>((size_t)optin, sm_total / per_sm - 1024);
+    size_t av = share > hdr + 64 ? share - hdr - 64 : 0;
+    c->eval_grid_words = (uint32_t)(av / 4);
+    c->eval_smem_bytes_ = eval_smem_bytes(c->eval_grid_words);
+  }
   if ((e = configure_kernels(c->smem_bytes)) != cudaSuccess) { c->err = cudaGetErrorString(e); return fail(ASSCPP_ECUDA); }
   double ext = frustum_max_extent(*params);
   double cells_cap = 1;

@@ -28,10 +28,11 @@ struct ModelDev {
   const int32_t* orig;  // [n] original index of sorted position
   const int32_t* pos_of;  // [n] sorted position of original index
   const int4* vox;      // [n_vox+1] {i, j, k, first point}; sentinel holds n
-  const int32_t* vox_cov;  // [n_vox] coverage id of the voxel when cov lattice == occlusion lattice
+  const int32_t* vox_cov;  // [n_vox] coverage id shared by all points of the voxel, -1 if they straddle coverage cells
   const int32_t* pt_cov;   // [n] coverage id per sorted position
   const float4* chunk_lo;  // [n_chunks] aabb min + first point (bits)
   const float4* chunk_hi;  // [n_chunks] aabb max + end point (bits)
+  const int32_t* chunk_vox;  // [n_chunks+1] first voxel of the chunk
   const float4* super_lo;  // [n_super]
   const float4* super_hi;  // [n_super]
   float leaf, inv_leaf, half_leaf;
@@ -83,6 +84,8 @@ struct EvalArgs {
   unsigned long long* phase_cycles;  // optional profiling counters (nullptr: off)
 };
 
+constexpr uint32_t kVoxInside = 0x80000000u;  // vox_list flag: every point of the voxel passes the frustum test
+constexpr uint32_t kVoxMask = 0x7fffffffu;
 constexpr uint32_t kVsError = 0x80000000u;  // internal consistency failure (scratch overflow)
 
 }  // namespace asscpp

@@ -66,6 +66,21 @@ __device__ __forceinline__ bool box_outside(const float* pl, float lx, float ly,
   return false;
 }
 
+// Conservative bucket accept: true only if every point of the box passes the exact test of every plane (same
+// margin argument as box_outside, on the maximum of the plane function over the box).
+__device__ __forceinline__ bool box_inside(const float* pl, float lx, float ly, float lz, float hx, float hy,
+                                           float hz) {
+#pragma unroll
+  for (int k = 0; k < 6; ++k) {
+    float a = pl[4 * k], b = pl[4 * k + 1], c = pl[4 * k + 2], w = pl[4 * k + 3];
+    float U = (a >= 0 ? a * hx : a * lx) + (b >= 0 ? b * hy : b * ly) + (c >= 0 ? c * hz : c * lz) + w;
+    float A = fabsf(a) * fmaxf(fabsf(lx), fabsf(hx)) + fabsf(b) * fmaxf(fabsf(ly), fabsf(hy)) +
+              fabsf(c) * fmaxf(fabsf(lz), fabsf(hz)) + fabsf(w);
+    if (!(U < -(1e-6f * A + 1e-30f))) return false;
+  }
+  return true;
+}
+
 // ------------------------------------------------------------------------------------------------
 // planes_kernel: one thread per pose.  Double part = <tf Matrix3x3::setRotation>; float part =
 // frustum_culling.cpp:97-141 with the operation order of SURVEY.md A.2.
@@ -338,7 +353,13 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
           unsigned base = 0;
           if (lane == 0) base = atomicAdd(&sh.chunk_count, (unsigned)__popc(cb));
           base = __shfl_sync(0xffffffffu, base, 0);
-          if (ck) chunk_list[base + __popc(cb & ((1u << lane) - 1))] = make_uint2(__float_as_uint(lo.w), __float_as_uint(hi.w));
+          if (ck) {
+            // chunks wholly inside the frustum are passed on as a voxel range: their points are never read
+            const bool in = box_inside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+            chunk_list[base + __popc(cb & ((1u << lane) - 1))] =
+                in ? make_uint2((uint32_t)m.chunk_vox[c] | kVoxInside, (uint32_t)m.chunk_vox[c + 1])
+                   : make_uint2(__float_as_uint(lo.w), __float_as_uint(hi.w));
+          }
         }
       }
     }
@@ -347,12 +368,37 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
   // P2: exact test, 32 points per warp step
   const int64_t nwork = brute ? m.n_chunks : (int64_t)sh.chunk_count;
   int bmin[3] = {INT_MAX, INT_MAX, INT_MAX}, bmax[3] = {INT_MIN, INT_MIN, INT_MIN};
-  unsigned surv = 0;
+  unsigned surv = 0, surv_in = 0;
   unsigned long long shash = 0;
   for (int64_t w = warp; w < nwork; w += nwarps) {
     uint32_t pb, pe;
     if (brute) { pb = __float_as_uint(m.chunk_lo[w].w); pe = __float_as_uint(m.chunk_hi[w].w); }
     else { uint2 r = chunk_list[w]; pb = r.x; pe = r.y; }
+    if (pb & kVoxInside) {
+      // voxel range [pb, pe) of a chunk inside the frustum: one lane per voxel, every point survives
+      for (uint32_t u0 = pb & kVoxMask; u0 < pe; u0 += 32) {
+        const uint32_t u = u0 + lane;
+        const bool on = u < pe;
+        if (on) {
+          const int4 vx = m.vox[u];
+          const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
+          surv_in += q1 - q0;
+          if (want_hash)
+            for (uint32_t q = q0; q < q1; ++q) shash += mix64((uint64_t)(uint32_t)m.orig[q]);
+          bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
+          bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
+        }
+        const unsigned ob = __ballot_sync(0xffffffffu, on);
+        unsigned slot = 0;
+        if (lane == 0) slot = atomicAdd(&sh.list_count, (unsigned)__popc(ob));
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (on) {
+          const unsigned at = slot + lane;
+          if (at < A.list_cap) vox_list[at] = u | kVoxInside;
+        }
+      }
+      continue;
+    }
     for (uint32_t base0 = pb; base0 < pe; base0 += 128) {
       // four independent 512-byte loads in flight per warp before any is consumed (latency, not bandwidth,
       // bounds this phase: a chunk holds at most kChunkMaxPoints = 128 points unless it is one big voxel)
@@ -403,7 +449,8 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
     int lo = __reduce_min_sync(0xffffffffu, bmin[c]), hi = __reduce_max_sync(0xffffffffu, bmax[c]);
     if (lane == 0 && lo <= hi) { atomicMin(&sh.bb_min[c], lo); atomicMax(&sh.bb_max[c], hi); }
   }
-  if (lane == 0 && surv) atomicAdd(&sh.survivors, surv);
+  surv_in = warp_sum(surv_in);
+  if (lane == 0 && (surv | surv_in)) atomicAdd(&sh.survivors, surv + surv_in);
   if (want_hash) {
     for (int o = 16; o; o >>= 1) shash += __shfl_xor_sync(0xffffffffu, shash, o);
     if (lane == 0 && shash) atomicAdd(&sh.surv_hash, shash);
@@ -478,7 +525,7 @@ __device__ bool build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_gri
   // interior: occupancy of the survivors' voxels
   unsigned uniq = 0;
   for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
-    uint32_t u = vox_list[e];
+    uint32_t u = vox_list[e] & kVoxMask;
     int4 vx = m.vox[u];
     int p = (vx.x - g.min_b[0] + 2) + (vx.y - g.min_b[1] + 2) * P0 + (vx.z - g.min_b[2] + 2) * P01;
     uint32_t bit = 1u << (p & 31);
@@ -516,40 +563,75 @@ __device__ bool build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_gri
 // visit the survivors of a voxel that turned out visible: counts, gains, hash, optional OR.
 // mode 0: count/gain/hash; mode 1: OR into A.accum.
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const ViewShared& sh, uint32_t u, int mode,
+// number of set bits of `bits` in positions [lo, hi)
+__device__ __forceinline__ unsigned count_bit_range(const uint32_t* bits, uint32_t lo, uint32_t hi) {
+  unsigned n = 0;
+  or_bit_range([&](unsigned w, uint32_t mask) { n += __popc(bits[w] & mask); }, lo, hi);
+  return n;
+}
+
+__device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const ViewShared& sh, uint32_t uf, int mode,
                                                    uint32_t* cov_scratch, unsigned& vis, unsigned& gain_p,
                                                    unsigned& gain_v, unsigned long long& vhash) {
   const ModelDev& m = A.m;
+  const uint32_t u = uf & kVoxMask;
   const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
   const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
+  const int32_t vcov = m.vox_cov[u];  // coverage voxel shared by all points of the voxel, or -1
   bool any = false;
-  for (uint32_t pos = pb; pos < pe; ++pos) {
-    float4 p = m.pts[pos];
-    if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
+  if (uf & kVoxInside) {
+    // every point of the voxel passed the frustum test (chunk inside the frustum): no coordinates needed
     any = true;
     if (mode == 0) {
-      ++vis;
-      if (!A.covered.pts || !bit_test(A.covered.pts, pos)) ++gain_p;
-      if (want_hash) vhash += mix64((uint64_t)(uint32_t)m.orig[pos]);
-      if (!m.cov_same) {
-        uint32_t id = (uint32_t)m.pt_cov[pos], bit = 1u << (id & 31);
-        uint32_t old = atomicOr(&cov_scratch[id >> 5], bit);
-        if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
-      }
+      vis += pe - pb;
+      gain_p += (pe - pb) - (A.covered.pts ? count_bit_range(A.covered.pts, pb, pe) : 0u);
+      if (want_hash)
+        for (uint32_t pos = pb; pos < pe; ++pos) vhash += mix64((uint64_t)(uint32_t)m.orig[pos]);
     } else {
-      atomicOr(&A.accum.pts[pos >> 5], 1u << (pos & 31));
-      if (!m.cov_same) {
-        uint32_t id = (uint32_t)m.pt_cov[pos];
-        atomicOr(&A.accum.vox[id >> 5], 1u << (id & 31));
+      or_bit_range([&](unsigned w, uint32_t mask) { atomicOr(&A.accum.pts[w], mask); }, pb, pe);
+    }
+    if (vcov < 0) {
+      for (uint32_t pos = pb; pos < pe; ++pos) {
+        uint32_t id = (uint32_t)m.pt_cov[pos], bit = 1u << (id & 31);
+        if (mode == 0) {
+          uint32_t old = atomicOr(&cov_scratch[id >> 5], bit);
+          if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
+        } else {
+          atomicOr(&A.accum.vox[id >> 5], bit);
+        }
+      }
+    }
+  } else {
+    for (uint32_t pos = pb; pos < pe; ++pos) {
+      float4 p = m.pts[pos];
+      if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
+      any = true;
+      if (mode == 0) {
+        ++vis;
+        if (!A.covered.pts || !bit_test(A.covered.pts, pos)) ++gain_p;
+        if (want_hash) vhash += mix64((uint64_t)(uint32_t)m.orig[pos]);
+      } else {
+        atomicOr(&A.accum.pts[pos >> 5], 1u << (pos & 31));
+      }
+      if (vcov < 0) {
+        uint32_t id = (uint32_t)m.pt_cov[pos], bit = 1u << (id & 31);
+        if (mode == 0) {
+          uint32_t old = atomicOr(&cov_scratch[id >> 5], bit);
+          if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
+        } else {
+          atomicOr(&A.accum.vox[id >> 5], bit);
+        }
       }
     }
   }
-  if (any && m.cov_same) {
-    uint32_t id = (uint32_t)m.vox_cov[u];
+  if (any && vcov >= 0) {
+    const uint32_t id = (uint32_t)vcov, bit = 1u << (id & 31);
     if (mode == 0) {
-      if (!A.covered.vox || !bit_test(A.covered.vox, id)) ++gain_v;
+      // several occlusion voxels share a coverage voxel: cov_scratch marks the ones already counted for this view
+      uint32_t old = m.cov_same ? 0u : atomicOr(&cov_scratch[id >> 5], bit);
+      if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
     } else {
-      atomicOr(&A.accum.vox[id >> 5], 1u << (id & 31));
+      atomicOr(&A.accum.vox[id >> 5], bit);
     }
   }
 }
@@ -580,6 +662,7 @@ __device__ __forceinline__ void trace_rays(const EvalArgs& A, ViewShared& sh, co
     uint32_t u = e < count ? vox_list[e] : 0xffffffffu;
     bool visible = false;
     if (u != 0xffffffffu) {
+      u &= kVoxMask;
       int4 vx = m.vox[u];
       int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
       float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
@@ -684,7 +767,7 @@ __device__ __forceinline__ int setup_ray(const ModelDev& m, const GridView& g, c
                                          uint32_t u, uint4& ra, float4& rb, float4& rc, unsigned& steps,
                                          unsigned& fails) {
   if (u == 0xffffffffu) return 0;
-  const int4 vx = m.vox[u];
+  const int4 vx = m.vox[u & kVoxMask];
   const int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
   const float tc[3] = {centre(g, 0, rt[0]), centre(g, 1, rt[1]), centre(g, 2, rt[2])};
   float d[3];
@@ -1043,7 +1126,7 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
       const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
       for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x) {
         const uint32_t u = vis_list[e];
-        const int4 vx = m.vox[u];
+        const int4 vx = m.vox[u & kVoxMask];
         const float tc[3] = {centre(g, 0, vx.x - g.min_b[0]), centre(g, 1, vx.y - g.min_b[1]),
                              centre(g, 2, vx.z - g.min_b[2])};
         if (!second_gate(g, pcd_o, tc)) { vis_list[e] = 0xffffffffu; continue; }
@@ -1178,7 +1261,7 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
     for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
     for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
       uint32_t u = vox_list[e];
-      if (u != 0xffffffffu) vstate[u] = 0xff;
+      if (u != 0xffffffffu) vstate[u & kVoxMask] = 0xff;
     }
     if (threadIdx.x == 0) {
       sh.status |= ASSCPP_VS_ORDERED;
@@ -1279,8 +1362,8 @@ void launch_planes(const double* d_poses, int64_t nviews, const FrustumConst& fc
   int blocks = (int)((nviews + threads - 1) / threads);
   planes_kernel<<<blocks, threads, 0, s>>>(d_poses, nviews, fc, views);
 }
-void launch_eval(const EvalArgs& a, int ctas, size_t smem_bytes, cudaStream_t s) {
-  eval_views_kernel<<<ctas, 1024, smem_bytes, s>>>(a);
+void launch_eval(const EvalArgs& a, int ctas, int threads, size_t smem_bytes, cudaStream_t s) {
+  eval_views_kernel<<<ctas, threads, smem_bytes, s>>>(a);
 }
 void launch_ordered(const EvalArgs& a, int ctas, size_t smem_bytes, cudaStream_t s) {
   ordered_views_kernel<<<ctas, 1024, smem_bytes, s>>>(a);

@@ -251,7 +251,14 @@ int preprocess_model(const float* xyz, int64_t n, const AsscppParams& p, ModelHo
     for (auto& t : th) t.join();
   }
   m.vox_cov.resize(m.n_vox);
-  for (int64_t u = 0; u < m.n_vox; ++u) m.vox_cov[u] = m.pt_cov[m.vox[u].w];
+  // coverage id shared by all points of the voxel, or -1 when they straddle coverage cells (possible whenever the
+  // two lattices do not nest exactly in float32)
+  for (int64_t u = 0; u < m.n_vox; ++u) {
+    int32_t id = m.pt_cov[m.vox[u].w];
+    for (int64_t q = m.vox[u].w + 1; q < m.vox[u + 1].w; ++q)
+      if (m.pt_cov[q] != id) { id = -1; break; }
+    m.vox_cov[u] = id;
+  }
   // ---- chunks of whole voxels, tight AABBs ------------------------------------------------------
   auto bits_of = [](uint32_t v) { float f; std::memcpy(&f, &v, 4); return f; };
   int64_t u = 0;
@@ -260,7 +267,6 @@ int preprocess_model(const float* xyz, int64_t n, const AsscppParams& p, ModelHo
     ++u;
     while (u < m.n_vox && m.vox[u + 1].w - pb <= kChunkMaxPoints) ++u;
     int64_t pe = m.vox[u].w;
-    (void)ub;
     Float4 l{INFINITY, INFINITY, INFINITY, bits_of((uint32_t)pb)}, h{-INFINITY, -INFINITY, -INFINITY, bits_of((uint32_t)pe)};
     for (int64_t q = pb; q < pe; ++q) {
       l.x = std::min(l.x, m.pts[q].x); l.y = std::min(l.y, m.pts[q].y); l.z = std::min(l.z, m.pts[q].z);
@@ -268,7 +274,9 @@ int preprocess_model(const float* xyz, int64_t n, const AsscppParams& p, ModelHo
     }
     m.chunk_lo.push_back(l);
     m.chunk_hi.push_back(h);
+    m.chunk_vox.push_back((int32_t)ub);
   }
+  m.chunk_vox.push_back((int32_t)m.n_vox);
   m.n_chunks = (int64_t)m.chunk_lo.size();
   m.n_super = (m.n_chunks + kSuperFanout - 1) / kSuperFanout;
   m.super_lo.resize(m.n_super);

@@ -14,7 +14,7 @@ struct Int4 { int32_t x, y, z, w; };
 struct ModelHost {
   int64_t n = 0, n_vox = 0, n_cov = 0, n_chunks = 0, n_super = 0;
   std::vector<Float4> pts;
-  std::vector<int32_t> orig, pos_of, vox_cov, pt_cov;
+  std::vector<int32_t> orig, pos_of, vox_cov, pt_cov, chunk_vox;
   std::vector<Int4> vox;
   std::vector<Float4> chunk_lo, chunk_hi, super_lo, super_hi;
   std::vector<int64_t> cov_keys;  // sorted linear keys of the coverage voxels (compact id = rank)
