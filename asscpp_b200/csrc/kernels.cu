@@ -186,7 +186,7 @@ struct ViewShared {
   int bb_min[3], bb_max[3];
   int view;
   int use_smem;
-  unsigned chunk_count, list_count, vis_count, ray_next, ray_count;
+  unsigned chunk_count, chunk_next, super_count, list_count, vis_count, ray_next, ray_count;
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
   int seg_last[1024];  // ordered path only
@@ -329,37 +329,55 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
   const bool brute = (A.flags & ASSCPP_EVAL_BRUTE) != 0;
   const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
   if (!brute) {
-    // P1: 32 super-chunks per warp step, then the 32 children of each surviving super-chunk
+    // P1a: every thread tests super-chunks; survivors go to a shared list (sh.seg_last doubles as that list)
+    constexpr unsigned kSuperListCap = 1024;
     for (int64_t s0 = (int64_t)warp * 32; s0 < m.n_super; s0 += (int64_t)nwarps * 32) {
-      int64_t s = s0 + lane;
+      const int64_t s = s0 + lane;
       bool keep = false;
       if (s < m.n_super) {
         float4 lo = m.super_lo[s], hi = m.super_hi[s];
         keep = !box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
       }
-      unsigned sb = __ballot_sync(0xffffffffu, keep);
-      while (sb) {
-        int b = __ffs(sb) - 1;
-        sb &= sb - 1;
-        int64_t c = (s0 + b) * kSuperFanout + lane;
-        bool ck = false;
-        float4 lo, hi;
-        if (c < m.n_chunks) {
-          lo = m.chunk_lo[c]; hi = m.chunk_hi[c];
-          ck = !box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
-        }
-        unsigned cb = __ballot_sync(0xffffffffu, ck);
-        if (cb) {
-          unsigned base = 0;
-          if (lane == 0) base = atomicAdd(&sh.chunk_count, (unsigned)__popc(cb));
-          base = __shfl_sync(0xffffffffu, base, 0);
-          if (ck) {
-            // chunks wholly inside the frustum are passed on as a voxel range: their points are never read
-            const bool in = box_inside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
-            chunk_list[base + __popc(cb & ((1u << lane) - 1))] =
-                in ? make_uint2((uint32_t)m.chunk_vox[c] | kVoxInside, (uint32_t)m.chunk_vox[c + 1])
-                   : make_uint2(__float_as_uint(lo.w), __float_as_uint(hi.w));
-          }
+      const unsigned sb = __ballot_sync(0xffffffffu, keep);
+      if (sb) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(&sh.super_count, (unsigned)__popc(sb));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        const unsigned at = base + __popc(sb & ((1u << lane) - 1));
+        if (keep && at < kSuperListCap) sh.seg_last[at] = (int)s;
+      }
+    }
+    __syncthreads();
+    // P1b: the 32 children of each surviving super-chunk, one super per warp step, spread evenly over the warps
+    const unsigned nsup = sh.super_count;
+    const bool listed = nsup <= kSuperListCap;  // otherwise (huge frustum): walk all super-chunks again
+    const int64_t nstep = listed ? (int64_t)nsup : m.n_super;
+    for (int64_t k = warp; k < nstep; k += nwarps) {
+      int64_t sup = k;
+      if (listed) {
+        sup = sh.seg_last[k];
+      } else {
+        float4 lo = m.super_lo[k], hi = m.super_hi[k];
+        if (box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z)) continue;
+      }
+      const int64_t c = sup * kSuperFanout + lane;
+      bool ck = false;
+      float4 lo, hi;
+      if (c < m.n_chunks) {
+        lo = m.chunk_lo[c]; hi = m.chunk_hi[c];
+        ck = !box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+      }
+      const unsigned cb = __ballot_sync(0xffffffffu, ck);
+      if (cb) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(&sh.chunk_count, (unsigned)__popc(cb));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (ck) {
+          // chunks wholly inside the frustum are passed on as a voxel range: their points are never read
+          const bool in = box_inside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+          chunk_list[base + __popc(cb & ((1u << lane) - 1))] =
+              in ? make_uint2((uint32_t)m.chunk_vox[c] | kVoxInside, (uint32_t)m.chunk_vox[c + 1])
+                 : make_uint2(__float_as_uint(lo.w), __float_as_uint(hi.w));
         }
       }
     }
@@ -370,7 +388,12 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
   int bmin[3] = {INT_MAX, INT_MAX, INT_MAX}, bmax[3] = {INT_MIN, INT_MIN, INT_MIN};
   unsigned surv = 0, surv_in = 0;
   unsigned long long shash = 0;
-  for (int64_t w = warp; w < nwork; w += nwarps) {
+  for (;;) {
+    // chunks are handed out one at a time: inside chunks are cheap, boundary chunks are not
+    unsigned w = 0;
+    if (lane == 0) w = atomicAdd(&sh.chunk_next, 1u);
+    w = __shfl_sync(0xffffffffu, w, 0);
+    if ((int64_t)w >= nwork) break;
     uint32_t pb, pe;
     if (brute) { pb = __float_as_uint(m.chunk_lo[w].w); pe = __float_as_uint(m.chunk_hi[w].w); }
     else { uint2 r = chunk_list[w]; pb = r.x; pe = r.y; }
@@ -1050,7 +1073,7 @@ __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   }
   if (threadIdx.x == 0) {
     sh.view = v;
-    sh.chunk_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.ray_count = 0;
+    sh.chunk_count = 0; sh.chunk_next = 0; sh.super_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.ray_count = 0;
     sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
     sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
     sh.words = 0; sh.use_smem = 1;
