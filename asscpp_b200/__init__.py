@@ -235,7 +235,7 @@ class CoverageContext:
 
     def phase_cycles(self, enable=True):
         """Read + reset the per-phase SM-cycle counters (cull, grid, DDA, visit, views, CTA lifetime)."""
-        out = np.zeros(8, np.uint64)
+        out = np.zeros(16, np.uint64)
         self._ck(self.L.asscpp_debug_phase_cycles(self.h, int(enable), _ptr(out, C.c_uint64)))
         return out
 

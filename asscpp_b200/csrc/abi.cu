@@ -334,6 +334,10 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
     c->cov_min_b[k] = h.cov_min_b[k]; c->cov_div[k] = h.cov_div[k];
   }
   m.dist_thr_sq = h.dist_thr_sq;
+  m.max_abs_coord = 0;
+  for (int k = 0; k < 3; ++k)
+    m.max_abs_coord = std::max(m.max_abs_coord, std::max(std::fabs((float)h.min_b[k]), std::fabs((float)h.max_b[k] + 1.0f)) * params->leaf);
+  m.max_abs_coord *= 1.001f;
   m.cov_same = h.cov_same;
   static_assert(sizeof(Float4) == sizeof(float4) && sizeof(Int4) == sizeof(int4), "layout");
   if ((rc = upload(c, (const Float4**)&m.pts, h.pts))) return fail(rc);
@@ -726,16 +730,16 @@ int asscpp_timer_end(AsscppCtx* c, float* ms) {
 
 int64_t asscpp_launch_count(const AsscppCtx* c) { return c ? c->launches : 0; }
 
-int asscpp_debug_phase_cycles(AsscppCtx* c, int enable, uint64_t out[8]) {
+int asscpp_debug_phase_cycles(AsscppCtx* c, int enable, uint64_t out[16]) {
   if (!c) return ASSCPP_EINVAL;
   cudaSetDevice(c->device);
   CU(c, cudaStreamSynchronize(c->stream));
-  if (c->d_phase && out) CU(c, cudaMemcpy(out, c->d_phase, 8 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+  if (c->d_phase && out) CU(c, cudaMemcpy(out, c->d_phase, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
   if (enable && !c->d_phase) {
-    int rc = dev_alloc(c, &c->d_phase, 8);
+    int rc = dev_alloc(c, &c->d_phase, 16);
     if (rc) return rc;
   }
-  if (c->d_phase) CU(c, cudaMemset(c->d_phase, 0, 8 * sizeof(uint64_t)));
+  if (c->d_phase) CU(c, cudaMemset(c->d_phase, 0, 16 * sizeof(uint64_t)));
   if (!enable) c->d_phase = nullptr;  // buffer stays in c->allocs and is released with the context
   return ASSCPP_OK;
 }

@@ -37,6 +37,7 @@ struct ModelDev {
   const float4* super_hi;  // [n_super]
   float leaf, inv_leaf, half_leaf;
   float pcd_origin[3];
+  float max_abs_coord;  // bound on |x|, |y|, |z| over the model
   float dist_thr_sq;    // largest f32 s with sqrt((double)s) <= (double)(leaf*2): occluder iff sum > this
   int cov_same;         // coverage lattice == occlusion lattice
   int32_t min_b[3], max_b[3];

@@ -178,18 +178,23 @@ __device__ __forceinline__ uint32_t grid_load(const GridMem& gm, unsigned w) {
   }
 }
 
+constexpr unsigned kDescShared = 1024;
+
 struct ViewShared {
   float planes[24];
   float origin[3];
+  float vox_hi[6];  // cull: voxel cube classification bound per plane
   GridView g;
   unsigned words;
   int bb_min[3], bb_max[3];
   int view;
   int use_smem;
+  unsigned long long cand_state;  // cull: descriptors handed out (high word) | candidate voxels so far (low word)
   unsigned chunk_count, chunk_next, super_count, list_count, vis_count, ray_next, ray_count;
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
-  int seg_last[1024];  // ordered path only
+  int seg_last[1024];  // ordered path; cull: list of surviving super-chunks
+  uint2 chunk_desc[kDescShared];  // cull: candidate chunk descriptors (the rest spill to the global chunk list)
 };
 
 // include/cscpp/voxel_grid_occlusion_estimation.h:143-157 with r = ijk - min_b
@@ -323,14 +328,29 @@ __device__ __forceinline__ unsigned warp_sum(unsigned v) { return __reduce_add_s
 // P1 + P2: cull.  Fills sh.survivors / bb_* / surv_hash and the per-CTA list of occupied voxels
 // (duplicates possible when a voxel's points straddle two 32-point loads; P3 removes them).
 // ------------------------------------------------------------------------------------------------
-__device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list) {
+__device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list,
+                          uint32_t* cut_list, unsigned cut_cap) {
   const ModelDev& m = A.m;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const bool brute = (A.flags & ASSCPP_EVAL_BRUTE) != 0;
   const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
+  if (threadIdx.x < 6) {
+    // Voxel cube vs plane k, centre / radius form: every point of a voxel lies within h = leaf/2 + slack of the
+    // cube centre on each axis (slack: float32 rounding of x * inv_leaf and of the centre itself, < 1e-6 of the
+    // largest model coordinate), so the plane function over the cube stays within r = h (|a|+|b|+|c|) of its value v
+    // at the centre; the exact float32 test value differs from the real one by less than M = 1e-6 A (16 ulps of
+    // the sum of magnitudes A).  v > r + M: all points fail plane k;  v < -(r + M): all pass it.
+    const float* pl = sh.planes + 4 * threadIdx.x;
+    const float n1 = fabsf(pl[0]) + fabsf(pl[1]) + fabsf(pl[2]);
+    const float h = 0.5f * m.leaf + 1e-6f * m.max_abs_coord;
+    sh.vox_hi[threadIdx.x] = h * n1 + (1e-6f * (n1 * (m.max_abs_coord + m.leaf) + fabsf(pl[3])) + 1e-30f);
+  }
+  if (brute) __syncthreads();
   if (!brute) {
     // P1a: every thread tests super-chunks; survivors go to a shared list (sh.seg_last doubles as that list)
     constexpr unsigned kSuperListCap = 1024;
+    const bool prof = A.phase_cycles != nullptr && threadIdx.x == 0;
+    const long long c0 = prof ? clock64() : 0;
     for (int64_t s0 = (int64_t)warp * 32; s0 < m.n_super; s0 += (int64_t)nwarps * 32) {
       const int64_t s = s0 + lane;
       bool keep = false;
@@ -348,6 +368,7 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
       }
     }
     __syncthreads();
+    const long long c1 = prof ? clock64() : 0;
     // P1b: the 32 children of each surviving super-chunk, one super per warp step, spread evenly over the warps
     const unsigned nsup = sh.super_count;
     const bool listed = nsup <= kSuperListCap;  // otherwise (huge frustum): walk all super-chunks again
@@ -369,25 +390,172 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
       }
       const unsigned cb = __ballot_sync(0xffffffffu, ck);
       if (cb) {
-        unsigned base = 0;
-        if (lane == 0) base = atomicAdd(&sh.chunk_count, (unsigned)__popc(cb));
+        // candidate chunk -> descriptor {first voxel | inside flag, offset of its voxels in the flat candidate order};
+        // one 64-bit atomic hands out descriptor slots (high word) and voxel offsets (low word) together, so
+        // offsets ascend with the slot index
+        uint32_t vb = 0, nv = 0;
+        if (ck) { vb = (uint32_t)m.chunk_vox[c]; nv = (uint32_t)m.chunk_vox[c + 1] - vb; }
+        uint32_t incl = nv;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(&sh.cand_state, ((unsigned long long)__popc(cb) << 32) | tot);
         base = __shfl_sync(0xffffffffu, base, 0);
         if (ck) {
-          // chunks wholly inside the frustum are passed on as a voxel range: their points are never read
+          // chunks wholly inside the frustum: every point passes, no voxel of it needs classifying
           const bool in = box_inside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
-          chunk_list[base + __popc(cb & ((1u << lane) - 1))] =
-              in ? make_uint2((uint32_t)m.chunk_vox[c] | kVoxInside, (uint32_t)m.chunk_vox[c + 1])
-                 : make_uint2(__float_as_uint(lo.w), __float_as_uint(hi.w));
+          const unsigned slot = (unsigned)(base >> 32) + __popc(cb & ((1u << lane) - 1));
+          const uint2 d = make_uint2(vb | (in ? kVoxInside : 0u), (uint32_t)base + incl - nv);
+          if (slot < kDescShared) sh.chunk_desc[slot] = d;
+          else chunk_list[slot] = d;
         }
       }
     }
     __syncthreads();
+    if (prof) {
+      atomicAdd(&A.phase_cycles[6], (unsigned long long)(c1 - c0));
+      atomicAdd(&A.phase_cycles[7], (unsigned long long)(clock64() - c1));
+    }
   }
-  // P2: exact test, 32 points per warp step
-  const int64_t nwork = brute ? m.n_chunks : (int64_t)sh.chunk_count;
   int bmin[3] = {INT_MAX, INT_MAX, INT_MAX}, bmax[3] = {INT_MIN, INT_MIN, INT_MIN};
   unsigned surv = 0, surv_in = 0;
   unsigned long long shash = 0;
+  if (!brute) {
+    // P2: the voxels of the candidate chunks in one flat order, cut into one contiguous segment per warp, one
+    // lane per voxel, kCullUnroll blocks of 32 in flight.  Chunk inside the frustum: every point survives.
+    // Otherwise the voxel's cube is classified against the planes (centre / radius form with the per-view
+    // bounds sh.vox_hi); voxels cut by a plane are set aside and their points tested one by one
+    // (frustum_culling.cpp:153-166) afterwards, one lane per such voxel.
+    constexpr int kCullUnroll = 2;
+    const unsigned total = (unsigned)sh.cand_state, ndesc = (unsigned)(sh.cand_state >> 32);
+    auto desc = [&](unsigned i) { return i < kDescShared ? sh.chunk_desc[i] : chunk_list[i]; };
+    auto emit_voxels = [&](bool emit, uint32_t entry) {
+      const unsigned ob = __ballot_sync(0xffffffffu, emit);
+      if (!ob) return;
+      unsigned slot = 0;
+      if (lane == 0) slot = atomicAdd(&sh.list_count, (unsigned)__popc(ob));
+      slot = __shfl_sync(0xffffffffu, slot, 0);
+      if (emit) {
+        const unsigned at = slot + __popc(ob & ((1u << lane) - 1));
+        if (at < A.list_cap) vox_list[at] = entry;
+      }
+    };
+    uint32_t* cut = cut_list;  // this warp's list of voxels cut by a plane
+    unsigned ncut = 0;         // warp-uniform
+    auto flush_cut = [&]() {
+      __syncwarp();
+      for (unsigned i0 = 0; i0 < ncut; i0 += 32) {
+        const unsigned i = i0 + lane;
+        unsigned cnt = 0;
+        uint32_t u = 0;
+        if (i < ncut) {
+          u = __ldcg(cut + i);
+          const int4 vx = m.vox[u];
+          const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
+          for (uint32_t q = q0; q < q1; ++q) {
+            const float4 p = m.pts[q];
+            if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
+            ++cnt;
+            if (want_hash) shash += mix64((uint64_t)(uint32_t)m.orig[q]);
+          }
+          if (cnt) {
+            surv_in += cnt;
+            bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
+            bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
+          }
+        }
+        emit_voxels(cnt != 0, u);
+      }
+      ncut = 0;
+      __syncwarp();
+    };
+    const bool prof2 = A.phase_cycles != nullptr && threadIdx.x == 0;
+    const long long d0 = prof2 ? clock64() : 0;
+    // warps claim runs of kCullClaim candidates (cut voxels make the cost per candidate uneven)
+    constexpr unsigned kCullClaim = 256;
+    for (;;) {
+    unsigned j_begin = 0;
+    if (lane == 0) j_begin = atomicAdd(&sh.chunk_next, kCullClaim);
+    j_begin = __shfl_sync(0xffffffffu, j_begin, 0);
+    if (j_begin >= total) break;
+    const unsigned j_end = min(total, j_begin + kCullClaim);
+    unsigned c = 0;  // descriptor of this lane's current candidate; only ever moves forward within a claim
+    {
+      unsigned lo = 0, hi = ndesc;  // last descriptor starting at or before j_begin
+      while (hi - lo > 1) {
+        const unsigned mid = (lo + hi) >> 1;
+        if (desc(mid).y <= j_begin) lo = mid; else hi = mid;
+      }
+      c = lo;
+    }
+    for (unsigned jb = j_begin; jb < j_end; jb += 32 * kCullUnroll) {
+      uint32_t uu[kCullUnroll], q1[kCullUnroll];
+      int4 vx[kCullUnroll];
+      bool on[kCullUnroll], cin[kCullUnroll];
+#pragma unroll
+      for (int b = 0; b < kCullUnroll; ++b) {
+        const unsigned j = jb + b * 32 + lane;
+        on[b] = j < j_end; cin[b] = false; uu[b] = 0; q1[b] = 0; vx[b] = make_int4(0, 0, 0, 0);
+        if (on[b]) {
+          while (c + 1 < ndesc && desc(c + 1).y <= j) ++c;
+          const uint2 d = desc(c);
+          uu[b] = (d.x & kVoxMask) + (j - d.y);
+          cin[b] = (d.x & kVoxInside) != 0;
+          vx[b] = m.vox[uu[b]];
+          q1[b] = (uint32_t)m.vox[uu[b] + 1].w;
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < kCullUnroll; ++b) {
+        if (jb + b * 32 >= j_end) break;
+        int cls = 0;  // 0 outside, 1 cut by a plane, 2 inside
+        if (on[b]) {
+          cls = 2;
+          if (!cin[b]) {
+            const float cx = ((float)vx[b].x + 0.5f) * m.leaf, cy = ((float)vx[b].y + 0.5f) * m.leaf,
+                        cz = ((float)vx[b].z + 0.5f) * m.leaf;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) {
+              const float v = sh.planes[4 * k] * cx + sh.planes[4 * k + 1] * cy + sh.planes[4 * k + 2] * cz +
+                              sh.planes[4 * k + 3];
+              if (v > sh.vox_hi[k]) cls = 0;
+              else if (!(v < -sh.vox_hi[k]) && cls == 2) cls = 1;
+            }
+          }
+          if (cls == 2) {
+            const uint32_t q0 = (uint32_t)vx[b].w;
+            surv_in += q1[b] - q0;
+            if (want_hash)
+              for (uint32_t q = q0; q < q1[b]; ++q) shash += mix64((uint64_t)(uint32_t)m.orig[q]);
+            bmin[0] = min(bmin[0], vx[b].x); bmin[1] = min(bmin[1], vx[b].y); bmin[2] = min(bmin[2], vx[b].z);
+            bmax[0] = max(bmax[0], vx[b].x); bmax[1] = max(bmax[1], vx[b].y); bmax[2] = max(bmax[2], vx[b].z);
+          }
+        }
+        emit_voxels(cls == 2, uu[b] | kVoxInside);
+        const unsigned sb = __ballot_sync(0xffffffffu, cls == 1);
+        if (sb) {
+          if (cls == 1) __stcg(cut + ncut + __popc(sb & ((1u << lane) - 1)), uu[b]);
+          ncut += (unsigned)__popc(sb);
+          if (ncut + 32 > cut_cap) flush_cut();
+        }
+      }
+    }
+    }  // claims
+    const long long d1 = prof2 ? clock64() : 0;
+    if (prof2) atomicAdd(&A.phase_cycles[10], (unsigned long long)ncut);
+    flush_cut();
+    if (prof2) {
+      atomicAdd(&A.phase_cycles[8], (unsigned long long)(d1 - d0));
+      atomicAdd(&A.phase_cycles[9], (unsigned long long)(clock64() - d1));
+      atomicAdd(&A.phase_cycles[11], (unsigned long long)total);
+    }
+  }
+  // brute mode: exact test of every point, 32 points per warp step
+  const int64_t nwork = brute ? m.n_chunks : 0;
   for (;;) {
     // chunks are handed out one at a time: inside chunks are cheap, boundary chunks are not
     unsigned w = 0;
@@ -395,33 +563,7 @@ __device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, 
     w = __shfl_sync(0xffffffffu, w, 0);
     if ((int64_t)w >= nwork) break;
     uint32_t pb, pe;
-    if (brute) { pb = __float_as_uint(m.chunk_lo[w].w); pe = __float_as_uint(m.chunk_hi[w].w); }
-    else { uint2 r = chunk_list[w]; pb = r.x; pe = r.y; }
-    if (pb & kVoxInside) {
-      // voxel range [pb, pe) of a chunk inside the frustum: one lane per voxel, every point survives
-      for (uint32_t u0 = pb & kVoxMask; u0 < pe; u0 += 32) {
-        const uint32_t u = u0 + lane;
-        const bool on = u < pe;
-        if (on) {
-          const int4 vx = m.vox[u];
-          const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
-          surv_in += q1 - q0;
-          if (want_hash)
-            for (uint32_t q = q0; q < q1; ++q) shash += mix64((uint64_t)(uint32_t)m.orig[q]);
-          bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
-          bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
-        }
-        const unsigned ob = __ballot_sync(0xffffffffu, on);
-        unsigned slot = 0;
-        if (lane == 0) slot = atomicAdd(&sh.list_count, (unsigned)__popc(ob));
-        slot = __shfl_sync(0xffffffffu, slot, 0);
-        if (on) {
-          const unsigned at = slot + lane;
-          if (at < A.list_cap) vox_list[at] = u | kVoxInside;
-        }
-      }
-      continue;
-    }
+    pb = __float_as_uint(m.chunk_lo[w].w); pe = __float_as_uint(m.chunk_hi[w].w);
     for (uint32_t base0 = pb; base0 < pe; base0 += 128) {
       // four independent 512-byte loads in flight per warp before any is consumed (latency, not bandwidth,
       // bounds this phase: a chunk holds at most kChunkMaxPoints = 128 points unless it is one big voxel)
@@ -1016,13 +1158,21 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
       qtail = nhave;
       have = 0; walking = 0;  // nothing of the walk state is live across the setup code below
       pbit = bit_base; pt = 0; k0 = k1 = k2 = 0; tx = ty = tz = dtx = dty = dtz = 0; u = w_s01 = w_s2t2 = w_t01 = 0;
-      unsigned e0 = 0;
-      if (lane == 0) e0 = atomicAdd(&sh.ray_next, (unsigned)kRayBatch);
+      // guided claim: full batches while plenty of entries remain, smaller ones near the end of the list so
+      // that the warps finish together
+      unsigned e0 = 0, bsz = 0;
+      if (lane == 0) {
+        const unsigned seen = *(volatile unsigned*)&sh.ray_next;
+        const unsigned rem = seen < total ? total - seen : 0u;
+        bsz = max(32u, min((unsigned)kRayBatch, (rem / (2u * (blockDim.x >> 5))) & ~31u));
+        e0 = atomicAdd(&sh.ray_next, bsz);
+      }
       e0 = __shfl_sync(0xffffffffu, e0, 0);
+      bsz = __shfl_sync(0xffffffffu, bsz, 0);
       if (e0 >= total) {
         more = false;
       } else {
-        const unsigned e1 = min(total, e0 + (unsigned)kRayBatch);
+        const unsigned e1 = min(total, e0 + bsz);
         for (unsigned eb = e0; eb < e1; eb += 32) {
           const unsigned e = eb + lane;
           const uint32_t uu = e < e1 ? vox_list[e] : 0xffffffffu;
@@ -1073,7 +1223,7 @@ __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   }
   if (threadIdx.x == 0) {
     sh.view = v;
-    sh.chunk_count = 0; sh.chunk_next = 0; sh.super_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.ray_count = 0;
+    sh.cand_state = 0; sh.chunk_count = 0; sh.chunk_next = 0; sh.super_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.ray_count = 0;
     sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
     sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
     sh.words = 0; sh.use_smem = 1;
@@ -1117,7 +1267,9 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     if (prof) t0 = clock64();
     reset_view(sh, A.views[v], v);
     __syncthreads();
-    cull_view(A, sh, chunk_list, vox_list);
+    cull_view(A, sh, chunk_list, vox_list,
+              reinterpret_cast<uint32_t*>(A.ray_buf + ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 3 * kRayQueueCap),
+              3u * kRayQueueCap * 4u);  // the warp's ray queue is idle during the cull
     if (prof) t1 = clock64();
     if (sh.survivors == 0) {  // empty frustum cloud: extractVisibleSurface returns an empty cloud
       if (threadIdx.x == 0) write_result(A, sh, v);
@@ -1221,7 +1373,9 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
     __syncthreads();
     reset_view(sh, A.views[v], v);
     __syncthreads();
-    cull_view(A, sh, chunk_list, vox_list);
+    cull_view(A, sh, chunk_list, vox_list,
+              reinterpret_cast<uint32_t*>(A.ray_buf + ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 3 * kRayQueueCap),
+              3u * kRayQueueCap * 4u);  // the warp's ray queue is idle during the cull
     GridMem gm;
     const bool in_smem = build_grid(A, sh, smem_grid, glob_grid, vox_list, &gm);
     // per-voxel state: bits 0-1 = 0 free / 1 occluded / 2 failed, bit 2 = second gate passes

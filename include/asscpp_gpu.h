@@ -149,9 +149,10 @@ int asscpp_timer_end(AsscppCtx* ctx, float* ms);  /* record + synchronise + elap
 /* kernels launched by this context since creation (the bench's gpu_launches claim) */
 int64_t asscpp_launch_count(const AsscppCtx* ctx);
 /* developer aid: SM-cycle counters of eval_views_kernel's phases, summed over views, read and reset.
- * out[0..3] = cull, grid build, DDA, point visit; out[4] = views; out[5] = CTA lifetimes.  enable != 0
+ * out[0..3] = cull, grid build, DDA, point visit; out[4] = views; out[5] = CTA lifetimes; out[6..15] = finer
+ * splits of the cull (see tools/phase_profile.py).  enable != 0
  * turns the counters on for subsequent evaluations, 0 turns them off. */
-int asscpp_debug_phase_cycles(AsscppCtx* ctx, int enable, uint64_t out[8]);
+int asscpp_debug_phase_cycles(AsscppCtx* ctx, int enable, uint64_t out[16]);
 /* device time of the dominant kernel (eval_views) accumulated between timer_begin/timer_end */
 int asscpp_eval_kernel_ms(AsscppCtx* ctx, float* ms, int64_t* launches);
 
