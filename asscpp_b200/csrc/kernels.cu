@@ -328,7 +328,7 @@ __device__ __forceinline__ unsigned warp_sum(unsigned v) { return __reduce_add_s
 // P1 + P2: cull.  Fills sh.survivors / bb_* / surv_hash and the per-CTA list of occupied voxels
 // (duplicates possible when a voxel's points straddle two 32-point loads; P3 removes them).
 // ------------------------------------------------------------------------------------------------
-__device__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list,
+__device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list,
                           uint32_t* cut_list, unsigned cut_cap) {
   const ModelDev& m = A.m;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -639,7 +639,7 @@ __device__ __forceinline__ void or_bit_range(F&& or_word, unsigned lo, unsigned 
   }
 }
 
-__device__ bool build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_grid, uint32_t* glob_grid,
+__device__ __forceinline__ bool build_grid(const EvalArgs& A, ViewShared& sh, uint32_t* smem_grid, uint32_t* glob_grid,
                            uint32_t* vox_list, GridMem* gm_out) {
   const ModelDev& m = A.m;
   if (threadIdx.x == 0) {
@@ -1214,7 +1214,7 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
   }
 }
 
-__device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
+__device__ __forceinline__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   if (threadIdx.x < 24) sh.planes[threadIdx.x] = vd.planes[threadIdx.x];
   if (threadIdx.x < 3) {
     sh.origin[threadIdx.x] = vd.origin[threadIdx.x];
@@ -1231,7 +1231,7 @@ __device__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   }
 }
 
-__device__ void write_result(const EvalArgs& A, const ViewShared& sh, int v) {
+__device__ __forceinline__ void write_result(const EvalArgs& A, const ViewShared& sh, int v) {
   AsscppViewResult r;
   r.survivors = sh.survivors; r.visible = sh.visible; r.carry = sh.carry; r.unique_rays = sh.unique;
   r.gain_pts = sh.gain_p; r.gain_vox = sh.gain_v; r.status = sh.status; r.reserved = 0;
