@@ -11,12 +11,13 @@ import ctypes as C
 import numpy as np
 
 from . import _abi
-from ._abi import (EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, RESULT_DTYPE, VS_GRID_GLOBAL, VS_GRID_SHARED,
-                   VS_ORDERED, ModelInfo, Params)
+from ._abi import (ACCURACY_DTYPE, EVAL_ACCURACY, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, RESULT_DTYPE,
+                   VS_GRID_GLOBAL, VS_GRID_SHARED, VS_ORDERED, ModelInfo, Params)
 
 __all__ = [
     "CoverageContext", "CoveredSet", "AsscppError", "default_params", "synth_structure", "synth_views",
-    "robot2sensor", "frustum_planes", "EVAL_HASH", "EVAL_BRUTE", "EVAL_FORCE_GLOBAL", "RESULT_DTYPE",
+    "robot2sensor", "frustum_planes", "pose_rpy", "viewport_transform", "EVAL_HASH", "EVAL_BRUTE",
+    "EVAL_FORCE_GLOBAL", "EVAL_ACCURACY", "RESULT_DTYPE", "ACCURACY_DTYPE",
 ]
 
 SEED_STRUCTURE, SEED_POINTS, SEED_VIEWS = 0xA55C0001, 0xA55C0002, 0xA55C0003
@@ -82,6 +83,28 @@ def frustum_planes(params, pose):
     if rc:
         raise AsscppError(rc, "frustum_planes")
     return pl.reshape(6, 4), o
+
+
+def pose_rpy(pose):
+    """tf::Matrix3x3(q).getRPY of a pose (host)."""
+    pose = np.ascontiguousarray(pose, np.float64)
+    out = np.zeros(3, np.float64)
+    rc = _abi.load().asscpp_pose_rpy(_ptr(pose, C.c_double), _ptr(out, C.c_double))
+    if rc:
+        raise AsscppError(rc, "pose_rpy")
+    return out
+
+
+def viewport_transform(pose, xyz):
+    """OcclusionCulling::pointCloudViewportTransform (host)."""
+    pose = np.ascontiguousarray(pose, np.float64)
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    out = np.zeros_like(xyz)
+    rc = _abi.load().asscpp_viewport_transform(_ptr(pose, C.c_double), _ptr(xyz, C.c_float), len(xyz),
+                                               _ptr(out, C.c_float))
+    if rc:
+        raise AsscppError(rc, "viewport_transform")
+    return out
 
 
 class CoveredSet:
@@ -186,6 +209,12 @@ class CoverageContext:
 
     def eval_batch(self, poses, covered=None, flags=0):
         return self.results(self.eval_async(poses, covered, flags))
+
+    def accuracy(self, nviews):
+        """Accuracy terms of the last evaluation issued with EVAL_ACCURACY (AsscppViewAccuracy per view)."""
+        out = np.zeros(nviews, ACCURACY_DTYPE)
+        self._ck(self.L.asscpp_get_accuracy(self.h, out.ctypes.data_as(C.c_void_p), nviews))
+        return out
 
     def eval_device(self, d_poses_ptr, nviews, covered=None, flags=0):
         """poses already in HBM (raw device pointer); results stay on the device."""

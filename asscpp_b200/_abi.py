@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("ASSCPP_LIB") or os.path.join(_HERE, "lib", "libasscpp_b200.so")
 
 OK, EINVAL, ENODEVICE, ECUDA, ERANGE, ENOMEM, ESTATE, ENCCL = 0, -1, -2, -3, -4, -5, -6, -7
-EVAL_HASH, EVAL_BRUTE, EVAL_FORCE_GLOBAL = 1, 2, 4
+EVAL_HASH, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_ACCURACY = 1, 2, 4, 8
 VS_GRID_SHARED, VS_GRID_GLOBAL, VS_ORDERED = 1, 2, 4
 
 
@@ -60,6 +60,19 @@ RESULT_DTYPE = np.dtype(
 )
 assert RESULT_DTYPE.itemsize == 64
 
+# numpy mirror of AsscppViewAccuracy
+ACCURACY_DTYPE = np.dtype(
+    [
+        ("err_sum_depth", np.float64),
+        ("err_sum_z", np.float64),
+        ("depth_min", np.float32),
+        ("depth_max", np.float32),
+        ("visible", np.uint32),
+        ("reserved", np.uint32),
+    ]
+)
+assert ACCURACY_DTYPE.itemsize == 32
+
 # every symbol include/asscpp_gpu.h declares (checked by tests/test_abi_symbols.py)
 SYMBOLS = [
     "asscpp_create", "asscpp_destroy", "asscpp_last_error", "asscpp_abi_version", "asscpp_model_info",
@@ -72,7 +85,7 @@ SYMBOLS = [
     "asscpp_debug_phase_cycles",
     "asscpp_comm_unique_id", "asscpp_comm_init", "asscpp_allgather_results", "asscpp_allreduce_or",
     "asscpp_comm_destroy", "asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor",
-    "asscpp_frustum_planes",
+    "asscpp_frustum_planes", "asscpp_get_accuracy", "asscpp_pose_rpy", "asscpp_viewport_transform",
 ]
 
 _lib = None
@@ -134,6 +147,9 @@ def load():
         "asscpp_synth_views_v1": (i32, [C.c_uint64, C.c_uint64, i64, f64p]),
         "asscpp_robot2sensor": (i32, [f64p, f64p, f64p, f64p]),
         "asscpp_frustum_planes": (i32, [C.POINTER(Params), f64p, f32p, f32p]),
+        "asscpp_get_accuracy": (i32, [vp, vp, i64]),
+        "asscpp_pose_rpy": (i32, [f64p, f64p]),
+        "asscpp_viewport_transform": (i32, [f64p, f32p, i64, f32p]),
     }
     assert sorted(sig) == sorted(SYMBOLS)
     for name, (res, args) in sig.items():

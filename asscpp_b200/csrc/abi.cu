@@ -95,6 +95,12 @@ struct AsscppCtx {
   ViewDev* d_views = nullptr;
   AsscppViewResult* d_results = nullptr;
   int32_t* d_ordered_list = nullptr;
+  ViewTrig* d_trig = nullptr;   // ASSCPP_EVAL_ACCURACY
+  AccRaw* d_acc = nullptr;
+  std::vector<ViewTrig> h_trig;
+  std::vector<AccRaw> h_acc;
+  double acc_scale_d = 1, acc_scale_z = 1;
+  bool last_had_acc = false;
   int64_t last_nviews = -1;
   std::vector<AsscppViewResult> h_results;
   // staging
@@ -188,25 +194,44 @@ int ensure_views(AsscppCtx* c, int64_t nviews) {
   CU(c, cudaStreamSynchronize(c->stream));
   int64_t cap = std::max<int64_t>(nviews, c->view_cap * 2);
   cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
+  cudaFree(c->d_trig); cudaFree(c->d_acc);
   c->d_poses = nullptr; c->d_views = nullptr; c->d_results = nullptr; c->d_ordered_list = nullptr;
+  c->d_trig = nullptr; c->d_acc = nullptr;
   c->view_cap = 0;
   int rc;
   if ((rc = dev_alloc(c, &c->d_poses, cap * 7, false))) return rc;
   if ((rc = dev_alloc(c, &c->d_views, cap, false))) return rc;
   if ((rc = dev_alloc(c, &c->d_results, cap, false))) return rc;
   if ((rc = dev_alloc(c, &c->d_ordered_list, cap, false))) return rc;
+  if ((rc = dev_alloc(c, &c->d_trig, cap, false))) return rc;
+  if ((rc = dev_alloc(c, &c->d_acc, cap, false))) return rc;
   c->view_cap = cap;
   return ASSCPP_OK;
 }
 
 // planes -> eval -> ordered, all on the context's stream
 int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_set, int accum_set,
-             int64_t accum_min_visible, uint32_t flags) {
+             int64_t accum_min_visible, uint32_t flags, const double* h_poses = nullptr) {
   if (nviews < 0 || nviews > 0x7fffffffLL) { c->err = "nviews out of range"; return ASSCPP_EINVAL; }
   if (covered_set != -1 && !valid_set(c, covered_set)) { c->err = "bad covered set handle"; return ASSCPP_EINVAL; }
   if (accum_set != -1 && !valid_set(c, accum_set)) { c->err = "bad accumulator set handle"; return ASSCPP_EINVAL; }
   c->last_nviews = nviews;
+  c->last_had_acc = (flags & ASSCPP_EVAL_ACCURACY) != 0;
   if (nviews == 0) return ASSCPP_OK;
+  if (flags & ASSCPP_EVAL_ACCURACY) {
+    if (h_poses) {
+      // yaw / pitch and their sines and cosines with the host's libm, as the reference computes them
+      // (occlusion_culling.cpp:556-584)
+      CU(c, cudaStreamSynchronize(c->stream));  // h_trig may still be in flight from the previous batch
+      c->h_trig.resize((size_t)nviews);
+      for (int64_t v = 0; v < nviews; ++v) viewport_trig_host(h_poses + 7 * v, &c->h_trig[(size_t)v]);
+      CU(c, cudaMemcpyAsync(c->d_trig, c->h_trig.data(), (size_t)nviews * sizeof(ViewTrig), cudaMemcpyHostToDevice,
+                            c->stream));
+    } else {
+      launch_trig(d_poses, nviews, c->d_trig, c->stream);
+      c->launches += 1;
+    }
+  }
   CU(c, cudaMemsetAsync(c->d_counters, 0, 2 * sizeof(int32_t), c->stream));
   launch_planes(d_poses, nviews, c->fc, c->d_views, c->stream);
   EvalArgs a;
@@ -221,6 +246,9 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   if (accum_set >= 0) a.accum = set_dev(c, accum_set);
   a.accum_min_visible = accum_min_visible;
   a.flags = flags;
+  a.trig = c->d_trig;
+  a.acc = (flags & ASSCPP_EVAL_ACCURACY) ? c->d_acc : nullptr;
+  a.acc_scale_d = c->acc_scale_d; a.acc_scale_z = c->acc_scale_z;
   a.chunk_list = c->d_chunk_list; a.chunk_cap = c->chunk_cap;
   a.vox_list = c->d_vox_list; a.list_cap = c->list_cap;
   a.vis_list = c->d_vis_list; a.vis_cap = c->vis_cap;
@@ -338,6 +366,22 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   for (int k = 0; k < 3; ++k)
     m.max_abs_coord = std::max(m.max_abs_coord, std::max(std::fabs((float)h.min_b[k]), std::fabs((float)h.max_b[k] + 1.0f)) * params->leaf);
   m.max_abs_coord *= 1.001f;
+  {
+    // fixed-point scales of the accuracy sums: term * 2^S < 2^70 and (hi part) * visible < 2^63
+    double dmax = std::sqrt((double)params->far_dist * params->far_dist + 0.25 * (double)c->fc.fp_w * c->fc.fp_w +
+                            0.25 * (double)c->fc.fp_h * c->fc.fp_h) * 1.01 + 1e-3;
+    double zmax = (double)m.max_abs_coord + 1e-3;
+    int extra = 0;
+    while (((int64_t)1 << (25 + extra)) < n) ++extra;
+    auto scale_for = [&](double vmax) {
+      double term = 0.0000285 * vmax * vmax;
+      int e = 0;
+      std::frexp(term, &e);  // term < 2^e
+      return std::ldexp(1.0, 70 - e - extra);
+    };
+    c->acc_scale_d = scale_for(dmax);
+    c->acc_scale_z = scale_for(zmax);
+  }
   m.cov_same = h.cov_same;
   static_assert(sizeof(Float4) == sizeof(float4) && sizeof(Int4) == sizeof(int4), "layout");
   if ((rc = upload(c, (const Float4**)&m.pts, h.pts))) return fail(rc);
@@ -427,6 +471,7 @@ int asscpp_destroy(AsscppCtx* c) {
   for (void* p : c->allocs) cudaFree(p);
   for (auto& s : c->sets) cudaFree(s.buf);
   cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
+  cudaFree(c->d_trig); cudaFree(c->d_acc);
   cudaFree(c->d_idx); cudaFree(c->d_cloud); cudaFree(c->d_gather);
   for (auto& ev : c->kernel_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
   if (c->ev_begin) cudaEventDestroy(c->ev_begin);
@@ -464,7 +509,7 @@ int asscpp_eval_batch(AsscppCtx* c, const double* poses, int64_t nviews, int cov
   if (rc) return rc;
   if (nviews > 0)
     CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-  return run_eval(c, c->d_poses, nviews, covered_set, -1, 0, flags);
+  return run_eval(c, c->d_poses, nviews, covered_set, -1, 0, flags, poses);
 }
 
 int asscpp_get_results(AsscppCtx* c, AsscppViewResult* out, int64_t nviews) {
@@ -473,6 +518,37 @@ int asscpp_get_results(AsscppCtx* c, AsscppViewResult* out, int64_t nviews) {
   int rc = fetch_results(c, nviews);
   if (rc) return rc;
   if (nviews > 0) memcpy(out, c->h_results.data(), (size_t)nviews * sizeof(AsscppViewResult));
+  return ASSCPP_OK;
+}
+
+int asscpp_get_accuracy(AsscppCtx* c, AsscppViewAccuracy* out, int64_t nviews) {
+  if (!c || (!out && nviews > 0) || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  if (c->last_nviews < 0 || !c->last_had_acc) { c->err = "the last evaluation was not issued with ASSCPP_EVAL_ACCURACY"; return ASSCPP_ESTATE; }
+  if (nviews > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
+  c->h_acc.resize((size_t)std::max<int64_t>(nviews, 1));
+  if (nviews > 0)
+    CU(c, cudaMemcpyAsync(c->h_acc.data(), c->d_acc, (size_t)nviews * sizeof(AccRaw), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  auto decode = [](unsigned long long hi, unsigned long long lo, double scale) {
+    unsigned __int128 t = ((unsigned __int128)hi << 32) + lo;  // exact sum of the scaled terms
+    return (double)t / scale;                                  // one rounding; the division by 2^S is exact
+  };
+  auto unkey = [](int32_t k) {
+    int32_t b = k >= 0 ? k : k ^ 0x7fffffff;
+    float f;
+    memcpy(&f, &b, 4);
+    return f;
+  };
+  for (int64_t v = 0; v < nviews; ++v) {
+    const AccRaw& r = c->h_acc[(size_t)v];
+    out[v].err_sum_depth = decode(r.d_hi, r.d_lo, c->acc_scale_d);
+    out[v].err_sum_z = decode(r.z_hi, r.z_lo, c->acc_scale_z);
+    out[v].depth_min = unkey(r.min_key);
+    out[v].depth_max = unkey(r.max_key);
+    out[v].visible = r.visible;
+    out[v].reserved = 0;
+  }
   return ASSCPP_OK;
 }
 
@@ -842,6 +918,30 @@ int asscpp_comm_destroy(AsscppCtx* c) {
 int asscpp_frustum_planes(const AsscppParams* p, const double pose[7], float planes[24], float origin[3]) {
   if (!p || !pose || !planes || !origin) return ASSCPP_EINVAL;
   frustum_planes_host(*p, pose, planes, origin, nullptr);
+  return ASSCPP_OK;
+}
+
+int asscpp_pose_rpy(const double pose[7], double rpy[3]) {
+  if (!pose || !rpy) return ASSCPP_EINVAL;
+  pose_rpy_host(pose, rpy);
+  return ASSCPP_OK;
+}
+
+int asscpp_viewport_transform(const double pose[7], const float* xyz, int64_t n, float* out) {
+  // OcclusionCulling::pointCloudViewportTransform (occlusion_culling.cpp:538-618): translate by -camera position,
+  // rotate about z by -yaw and about y by -pitch; every stage in double on float32 inputs, narrowed to float32
+  // (transformPointMatVec, :521-531).  Same arithmetic as acc_point in kernels.cu.
+  if (!pose || (!xyz && n > 0) || (!out && n > 0) || n < 0) return ASSCPP_EINVAL;
+  ViewTrig t;
+  viewport_trig_host(pose, &t);
+  for (int64_t i = 0; i < n; ++i) {
+    const float a0 = (float)((double)xyz[3 * i] + t.t[0]), a1 = (float)((double)xyz[3 * i + 1] + t.t[1]),
+                a2 = (float)((double)xyz[3 * i + 2] + t.t[2]);
+    const float b0 = (float)(t.cz * (double)a0 + (-t.sz) * (double)a1), b1 = (float)(t.sz * (double)a0 + t.cz * (double)a1);
+    out[3 * i] = (float)(t.cy * (double)b0 + t.sy * (double)a2);
+    out[3 * i + 1] = b1;
+    out[3 * i + 2] = (float)((-t.sy) * (double)b0 + t.cy * (double)a2);
+  }
   return ASSCPP_OK;
 }
 

@@ -49,6 +49,20 @@ struct ViewDev {  // per view, written by planes_kernel
   float pad;
 };
 
+// pointCloudViewportTransform constants of one view (occlusion_culling.cpp:545-584)
+struct ViewTrig {
+  double t[3];            // -camera position
+  double cz, sz, cy, sy;  // cos / sin of -yaw and of -pitch
+  double pad;
+};
+
+// accuracy accumulators of one view: fixed-point sums (value * 2^S split into hi * 2^32 + lo) and ordered-int keys
+struct AccRaw {
+  unsigned long long d_hi, d_lo, z_hi, z_lo;
+  int32_t min_key, max_key;
+  uint32_t visible, pad;
+};
+
 struct CoveredDev {
   uint32_t* pts;  // bit per sorted position
   uint32_t* vox;  // bit per compact coverage id
@@ -64,6 +78,9 @@ struct EvalArgs {
   CoveredDev accum;          // OR visible sets into (pts == nullptr: none)
   int64_t accum_min_visible;
   uint32_t flags;
+  const ViewTrig* trig;      // per view, ASSCPP_EVAL_ACCURACY only
+  AccRaw* acc;               // per view, ASSCPP_EVAL_ACCURACY only
+  double acc_scale_d, acc_scale_z;  // 2^S of the two fixed-point sums
   // per-CTA scratch (global memory, L2-resident in steady state)
   uint2* chunk_list;         // [ctas][chunk_cap] candidate chunks {first point, end point}
   int64_t chunk_cap;

@@ -18,6 +18,8 @@
 // contracted into FMA) in the operation order fixed in SURVEY.md Appendix A.
 #include <cuda_runtime.h>
 
+#include <cmath>
+
 #include "common.h"
 #include "kernels.h"
 
@@ -193,6 +195,8 @@ struct ViewShared {
   unsigned chunk_count, chunk_next, super_count, list_count, vis_count, ray_next, ray_count;
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
+  unsigned long long acc[4];  // accuracy: fixed-point sums (depth hi / lo, z hi / lo)
+  int acc_min, acc_max;       // accuracy: ordered-int keys of the depth extrema
   int seg_last[1024];  // ordered path; cull: list of surviving super-chunks
   uint2 chunk_desc[kDescShared];  // cull: candidate chunk descriptors (the rest spill to the global chunk list)
 };
@@ -1214,6 +1218,94 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// accuracy terms (ASSCPP_EVAL_ACCURACY): occlusion_culling.cpp:445-475, 505-513, 538-618
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int float_key(float f) {  // order-preserving map float -> int (for atomicMin / atomicMax)
+  int k = __float_as_int(f);
+  return k >= 0 ? k : k ^ 0x7fffffff;
+}
+
+struct AccLocal {
+  unsigned long long d_hi = 0, d_lo = 0, z_hi = 0, z_lo = 0;
+  float mn = INFINITY, mx = -INFINITY;
+};
+
+// value * scale (scale = 2^S, exact) split into hi * 2^32 + lo and added to integer accumulators: integer adds
+// commute, so the sum does not depend on the order in which threads visit the points
+__device__ __forceinline__ void acc_fixed(double e, double scale, unsigned long long& hi, unsigned long long& lo) {
+  const double v = __dmul_rn(e, scale);
+  const unsigned long long h = __double2ull_rz(__dmul_rn(v, 2.3283064365386963e-10));  // v * 2^-32
+  hi += h;
+  lo += __double2ull_rz(__dsub_rn(v, __dmul_rn((double)h, 4294967296.0)));
+}
+
+// one visible point: depth = x of pointCloudViewportTransform (translate, rotate about z, rotate about y; every
+// stage in double on float32 inputs and narrowed to float32, transformPointMatVec :521-531), then the two error
+// terms 0.0000285 * val * val of calcAvgAccuracy (:452, :469)
+__device__ __forceinline__ void acc_point(const ViewTrig& tr, double sc_d, double sc_z, float px, float py, float pz,
+                                          AccLocal& a) {
+  const float a0 = (float)__dadd_rn((double)px, tr.t[0]);
+  const float a1 = (float)__dadd_rn((double)py, tr.t[1]);
+  const float a2 = (float)__dadd_rn((double)pz, tr.t[2]);
+  const float b0 = (float)__dadd_rn(__dmul_rn(tr.cz, (double)a0), __dmul_rn(-tr.sz, (double)a1));
+  const float b2 = a2;
+  const float depth = (float)__dadd_rn(__dmul_rn(tr.cy, (double)b0), __dmul_rn(tr.sy, (double)b2));
+  const double val = (double)depth;
+  acc_fixed(__dmul_rn(__dmul_rn(0.0000285, val), val), sc_d, a.d_hi, a.d_lo);
+  const double vz = (double)pz;
+  acc_fixed(__dmul_rn(__dmul_rn(0.0000285, vz), vz), sc_z, a.z_hi, a.z_lo);
+  a.mn = fminf(a.mn, depth);
+  a.mx = fmaxf(a.mx, depth);
+}
+
+__device__ __forceinline__ void acc_commit(ViewShared& sh, AccLocal& a) {
+  for (int o = 16; o; o >>= 1) {
+    a.d_hi += __shfl_xor_sync(0xffffffffu, a.d_hi, o);
+    a.d_lo += __shfl_xor_sync(0xffffffffu, a.d_lo, o);
+    a.z_hi += __shfl_xor_sync(0xffffffffu, a.z_hi, o);
+    a.z_lo += __shfl_xor_sync(0xffffffffu, a.z_lo, o);
+    a.mn = fminf(a.mn, __shfl_xor_sync(0xffffffffu, a.mn, o));
+    a.mx = fmaxf(a.mx, __shfl_xor_sync(0xffffffffu, a.mx, o));
+  }
+  if ((threadIdx.x & 31) == 0 && (a.d_hi | a.d_lo | a.z_hi | a.z_lo | (a.mn <= a.mx))) {
+    atomicAdd(&sh.acc[0], a.d_hi); atomicAdd(&sh.acc[1], a.d_lo);
+    atomicAdd(&sh.acc[2], a.z_hi); atomicAdd(&sh.acc[3], a.z_lo);
+    atomicMin(&sh.acc_min, float_key(a.mn));
+    atomicMax(&sh.acc_max, float_key(a.mx));
+  }
+}
+
+// pointCloudViewportTransform constants from device-resident poses (asscpp_eval_batch_device).  The host path
+// computes them with libm instead (abi.cu): CUDA's double asin / atan2 / sin / cos may differ from libm in the
+// last ulp.
+__global__ void trig_kernel(const double* __restrict__ poses, int64_t nviews, ViewTrig* __restrict__ out) {
+  int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nviews) return;
+  const double* ps = poses + 7 * v;
+  double x = ps[3], y = ps[4], z = ps[5], w = ps[6];
+  double d = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)), __dmul_rn(w, w));
+  double s = __ddiv_rn(2.0, d);
+  double xs = __dmul_rn(x, s), ys = __dmul_rn(y, s), zs = __dmul_rn(z, s);
+  double wy = __dmul_rn(w, ys), wz = __dmul_rn(w, zs);
+  double xy = __dmul_rn(x, ys), xz = __dmul_rn(x, zs);
+  double yy = __dmul_rn(y, ys), zz = __dmul_rn(z, zs);
+  double r00 = __dsub_rn(1.0, __dadd_rn(yy, zz)), r10 = __dadd_rn(xy, wz), r20 = __dsub_rn(xz, wy);
+  double yaw, pitch;
+  if (fabs(r20) >= 1) {
+    yaw = 0;
+    pitch = r20 < 0 ? 1.5707963267948966 : -1.5707963267948966;
+  } else {
+    pitch = -asin(r20);
+    yaw = atan2(__ddiv_rn(r10, cos(pitch)), __ddiv_rn(r00, cos(pitch)));
+  }
+  ViewTrig t;
+  t.t[0] = -ps[0]; t.t[1] = -ps[1]; t.t[2] = -ps[2];
+  t.cz = cos(-yaw); t.sz = sin(-yaw); t.cy = cos(-pitch); t.sy = sin(-pitch);
+  t.pad = 0;
+  out[v] = t;
+}
+
 __device__ __forceinline__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
   if (threadIdx.x < 24) sh.planes[threadIdx.x] = vd.planes[threadIdx.x];
   if (threadIdx.x < 3) {
@@ -1226,6 +1318,8 @@ __device__ __forceinline__ void reset_view(ViewShared& sh, const ViewDev& vd, in
     sh.cand_state = 0; sh.chunk_count = 0; sh.chunk_next = 0; sh.super_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.ray_count = 0;
     sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
     sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
+    sh.acc[0] = sh.acc[1] = sh.acc[2] = sh.acc[3] = 0;
+    sh.acc_min = 0x7f800000; sh.acc_max = (int)0xff800000 ^ 0x7fffffff;  // float_key(+inf), float_key(-inf)
     sh.words = 0; sh.use_smem = 1;
     sh.g.cells = 0;
   }
@@ -1238,6 +1332,13 @@ __device__ __forceinline__ void write_result(const EvalArgs& A, const ViewShared
   r.cells = sh.survivors ? (uint64_t)sh.g.cells : 0;
   r.steps = sh.steps; r.vis_hash = sh.vis_hash; r.surv_hash = sh.surv_hash;
   A.results[v] = r;
+  if (A.acc) {
+    AccRaw a;
+    a.d_hi = sh.acc[0]; a.d_lo = sh.acc[1]; a.z_hi = sh.acc[2]; a.z_lo = sh.acc[3];
+    a.min_key = sh.acc_min; a.max_key = sh.acc_max;
+    a.visible = sh.visible; a.pad = 0;
+    A.acc[v] = a;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1317,6 +1418,25 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
       }
     }
     __syncthreads();
+    if (A.acc && sh.visible && !sh.carry) {
+      // P4c: accuracy terms of the visible points (occlusion_culling.cpp:445-475, 505-513)
+      const ViewTrig tr = A.trig[v];
+      AccLocal acc;
+      const unsigned nvis = sh.vis_count;
+      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x) {
+        const uint32_t uf = vis_list[e];
+        if (uf == 0xffffffffu) continue;
+        const uint32_t u = uf & kVoxMask;
+        const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
+        for (uint32_t pos = pb; pos < pe; ++pos) {
+          const float4 p = m.pts[pos];
+          if (!(uf & kVoxInside) && !point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
+          acc_point(tr, A.acc_scale_d, A.acc_scale_z, p.x, p.y, p.z, acc);
+        }
+      }
+      acc_commit(sh, acc);
+      __syncthreads();
+    }
     if (!m.cov_same && sh.visible) {
       for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
     }
@@ -1405,6 +1525,9 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
       int st = state;
       unsigned vis = 0, gain_p = 0, gain_v = 0, carry = 0;
       unsigned long long vhash = 0;
+      AccLocal acc;
+      ViewTrig tr;
+      if (A.acc && pass == 0) tr = A.trig[v];
       for (int64_t j = j0; j < j1; ++j) {
         uint32_t pos = (uint32_t)m.pos_of[j];
         float4 p = m.pts[pos];
@@ -1418,6 +1541,7 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
             ++vis;
             if (!A.covered.pts || !bit_test(A.covered.pts, pos)) ++gain_p;
             if (want_hash) vhash += mix64((uint64_t)j);
+            if (A.acc) acc_point(tr, A.acc_scale_d, A.acc_scale_z, p.x, p.y, p.z, acc);
             uint32_t old = atomicOr(&cov_scratch[id >> 5], bit);
             if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
           } else {
@@ -1427,6 +1551,7 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
         }
       }
       if (pass == 0) {
+        if (A.acc) acc_commit(sh, acc);
         if (vis) atomicAdd(&sh.visible, vis);
         if (gain_p) atomicAdd(&sh.gain_p, gain_p);
         if (gain_v) atomicAdd(&sh.gain_v, gain_v);
@@ -1538,6 +1663,10 @@ void launch_planes(const double* d_poses, int64_t nviews, const FrustumConst& fc
   int threads = 128;
   int blocks = (int)((nviews + threads - 1) / threads);
   planes_kernel<<<blocks, threads, 0, s>>>(d_poses, nviews, fc, views);
+}
+void launch_trig(const double* d_poses, int64_t nviews, ViewTrig* out, cudaStream_t s) {
+  if (nviews <= 0) return;
+  trig_kernel<<<(int)((nviews + 127) / 128), 128, 0, s>>>(d_poses, nviews, out);
 }
 void launch_eval(const EvalArgs& a, int ctas, int threads, size_t smem_bytes, cudaStream_t s) {
   eval_views_kernel<<<ctas, threads, smem_bytes, s>>>(a);

@@ -86,6 +86,39 @@ double frustum_max_extent(const AsscppParams& p) {
   return std::max(fd, cross);
 }
 
+// <tf Matrix3x3::getRPY> (getEulerYPR, solution 1) on the <tf Matrix3x3::setRotation> matrix of the pose's
+// quaternion, as called at occlusion_culling.cpp:497-500 and :558-561.  Host libm, double.
+void pose_rpy_host(const double pose[7], double rpy[3]) {
+  const double x = pose[3], y = pose[4], z = pose[5], w = pose[6];
+  const double d = x * x + y * y + z * z + w * w, s = 2.0 / d;
+  const double xs = x * s, ys = y * s, zs = z * s, wx = w * xs, wy = w * ys, wz = w * zs;
+  const double xx = x * xs, xy = x * ys, xz = x * zs, yy = y * ys, yz = y * zs, zz = z * zs;
+  const double r00 = 1.0 - (yy + zz), r01 = xy - wz, r02 = xz + wy, r10 = xy + wz, r20 = xz - wy, r21 = yz + wx,
+               r22 = 1.0 - (xx + yy);
+  const double pi = 3.1415926535897932384626433832795029;
+  double yaw, pitch, roll;
+  if (std::fabs(r20) >= 1) {
+    yaw = 0;
+    if (r20 < 0) { pitch = pi / 2.0; roll = std::atan2(r01, r02); }
+    else { pitch = -pi / 2.0; roll = std::atan2(-r01, -r02); }
+  } else {
+    pitch = -std::asin(r20);
+    roll = std::atan2(r21 / std::cos(pitch), r22 / std::cos(pitch));
+    yaw = std::atan2(r10 / std::cos(pitch), r00 / std::cos(pitch));
+  }
+  rpy[0] = roll; rpy[1] = pitch; rpy[2] = yaw;
+}
+
+void viewport_trig_host(const double pose[7], ViewTrig* out) {
+  double rpy[3];
+  pose_rpy_host(pose, rpy);
+  const double yaw = -1 * rpy[2], pitch = -1 * rpy[1];  // occlusion_culling.cpp:562, 579
+  out->t[0] = -1 * pose[0]; out->t[1] = -1 * pose[1]; out->t[2] = -1 * pose[2];  // :545
+  out->cz = std::cos(yaw); out->sz = std::sin(yaw);
+  out->cy = std::cos(pitch); out->sy = std::sin(pitch);
+  out->pad = 0;
+}
+
 void frustum_planes_host(const AsscppParams& p, const double pose[7], float planes[24], float origin[3],
                          float corners[24]) {
   // occlusion_culling.cpp:271-290 (tf::Matrix3x3(q) in double, cast to float) then

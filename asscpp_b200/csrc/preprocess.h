@@ -30,6 +30,9 @@ int preprocess_model(const float* xyz, int64_t n, const AsscppParams& p, ModelHo
 FrustumConst frustum_const(const AsscppParams& p);
 void frustum_planes_host(const AsscppParams& p, const double pose[7], float planes[24], float origin[3],
                          float corners[24]);
+// pointCloudViewportTransform constants (occlusion_culling.cpp:545-584) with the host's libm
+void viewport_trig_host(const double pose[7], ViewTrig* out);
+void pose_rpy_host(const double pose[7], double rpy[3]);
 // largest extent of the frustum along any axis over all orientations (bound for grid scratch)
 double frustum_max_extent(const AsscppParams& p);
 

@@ -85,8 +85,25 @@ enum {
 enum {
   ASSCPP_EVAL_HASH = 1u,        /* also compute vis_hash / surv_hash                               */
   ASSCPP_EVAL_BRUTE = 2u,       /* no bucket pre-cull: stream every point for every view           */
-  ASSCPP_EVAL_FORCE_GLOBAL = 4u /* keep every per-view grid in global memory (test / profiling)    */
+  ASSCPP_EVAL_FORCE_GLOBAL = 4u, /* keep every per-view grid in global memory (test / profiling)   */
+  ASSCPP_EVAL_ACCURACY = 8u      /* also reduce the accuracy terms of the visible set (asscpp_get_accuracy) */
 };
+
+/* Accuracy terms of one viewpoint's visible cloud (ASSCPP_EVAL_ACCURACY).
+ *   err_sum_depth / visible = OcclusionCulling::calcAvgAccuracy(cloud, pose)  (occlusion_culling.cpp:459-475)
+ *   err_sum_z     / visible = OcclusionCulling::calcAvgAccuracy(cloud)        (occlusion_culling.cpp:445-458)
+ *   depth_min / depth_max   = what SSMaxMinAccuracy folds over the search space (occlusion_culling.cpp:505-513)
+ * depth = x of pointCloudViewportTransform (:538-618), float32.  The sums are the EXACT sums of the per-point
+ * double terms 0.0000285*val*val, rounded once; the reference's left-to-right double sum differs from that by at
+ * most visible/2 ulp. */
+typedef struct AsscppViewAccuracy {
+  double err_sum_depth;
+  double err_sum_z;
+  float depth_min;   /* +inf when nothing is visible */
+  float depth_max;   /* -inf when nothing is visible */
+  uint32_t visible;
+  uint32_t reserved;
+} AsscppViewAccuracy;
 
 typedef struct AsscppCtx AsscppCtx;
 
@@ -111,6 +128,9 @@ int asscpp_eval_batch(AsscppCtx* ctx, const double* poses, int64_t nviews, int c
 int asscpp_get_results(AsscppCtx* ctx, AsscppViewResult* out, int64_t nviews); /* synchronises */
 int asscpp_get_counts(AsscppCtx* ctx, uint32_t* survivors, uint32_t* visible, uint32_t* carry, int64_t nviews);
 int asscpp_get_gain(AsscppCtx* ctx, uint32_t* gain_pts, uint32_t* gain_vox, int64_t nviews);
+
+/* accuracy terms of the last evaluation issued with ASSCPP_EVAL_ACCURACY (synchronises) */
+int asscpp_get_accuracy(AsscppCtx* ctx, AsscppViewAccuracy* out, int64_t nviews);
 
 /* Same evaluation with device-resident poses (nviews x 7 doubles already in HBM) and results left
  * on the device (AsscppViewResult[nviews], device pointer returned).  Used by the batcher when
@@ -176,6 +196,10 @@ int asscpp_synth_views_v1(uint64_t structure_seed, uint64_t view_seed, int64_t n
 /* sspp/src/sensors.cpp:47-90 robot pose -> sensor pose (batcher input), host, double */
 int asscpp_robot2sensor(const double robot_pose[7], const double offset[3], const double rpy[3],
                         double sensor_pose[7]);
+/* tf::Matrix3x3(q).getRPY(roll, pitch, yaw) of a pose, as used by occlusion_culling.cpp:497-500, 558-561 (host) */
+int asscpp_pose_rpy(const double pose[7], double rpy[3]);
+/* OcclusionCulling::pointCloudViewportTransform (occlusion_culling.cpp:538-618), host: n x xyz float32 -> same */
+int asscpp_viewport_transform(const double pose[7], const float* xyz, int64_t n, float* xyz_out);
 /* frustum planes (l r t b f n) and camera origin of a pose: frustum_culling.cpp:75-141 */
 int asscpp_frustum_planes(const AsscppParams* p, const double pose[7], float planes[24], float origin[3]);
 

@@ -513,6 +513,64 @@ void mat_to_quat(const double m[3][3], double q[4]) {
   q[0] = t[0]; q[1] = t[1]; q[2] = t[2]; q[3] = t[3];
 }
 
+
+// <tf Matrix3x3::getRPY> = getEulerYPR(yaw, pitch, roll, solution 1) on the matrix of <tf Matrix3x3::setRotation>;
+// called at occlusion_culling.cpp:497-500 and :558-561.  Restated from the published tf algorithm (tf is not
+// vendored under /root/reference).  All double, libm asin / atan2 / cos.
+void pose_rpy(const double pose[7], double rpy[3]) {
+  double R[3][3];
+  quat_to_mat(pose + 3, R);
+  const double pi = 3.1415926535897932384626433832795029;  // TFSIMD_PI
+  double yaw, pitch, roll;
+  if (std::fabs(R[2][0]) >= 1) {
+    yaw = 0;
+    if (R[2][0] < 0) {
+      pitch = pi / 2.0;
+      roll = std::atan2(R[0][1], R[0][2]);
+    } else {
+      pitch = -pi / 2.0;
+      roll = std::atan2(-R[0][1], -R[0][2]);
+    }
+  } else {
+    pitch = -std::asin(R[2][0]);
+    roll = std::atan2(R[2][1] / std::cos(pitch), R[2][2] / std::cos(pitch));
+    yaw = std::atan2(R[1][0] / std::cos(pitch), R[0][0] / std::cos(pitch));
+  }
+  rpy[0] = roll; rpy[1] = pitch; rpy[2] = yaw;
+}
+
+// OcclusionCulling::pointCloudViewportTransform (occlusion_culling.cpp:538-618) for one point: translate by
+// -camera position, rotate about z by -yaw, about y by -pitch.  Every stage goes through transformPointMatVec
+// (:521-531): double arithmetic on float32 inputs (geometry_msgs::Point32), result narrowed back to float32.
+struct ViewportXf {
+  double t[3];          // cameraPoseTrans (:545)
+  double cz, sz, cy, sy;  // cos / sin of yaw' = -yaw (:562-569) and of pitch' = -pitch (:579-584)
+};
+ViewportXf viewport_xf(const double pose[7]) {
+  ViewportXf x;
+  x.t[0] = -1 * pose[0]; x.t[1] = -1 * pose[1]; x.t[2] = -1 * pose[2];
+  double rpy[3];
+  pose_rpy(pose, rpy);
+  const double yaw = -1 * rpy[2], pitch = -1 * rpy[1];
+  x.cz = std::cos(yaw); x.sz = std::sin(yaw);
+  x.cy = std::cos(pitch); x.sy = std::sin(pitch);
+  return x;
+}
+inline void viewport_point(const ViewportXf& x, const f32 in[3], f32 out[3]) {
+  // stage 1 (:594): identity rotation + translation; 1*a + 0*b + 0*c + t evaluated left to right in double
+  f32 a0 = (f32)(1.0 * in[0] + 0.0 * in[1] + 0.0 * in[2] + x.t[0]);
+  f32 a1 = (f32)(0.0 * in[0] + 1.0 * in[1] + 0.0 * in[2] + x.t[1]);
+  f32 a2 = (f32)(0.0 * in[0] + 0.0 * in[1] + 1.0 * in[2] + x.t[2]);
+  // stage 2 (:598): rotZ = [c -s 0; s c 0; 0 0 1], no translation
+  f32 b0 = (f32)(x.cz * a0 + (-1 * x.sz) * a1 + 0.0 * a2 + 0.0);
+  f32 b1 = (f32)(x.sz * a0 + x.cz * a1 + 0.0 * a2 + 0.0);
+  f32 b2 = (f32)(0.0 * a0 + 0.0 * a1 + 1.0 * a2 + 0.0);
+  // stage 3 (:602): rotY = [c 0 s; 0 1 0; -s 0 c]
+  out[0] = (f32)(x.cy * b0 + 0.0 * b1 + x.sy * b2 + 0.0);
+  out[1] = (f32)(0.0 * b0 + 1.0 * b1 + 0.0 * b2 + 0.0);
+  out[2] = (f32)((-1 * x.sy) * b0 + 0.0 * b1 + x.cy * b2 + 0.0);
+}
+
 }  // namespace
 
 struct OrcCtx { Ctx c; };
@@ -667,6 +725,36 @@ void orc_robot2sensor(const double robot_pose[7], const double offset[3], const 
   mat_to_quat(N, q);
   sensor_pose[0] = T[0]; sensor_pose[1] = T[1]; sensor_pose[2] = T[2];
   sensor_pose[3] = q[0]; sensor_pose[4] = q[1]; sensor_pose[5] = q[2]; sensor_pose[6] = q[3];
+}
+
+void orc_pose_rpy(const double pose[7], double rpy[3]) { pose_rpy(pose, rpy); }
+
+void orc_viewport_transform(const double pose[7], const float* xyz, int64_t n, float* out) {
+  const ViewportXf x = viewport_xf(pose);
+  for (int64_t i = 0; i < n; ++i) viewport_point(x, xyz + 3 * i, out + 3 * i);
+}
+
+void orc_accuracy_idx(const OrcCtx* c, const double pose[7], const int32_t* idx, int64_t n, double* err_sum_depth,
+                      double* err_sum_z, float* depth_min, float* depth_max) {
+  // calcAvgAccuracy(cloud, pose) occlusion_culling.cpp:459-475 and calcAvgAccuracy(cloud) :445-458: sums run over
+  // the cloud in its own order (extractVisibleSurface returns ascending original index); the depth extrema are the
+  // quantities SSMaxMinAccuracy folds over the whole search space (:505-513)
+  const ViewportXf x = viewport_xf(pose);
+  double sd = 0, sz = 0;
+  float lo = INFINITY, hi = -INFINITY;
+  for (int64_t k = 0; k < n; ++k) {
+    const f32* p = c->c.xyz.data() + 3 * (int64_t)idx[k];
+    f32 q[3];
+    viewport_point(x, p, q);
+    double val = q[0];
+    double e = 0.0000285 * val * val;  // :469
+    sd += e;
+    double vz = p[2];
+    sz += 0.0000285 * vz * vz;         // :452
+    lo = std::min(lo, q[0]);
+    hi = std::max(hi, q[0]);
+  }
+  *err_sum_depth = sd; *err_sum_z = sz; *depth_min = lo; *depth_max = hi;
 }
 
 }  // extern "C"

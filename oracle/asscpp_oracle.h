@@ -102,6 +102,15 @@ int64_t orc_popcount(const uint64_t* bits, int64_t nbits);
 void orc_robot2sensor(const double robot_pose[7], const double offset[3], const double rpy[3],
                       double sensor_pose[7]);
 
+/* tf::Matrix3x3(q).getRPY(roll, pitch, yaw) as called at occlusion_culling.cpp:497-500 / :558-561 */
+void orc_pose_rpy(const double pose[7], double rpy[3]);
+/* OcclusionCulling::pointCloudViewportTransform, occlusion_culling.cpp:538-618 (n x xyz float32 -> same) */
+void orc_viewport_transform(const double pose[7], const float* xyz, int64_t n, float* out);
+/* calcAvgAccuracy(cloud, pose) :459-475 (err_sum_depth / n) and calcAvgAccuracy(cloud) :445-458 (err_sum_z / n)
+ * over the model points idx[0..n) in that order, plus the depth extrema of SSMaxMinAccuracy :505-513 */
+void orc_accuracy_idx(const OrcCtx* c, const double pose[7], const int32_t* idx, int64_t n, double* err_sum_depth,
+                      double* err_sum_z, float* depth_min, float* depth_max);
+
 /* 64-bit mix used for the order-independent set hashes (sum of mix(idx)) */
 uint64_t orc_mix64(uint64_t x);
 

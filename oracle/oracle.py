@@ -87,6 +87,12 @@ def lib():
         L.orc_popcount.restype = i64
         L.orc_robot2sensor.argtypes = [f64p, f64p, f64p, f64p]
         L.orc_robot2sensor.restype = None
+        L.orc_pose_rpy.argtypes = [f64p, f64p]
+        L.orc_pose_rpy.restype = None
+        L.orc_viewport_transform.argtypes = [f64p, f32p, i64, f32p]
+        L.orc_viewport_transform.restype = None
+        L.orc_accuracy_idx.argtypes = [vp, f64p, i32p, i64, f64p, f64p, f32p, f32p]
+        L.orc_accuracy_idx.restype = None
         L.orc_mix64.argtypes = [C.c_uint64]
         L.orc_mix64.restype = C.c_uint64
         _lib = L
@@ -177,8 +183,36 @@ class Oracle:
         idx = np.ascontiguousarray(idx, dtype=np.int32)
         return float(self.L.orc_coverage_percent_idx(self.h, _p(idx, C.c_int32), idx.shape[0]))
 
+    def accuracy_idx(self, pose, idx):
+        """(err_sum_depth, err_sum_z, depth_min, depth_max) over the points idx in that order:
+        calcAvgAccuracy(cloud, pose) = err_sum_depth / n, calcAvgAccuracy(cloud) = err_sum_z / n."""
+        pose = np.ascontiguousarray(pose, np.float64)
+        idx = np.ascontiguousarray(idx, np.int32)
+        sd, sz = C.c_double(0), C.c_double(0)
+        lo, hi = C.c_float(0), C.c_float(0)
+        lib().orc_accuracy_idx(self.h, _p(pose, C.c_double), _p(idx, C.c_int32), len(idx), C.byref(sd), C.byref(sz),
+                               C.byref(lo), C.byref(hi))
+        return sd.value, sz.value, lo.value, hi.value
+
     def coverage_percent_vox(self, covered_vox):
         return float(self.L.orc_coverage_percent_vox(self.h, _p(covered_vox, C.c_uint64)))
+
+
+def pose_rpy(pose):
+    """tf::Matrix3x3(q).getRPY as used by occlusion_culling.cpp:497-500."""
+    pose = np.ascontiguousarray(pose, np.float64)
+    out = np.zeros(3, np.float64)
+    lib().orc_pose_rpy(_p(pose, C.c_double), _p(out, C.c_double))
+    return out
+
+
+def viewport_transform(pose, xyz):
+    """pointCloudViewportTransform, occlusion_culling.cpp:538-618."""
+    pose = np.ascontiguousarray(pose, np.float64)
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    out = np.zeros_like(xyz)
+    lib().orc_viewport_transform(_p(pose, C.c_double), _p(xyz, C.c_float), len(xyz), _p(out, C.c_float))
+    return out
 
 
 def robot2sensor(robot_pose, offset, rpy):

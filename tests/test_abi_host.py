@@ -94,3 +94,21 @@ def test_synth_generators_deterministic(lib_built):
 
 SYNTH_POINT_DIGEST = 3175316270458
 SYNTH_VIEW_DIGEST = 1637634120653
+
+
+def test_viewport_transform_and_rpy_equal_oracle(lib_built, oracle_mod, etihad, space_2p5):
+    """pointCloudViewportTransform / getRPY (occlusion_culling.cpp:538-618) on the host side of the C ABI are
+    bit-identical to the oracle's restatement, and the transformed x is the depth along the camera's view axis."""
+    import asscpp_b200 as A
+    xyz, _ = etihad
+    pts = xyz[::997]
+    for pose in np.concatenate([space_2p5["cam0"][::97], space_2p5["cam1"][::89]]):
+        assert np.array_equal(A.pose_rpy(pose), oracle_mod.pose_rpy(pose))
+        a = A.viewport_transform(pose, pts)
+        b = oracle_mod.viewport_transform(pose, pts)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+        x, y, z, w = pose[3:]
+        n = x * x + y * y + z * z + w * w
+        view = np.array([1 - 2 * (y * y + z * z) / n, 2 * (x * y + w * z) / n, 2 * (x * z - w * y) / n])
+        depth = (pts.astype(np.float64) - pose[:3]) @ view
+        assert np.abs(a[:, 0] - depth).max() < 2e-5  # float32 stages over coordinates of tens of metres

@@ -309,3 +309,74 @@ def test_nccl_legs_two_gpus():
                           "--master-addr", "127.0.0.1", "--master-port", "29617",
                           os.path.join(root, "tools", "nccl_check.py")], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0 and "OK" in out.stdout, out.stdout + out.stderr
+
+
+@pytest.mark.gpu
+def test_accuracy_terms(A, oracle_mod, etihad_ctx, etihad_oracle, etihad, space_2p5):
+    """§8f rank 1: calcAvgAccuracy (both overloads) and the depth extrema SSMaxMinAccuracy folds
+    (occlusion_culling.cpp:445-520) per view.  Depths are float32 and bit-exact (host libm feeds the same
+    sines / cosines to both sides); the GPU sums are the exact sums of the per-point double terms rounded once,
+    the reference's left-to-right double sum may differ from that by at most visible/2 ulp: tolerance
+    visible * 2^-53 relative, written here."""
+    O = oracle_mod
+    xyz, _ = etihad
+    poses = np.ascontiguousarray(np.concatenate([space_2p5["cam0"][400:900:3], space_2p5["cam1"][400:900:3]]))
+    res = etihad_ctx.eval_batch(poses, flags=A.EVAL_ACCURACY | A.EVAL_HASH)
+    acc = etihad_ctx.accuracy(len(poses))
+    assert np.array_equal(acc["visible"], res["visible"])
+    checked = 0
+    for v, pose in enumerate(poses):
+        r = etihad_oracle.eval_view(pose)
+        vis = r["visible"]
+        assert len(vis) == int(res["visible"][v])
+        if len(vis) == 0:
+            assert acc["err_sum_depth"][v] == 0 and acc["err_sum_z"][v] == 0
+            assert np.isposinf(acc["depth_min"][v]) and np.isneginf(acc["depth_max"][v])
+            continue
+        sd, sz, lo, hi = etihad_oracle.accuracy_idx(pose, vis)
+        tol = len(vis) * 2.0 ** -53
+        assert abs(acc["err_sum_depth"][v] - sd) <= tol * sd
+        assert abs(acc["err_sum_z"][v] - sz) <= tol * sz
+        assert np.float32(lo) == acc["depth_min"][v] and np.float32(hi) == acc["depth_max"][v]
+        # the GPU value is the exact sum: compare against exact rational arithmetic on the oracle's depths
+        if checked < 6:
+            from fractions import Fraction
+            t = O.viewport_transform(pose, xyz[vis])
+            ex = sum(Fraction(0.0000285 * float(d) * float(d)) for d in t[:, 0])
+            assert acc["err_sum_depth"][v] == float(ex)
+        checked += 1
+    assert checked > 50
+    # run-to-run determinism of the integer accumulation
+    etihad_ctx.eval_batch(poses, flags=A.EVAL_ACCURACY)
+    acc2 = etihad_ctx.accuracy(len(poses))
+    assert acc.tobytes() == acc2.tobytes()
+    # SSMaxMinAccuracy over this search space (occlusion_culling.cpp:486-520), including its initial values
+    mx, mn = np.finfo(np.float64).tiny, np.finfo(np.float64).max
+    for v in range(len(poses)):
+        if acc["visible"][v]:
+            mx = max(mx, float(acc["depth_max"][v]))
+            mn = min(mn, float(acc["depth_min"][v]))
+    assert 0.7 < mn < mx < 7.5
+
+
+@pytest.mark.gpu
+def test_accuracy_terms_synthetic_fine_grid(A, oracle_mod):
+    """Same bar on the synthetic structure at 0.05 m (inside-chunk voxels, cut voxels, shared and global grids)."""
+    O = oracle_mod
+    xyz = A.synth_structure(300_000)
+    poses = A.synth_views(96)
+    ctx = A.CoverageContext(xyz, A.default_params(leaf=0.05, cov_leaf=0.5))
+    orc = O.Oracle(xyz, O.make_params(leaf=0.05, cov_leaf=0.5))
+    for flags in (A.EVAL_ACCURACY, A.EVAL_ACCURACY | A.EVAL_FORCE_GLOBAL, A.EVAL_ACCURACY | A.EVAL_BRUTE):
+        res = ctx.eval_batch(poses, flags=flags)
+        acc = ctx.accuracy(len(poses))
+        for v, pose in enumerate(poses):
+            vis = orc.eval_view(pose)["visible"]
+            assert len(vis) == int(res["visible"][v]) == int(acc["visible"][v])
+            if len(vis) == 0:
+                continue
+            sd, sz, lo, hi = orc.accuracy_idx(pose, vis)
+            tol = len(vis) * 2.0 ** -53
+            assert abs(acc["err_sum_depth"][v] - sd) <= tol * sd and abs(acc["err_sum_z"][v] - sz) <= tol * sz + 1e-300
+            assert np.float32(lo) == acc["depth_min"][v] and np.float32(hi) == acc["depth_max"][v]
+    ctx.close()

@@ -205,3 +205,29 @@ def test_gain_against_covered_set(oracle_mod, etihad, space_2p5):
     cp2, cv2 = cp.copy(), cv.copy()
     o.accumulate(poses[:20], cp2, cv2, min_visible=5)
     assert np.array_equal(cp, cp2) and np.array_equal(cv, cv2)
+
+
+def test_accuracy_terms_literal(oracle_mod, etihad, space_2p5):
+    """calcAvgAccuracy (occlusion_culling.cpp:445-475) restated literally in numpy float64 on the oracle's
+    own viewport transform equals orc_accuracy_idx bit for bit (same left-to-right double sum)."""
+    O = oracle_mod
+    xyz, _ = etihad
+    o = O.Oracle(xyz)
+    seen = 0
+    for pose in space_2p5["cam1"][600:640:3]:
+        vis = o.eval_view(pose)["visible"]
+        if len(vis) == 0:
+            continue
+        seen += 1
+        sd, sz, lo, hi = o.accuracy_idx(pose, vis)
+        t = O.viewport_transform(pose, xyz[vis])
+        ed = 0.0
+        ez = 0.0
+        for k in range(len(vis)):
+            val = float(t[k, 0])
+            ed += 0.0000285 * val * val
+            vz = float(xyz[vis[k], 2])
+            ez += 0.0000285 * vz * vz
+        assert sd == ed and sz == ez
+        assert lo == t[:, 0].min() and hi == t[:, 0].max()
+    assert seen >= 3
