@@ -13,11 +13,13 @@
 // There is no CPU fallback: construction throws std::runtime_error when no sm_100 GPU is usable.
 #pragma once
 #include <cstring>
+#include <limits>
 #include <stdexcept>
 #include <string>
 #include <vector>
 
 #include <geometry_msgs/Pose.h>
+#include <geometry_msgs/PoseArray.h>
 #include <pcl/io/pcd_io.h>
 #include <pcl/point_types.h>
 
@@ -83,6 +85,64 @@ class OcclusionCulling {
     return pct;
   }
 
+  // occlusion_culling.cpp:445-458: raw z of the given cloud as depth (as the reference does)
+  double calcAvgAccuracy(pcl::PointCloud<pcl::PointXYZ> pointCloud) {
+    double errorSum = 0;
+    for (size_t j = 0; j < pointCloud.points.size(); ++j) {
+      double val = pointCloud.points[j].z;
+      double pointError = 0.0000285 * val * val;
+      errorSum += pointError;
+    }
+    return errorSum / pointCloud.points.size();
+  }
+  // occlusion_culling.cpp:459-475: depth = x after pointCloudViewportTransform
+  double calcAvgAccuracy(pcl::PointCloud<pcl::PointXYZ> pointCloud, geometry_msgs::Pose cameraPose) {
+    pcl::PointCloud<pcl::PointXYZ> t = pointCloudViewportTransform(pointCloud, cameraPose);
+    double errorSum = 0;
+    for (size_t j = 0; j < t.points.size(); ++j) {
+      double val = t.points[j].x;
+      double pointError = 0.0000285 * val * val;
+      errorSum += pointError;
+    }
+    return errorSum / t.points.size();
+  }
+  // occlusion_culling.cpp:538-618 (host arithmetic of the C ABI, same as the device path)
+  pcl::PointCloud<pcl::PointXYZ> pointCloudViewportTransform(pcl::PointCloud<pcl::PointXYZ> pointCloud,
+                                                             geometry_msgs::Pose cameraPose) {
+    double p[7];
+    pack(cameraPose, p);
+    std::vector<float> in(3 * pointCloud.points.size()), out(3 * pointCloud.points.size());
+    for (size_t i = 0; i < pointCloud.points.size(); ++i) {
+      in[3 * i] = pointCloud.points[i].x; in[3 * i + 1] = pointCloud.points[i].y; in[3 * i + 2] = pointCloud.points[i].z;
+    }
+    check(asscpp_viewport_transform(p, in.data(), (int64_t)pointCloud.points.size(), out.data()));
+    pcl::PointCloud<pcl::PointXYZ> posArray;
+    posArray.points.resize(pointCloud.points.size());
+    for (size_t i = 0; i < pointCloud.points.size(); ++i) {
+      posArray.points[i].x = out[3 * i]; posArray.points[i].y = out[3 * i + 1]; posArray.points[i].z = out[3 * i + 2];
+    }
+    return posArray;
+  }
+  // occlusion_culling.cpp:486-520: depth extrema over the whole search space in ONE batched launch; keeps the
+  // reference's initial values (max starts at numeric_limits<double>::min(), the smallest positive double)
+  void SSMaxMinAccuracy(std::vector<geometry_msgs::PoseArray> sensorsPoses) {
+    std::vector<geometry_msgs::Pose> flat;
+    for (size_t i = 0; i < sensorsPoses.size(); ++i)
+      flat.insert(flat.end(), sensorsPoses[i].poses.begin(), sensorsPoses[i].poses.end());
+    std::vector<AsscppViewResult> res;
+    std::vector<AsscppViewAccuracy> acc;
+    evalBatch(flat, res, -1, ASSCPP_EVAL_ACCURACY, &acc);
+    double max = std::numeric_limits<double>::min(), min = std::numeric_limits<double>::max();
+    for (size_t k = 0; k < acc.size(); ++k) {
+      if (!acc[k].visible) continue;
+      if ((double)acc[k].depth_max > max) max = acc[k].depth_max;
+      if ((double)acc[k].depth_min < min) min = acc[k].depth_min;
+    }
+    maxAccuracyError = 0.0000285 * max * max;
+    minAccuracyError = 0.0000285 * min * min;
+    AccuracyMaxSet = true;
+  }
+
   // ---- additions (non-breaking) -----------------------------------------------------------------
   // ascending original indices of extractVisibleSurface's cloud
   void visibleIndices(const geometry_msgs::Pose& location, std::vector<int32_t>& idx) {
@@ -95,12 +155,17 @@ class OcclusionCulling {
   }
   // one launch for a whole batch of viewpoints; covered_set = -1 scores against the empty set
   void evalBatch(const std::vector<geometry_msgs::Pose>& poses, std::vector<AsscppViewResult>& out,
-                 int covered_set = -1, uint32_t flags = 0) {
+                 int covered_set = -1, uint32_t flags = 0, std::vector<AsscppViewAccuracy>* accuracy = nullptr) {
     std::vector<double> p(7 * poses.size());
     for (size_t i = 0; i < poses.size(); ++i) pack(poses[i], &p[7 * i]);
     out.resize(poses.size());
+    if (accuracy) flags |= ASSCPP_EVAL_ACCURACY;
     check(asscpp_eval_batch(ctx_, p.data(), (int64_t)poses.size(), covered_set, flags));
     check(asscpp_get_results(ctx_, out.data(), (int64_t)poses.size()));
+    if (accuracy) {
+      accuracy->resize(poses.size());
+      check(asscpp_get_accuracy(ctx_, accuracy->data(), (int64_t)poses.size()));
+    }
   }
   AsscppCtx* context() { return ctx_; }
   static void pack(const geometry_msgs::Pose& q, double p[7]) {

@@ -59,10 +59,22 @@ class ViewpointBatcher {
   int launches_ = 0;
 };
 
+// heuristic types of cscpp/include/cscpp/coverage_path_planning_heuristic.h:72 that live on the hot path
+enum { SurfaceCoverageH = 0, SurfaceCoveragewithOrientationH = 1, SurfaceCoveragewithAccuracyH = 2 };
+
 class CoverageHeuristicB200 {
  public:
-  CoverageHeuristicB200(OcclusionCulling* oc, double coverageTarget, double coverageTolerance)
-      : oc_(oc), batcher_(oc), target_(coverageTarget), tol_(coverageTolerance) {}
+  CoverageHeuristicB200(OcclusionCulling* oc, double coverageTarget, double coverageTolerance,
+                        int heuristicType = SurfaceCoverageH)
+      : oc_(oc), batcher_(oc), target_(coverageTarget), tol_(coverageTolerance), type_(heuristicType) {}
+
+  // setMaxMinSensorAccuracy (coverage_path_planning_heuristic.cpp:399-403): needed before SurfaceCoveragewithAccuracyH
+  void setMaxMinSensorAccuracy(std::vector<geometry_msgs::PoseArray> sensorsViewsSS) {
+    oc_->SSMaxMinAccuracy(sensorsViewsSS);
+    maxDepth = std::sqrt(oc_->maxAccuracyError / 0.0000285);
+  }
+  double maxDepth = 0;
+  double accuracySum = 0;  // :497, :837
 
   ViewpointBatcher& batcher() { return batcher_; }
 
@@ -80,6 +92,19 @@ class CoverageHeuristicB200 {
     for (size_t s = 0; s < node->senPoses.size(); ++s) OcclusionCulling::pack(node->senPoses[s], &p[7 * s]);
     // visibleCloud += extractVisibleSurface(senPoses[i]) for every sensor (:439-445); union into the set (:474-480)
     oc_->check(asscpp_covered_or_views(c, node->covered_set, p.data(), (int64_t)node->senPoses.size(), -1));
+    double a = 1.0;
+    if (type_ == SurfaceCoveragewithAccuracyH && node->parent) {
+      // a = (maxAccuracyError - calcAvgAccuracy(visibleCloud)) / maxAccuracyError (:493-494, :836-838); the
+      // one-argument overload averages 0.0000285 z^2 over the concatenated sensor clouds
+      oc_->check(asscpp_eval_batch(c, p.data(), (int64_t)node->senPoses.size(), -1, ASSCPP_EVAL_ACCURACY));
+      std::vector<AsscppViewAccuracy> acc(node->senPoses.size());
+      oc_->check(asscpp_get_accuracy(c, acc.data(), (int64_t)acc.size()));
+      double sum = 0, cnt = 0;
+      for (size_t s = 0; s < acc.size(); ++s) { sum += acc[s].err_sum_z; cnt += acc[s].visible; }
+      const double avgAcc = sum / cnt;  // 0/0 = NaN for an empty cloud, as in the reference
+      accuracySum += avgAcc;
+      a = (oc_->maxAccuracyError - avgAcc) / oc_->maxAccuracyError;
+    }
     float pct = 0;
     oc_->check(asscpp_coverage_percent(c, node->covered_set, &pct));  // :482
     node->coverage = pct;
@@ -91,8 +116,29 @@ class CoverageHeuristicB200 {
       node->distance = node->parent->distance + d;         // :452
       double cgain = node->coverage - node->parent->coverage;  // :483
       node->h_value = 0; node->g_value = 0;
-      node->f_value = d != 0.0 ? node->parent->f_value + (1 / d) * cgain  // :487
-                               : node->parent->f_value + cgain;            // :780
+      double normAngle = 1.0;
+      if (d == 0.0 && type_ != SurfaceCoverageH) {
+        // <tf Quaternion::angleShortestPath> between parent and node orientation (:785-790, :813-817)
+        const geometry_msgs::Pose &pp = node->parent->pose, &pn = node->pose;
+        const double l2p = pp.orientation.x * pp.orientation.x + pp.orientation.y * pp.orientation.y +
+                           pp.orientation.z * pp.orientation.z + pp.orientation.w * pp.orientation.w;
+        const double l2n = pn.orientation.x * pn.orientation.x + pn.orientation.y * pn.orientation.y +
+                           pn.orientation.z * pn.orientation.z + pn.orientation.w * pn.orientation.w;
+        const double sq = std::sqrt(l2n * l2p);
+        const double dt = pp.orientation.x * pn.orientation.x + pp.orientation.y * pn.orientation.y +
+                          pp.orientation.z * pn.orientation.z + pp.orientation.w * pn.orientation.w;
+        const double angle = dt < 0 ? std::acos(-dt / sq) * 2.0 : std::acos(dt / sq) * 2.0;
+        normAngle = 1 - angle / (2 * M_PI);
+      }
+      if (type_ == SurfaceCoveragewithAccuracyH)
+        node->f_value = d != 0.0 ? node->parent->f_value + ((1 / d) * cgain * a)   // :512
+                                 : node->parent->f_value + a * cgain * normAngle;  // :840
+      else if (type_ == SurfaceCoveragewithOrientationH)
+        node->f_value = d != 0.0 ? node->parent->f_value + (1 / d) * cgain         // :487 (shared with SurfaceCoverageH)
+                                 : node->parent->f_value + normAngle * cgain;      // :807
+      else
+        node->f_value = d != 0.0 ? node->parent->f_value + (1 / d) * cgain  // :487
+                                 : node->parent->f_value + cgain;            // :780
     } else {
       node->distance = 0; node->h_value = 0; node->g_value = 0;
       node->f_value = node->coverage;  // root: :1232-1238
@@ -140,6 +186,7 @@ class CoverageHeuristicB200 {
   OcclusionCulling* oc_;
   ViewpointBatcher batcher_;
   double target_, tol_;
+  int type_;
 };
 
 }  // namespace SSPP

@@ -90,5 +90,30 @@ int main(int argc, char** argv) {
   int nacc = 0;
   for (size_t i = 0; i < accepted.size(); ++i) nacc += accepted[i];
   std::printf("accepted %d of %zu uncovered %.17g\n", nacc, accepted.size(), heur.uncoveredPercent(global_set));
+  // 4. accuracy terms: the two calcAvgAccuracy overloads per view and SSMaxMinAccuracy over all poses
+  oc.accumulateOcclusionFreeCloud = false;
+  for (size_t k = 0; k < poses.size(); ++k) {
+    pcl::PointCloud<pcl::PointXYZ> vis = oc.extractVisibleSurface(poses[k]);
+    if (vis.points.empty()) continue;
+    std::printf("accuracy %zu pose %.17g z %.17g\n", k, oc.calcAvgAccuracy(vis, poses[k]), oc.calcAvgAccuracy(vis));
+  }
+  geometry_msgs::PoseArray pa;
+  pa.poses = poses;
+  oc.SSMaxMinAccuracy(std::vector<geometry_msgs::PoseArray>(1, pa));
+  std::printf("ssmaxmin max %.17g min %.17g set %d\n", oc.maxAccuracyError, oc.minAccuracyError, (int)oc.AccuracyMaxSet);
+  // 5. SurfaceCoveragewithAccuracyH: one expansion from waypoint 0 (heuristic.cpp:490-513)
+  {
+    SSPP::CoverageHeuristicB200 hacc(&oc, 100.0, 1.0, SSPP::SurfaceCoveragewithAccuracyH);
+    hacc.setMaxMinSensorAccuracy(std::vector<geometry_msgs::PoseArray>(1, pa));
+    SSPP::NodeB200 r0 = nodes[0];
+    hacc.calculateHeuristic(&r0);
+    std::printf("acc_root coverage %.17g f %.17g maxDepth %.17g\n", r0.coverage, r0.f_value, hacc.maxDepth);
+    for (size_t i = 1; i < nodes.size(); ++i) {
+      SSPP::NodeB200 kid = nodes[i];
+      kid.parent = &r0;
+      hacc.calculateHeuristic(&kid);
+      std::printf("acc_child %zu coverage %.17g f %.17g\n", i, kid.coverage, kid.f_value);
+    }
+  }
   return 0;
 }

@@ -93,3 +93,43 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
     m = re.search(r"accepted (\d+) of (\d+) uncovered (\S+)", out)
     assert int(m.group(1)) == int((vis.sum(1) > 5).sum()) and int(m.group(2)) == len(rows)
     assert float(m.group(3)) == pytest.approx((o.n_cov - nvox) / o.n_cov * 100, rel=1e-12)
+    # 4. accuracy terms (occlusion_culling.cpp:445-520): the shim's host loops are the reference's loops on the same
+    #    float32 depths, so the averages are bit-identical; SSMaxMinAccuracy comes from the batched GPU extrema
+    accs = dict((int(k), (float(a), float(b))) for k, a, b in re.findall(r"accuracy (\d+) pose (\S+) z (\S+)", out))
+    dmax, dmin = np.finfo(np.float64).tiny, np.finfo(np.float64).max
+    nseen = 0
+    for k, pose in enumerate(poses):
+        vis_k = o.eval_view(pose)["visible"]
+        if len(vis_k) == 0:
+            assert k not in accs
+            continue
+        nseen += 1
+        sd, sz, lo, hi = o.accuracy_idx(pose, vis_k)
+        assert accs[k] == (sd / len(vis_k), sz / len(vis_k))
+        dmax, dmin = max(dmax, float(hi)), min(dmin, float(lo))
+    assert nseen > 0
+    m = re.search(r"ssmaxmin max (\S+) min (\S+) set 1", out)
+    assert float(m.group(1)) == 0.0000285 * dmax * dmax and float(m.group(2)) == 0.0000285 * dmin * dmin
+    # 5. SurfaceCoveragewithAccuracyH (heuristic.cpp:490-513): f = parent.f + (1/d) * c * a with
+    #    a = (maxAccuracyError - avg(0.0000285 z^2 over both sensors' visible clouds)) / maxAccuracyError.
+    #    The average comes from exact GPU sums; the reference's running double sum may differ by n/2 ulp.
+    max_err = 0.0000285 * dmax * dmax
+    m = re.search(r"acc_root coverage (\S+) f (\S+) maxDepth (\S+)", out)
+    cov0 = pct(set(vox[0].tolist()))
+    assert float(m.group(1)) == cov0 and float(m.group(2)) == cov0
+    assert float(m.group(3)) == pytest.approx(np.sqrt(max_err / 0.0000285), rel=1e-15)
+    kids = re.findall(r"acc_child (\d+) coverage (\S+) f (\S+)", out)
+    assert len(kids) == len(rows) - 1
+    for i, c_s, f_s in kids:
+        i = int(i)
+        both = np.concatenate([o.eval_view(poses[2 * i])["visible"], o.eval_view(poses[2 * i + 1])["visible"]])
+        cov_i = pct(set(vox[0].tolist()) | set(vox[i].tolist()))
+        assert float(c_s) == cov_i
+        d = float(np.linalg.norm(pos[i] - pos[0]))
+        if len(both) == 0:
+            assert np.isnan(float(f_s))
+            continue
+        z = xyz[both, 2].astype(np.float64)
+        avg = float(np.sum(0.0000285 * z * z)) / len(both)
+        a = (max_err - avg) / max_err
+        assert float(f_s) == pytest.approx(cov0 + (1 / d) * (cov_i - cov0) * a, rel=1e-12, abs=1e-12)
