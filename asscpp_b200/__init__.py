@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import _abi
-from ._abi import (ACCURACY_DTYPE, EVAL_ACCURACY, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, RESULT_DTYPE,
+from ._abi import (ACCURACY_DTYPE, CLUSTER_DTYPE, EVAL_ACCURACY, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, RESULT_DTYPE,
                    VS_GRID_GLOBAL, VS_GRID_SHARED, VS_ORDERED, ModelInfo, Params)
 
 __all__ = [
@@ -155,6 +155,27 @@ class CoveredSet:
         vox = None if voxel_bits is None else np.ascontiguousarray(voxel_bits, np.uint64)
         self.ctx._ck(self.ctx.L.asscpp_covered_import(self.ctx.h, self.handle, _ptr(pts, C.c_uint64),
                                                       _ptr(vox, C.c_uint64)))
+
+    def uncovered(self):
+        """pointCloudDiff (heuristic.cpp:88-145): (ids, centres) of the model's coverage voxels not in the set."""
+        n_cov = self.ctx.n_cov_voxels
+        ids = np.zeros(max(n_cov, 1), np.int32)
+        ctr = np.zeros((max(n_cov, 1), 3), np.float32)
+        n = C.c_int64()
+        self.ctx._ck(self.ctx.L.asscpp_uncovered_voxels(self.ctx.h, self.handle, _ptr(ids, C.c_int32),
+                                                        _ptr(ctr, C.c_float), n_cov, C.byref(n)))
+        return ids[:n.value].copy(), ctr[:n.value].copy()
+
+    def uncovered_clusters(self, tolerance=0.8, min_size=5, max_size=50000):
+        """clusteringPointCloud + findClusterBB (heuristic.cpp:147-246): (labels per coverage voxel, clusters)."""
+        n_cov = self.ctx.n_cov_voxels
+        labels = np.zeros(max(n_cov, 1), np.int32)
+        out = np.zeros(max(n_cov, 1), CLUSTER_DTYPE)
+        n = C.c_int64()
+        self.ctx._ck(self.ctx.L.asscpp_uncovered_clusters(self.ctx.h, self.handle, tolerance, min_size, max_size,
+                                                          _ptr(labels, C.c_int32), out.ctypes.data_as(C.c_void_p),
+                                                          n_cov, C.byref(n)))
+        return labels[:n_cov], out[:n.value].copy()
 
     def coverage_percent(self):
         out = C.c_float()

@@ -73,6 +73,19 @@ ACCURACY_DTYPE = np.dtype(
 )
 assert ACCURACY_DTYPE.itemsize == 32
 
+# numpy mirror of AsscppCluster
+CLUSTER_DTYPE = np.dtype(
+    [
+        ("size", np.int32),
+        ("first_id", np.int32),
+        ("min_ijk", np.int32, 3),
+        ("max_ijk", np.int32, 3),
+        ("grid_start", np.float64, 3),
+        ("grid_size", np.float64, 3),
+    ]
+)
+assert CLUSTER_DTYPE.itemsize == 80
+
 # every symbol include/asscpp_gpu.h declares (checked by tests/test_abi_symbols.py)
 SYMBOLS = [
     "asscpp_create", "asscpp_destroy", "asscpp_last_error", "asscpp_abi_version", "asscpp_model_info",
@@ -86,6 +99,7 @@ SYMBOLS = [
     "asscpp_comm_unique_id", "asscpp_comm_init", "asscpp_allgather_results", "asscpp_allreduce_or",
     "asscpp_comm_destroy", "asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor",
     "asscpp_frustum_planes", "asscpp_get_accuracy", "asscpp_pose_rpy", "asscpp_viewport_transform",
+    "asscpp_uncovered_voxels", "asscpp_uncovered_clusters",
 ]
 
 _lib = None
@@ -150,6 +164,8 @@ def load():
         "asscpp_get_accuracy": (i32, [vp, vp, i64]),
         "asscpp_pose_rpy": (i32, [f64p, f64p]),
         "asscpp_viewport_transform": (i32, [f64p, f32p, i64, f32p]),
+        "asscpp_uncovered_voxels": (i32, [vp, i32, i32p, f32p, i64, i64p]),
+        "asscpp_uncovered_clusters": (i32, [vp, i32, C.c_double, C.c_int32, C.c_int32, i32p, vp, i64, i64p]),
     }
     assert sorted(sig) == sorted(SYMBOLS)
     for name, (res, args) in sig.items():

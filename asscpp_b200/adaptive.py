@@ -8,10 +8,11 @@ Restates the skeleton of PathPlanner::dynamicNodesGenerationAndConnection (sspp/
   * evaluate + accept    = isFilteringConditionSatisfied's coverage part (heuristic.cpp:339-357), batched
   * uncovered percentage = pointCloudDiff (heuristic.cpp:88-145) on the covered voxel bitset
   * clusters + boxes     = clusteringPointCloud / findClusterBB (heuristic.cpp:147-246)
-Deviations (stated in DESIGN.md): the CGAL inside-mesh / distance filters are replaced by a stand-off test
-against the model's voxel grid, PCL's Euclidean clustering (tolerance 0.8 m on 0.5 m voxel centres) by
-18-connected components of the uncovered voxels.  Both run on the host; only the viewpoint evaluation and
-the covered-set union run on the GPUs, sharded over ranks with ONE covered-bitset OR-allreduce per iteration.
+Deviation (stated in DESIGN.md): the CGAL inside-mesh / distance filters are replaced by a stand-off test
+against the model's voxel grid, on the host.  Viewpoint evaluation, the covered-set union, the uncovered
+voxel extraction, the Euclidean clustering (tolerance 0.8 m, sizes 5..50000) and the cluster boxes run on the
+GPUs (asscpp_uncovered_voxels / asscpp_uncovered_clusters), viewpoints sharded over ranks with ONE
+covered-bitset OR-allreduce per iteration.
 
 The `backend` is duck-typed (GpuBackend here, OracleBackend in tests/): the same loop drives the CUDA
 path and the CPU oracle, which is how the per-iteration parity of config 4 is asserted.
@@ -78,35 +79,6 @@ class VoxelModel:
             ok[s:s + 512] = (d >= dmin) & (d <= dmax)
         return ok
 
-    def clusters(self, uncovered_ids, min_size=5):
-        """18-connected components of the uncovered voxels (centres within 0.8 m at a 0.5 m lattice)."""
-        pts = {tuple(self.ijk[i]): i for i in uncovered_ids}
-        offs = [(a, b, c) for a in (-1, 0, 1) for b in (-1, 0, 1) for c in (-1, 0, 1) if 0 < abs(a) + abs(b) + abs(c) <= 2]
-        seen, out = set(), []
-        for start in sorted(pts):
-            if start in seen:
-                continue
-            comp, stack = [], [start]
-            seen.add(start)
-            while stack:
-                v = stack.pop()
-                comp.append(pts[v])
-                for o in offs:
-                    w = (v[0] + o[0], v[1] + o[1], v[2] + o[2])
-                    if w in pts and w not in seen:
-                        seen.add(w)
-                        stack.append(w)
-            if len(comp) >= min_size:
-                out.append(np.array(sorted(comp)))
-        return out
-
-    def cluster_box(self, ids):
-        """findClusterBB (heuristic.cpp:218-246): centre of the min / max voxel, +5 m in x, y, +3 m in z."""
-        lo, hi = self.centres[ids].min(0), self.centres[ids].max(0)
-        size = np.array([abs(hi[0] - lo[0]) + 5.0, abs(hi[1] - lo[1]) + 5.0, abs(hi[2] - lo[2]) + 3.0])
-        start = np.array([lo[0] - 2.5, lo[1] - 2.5, lo[2]])
-        return start, size
-
 
 def bits_to_ids(bits, n):
     return np.nonzero(np.unpackbits(bits.view(np.uint8), bitorder="little")[:n])[0]
@@ -138,6 +110,12 @@ class GpuBackend:
     def covered_voxels(self):
         return self.set.export()[1]
 
+    def uncovered_regions(self):
+        """(number of uncovered coverage voxels, [(grid_start, grid_size)] per cluster, largest first)."""
+        ids, _ = self.set.uncovered()                       # pointCloudDiff, heuristic.cpp:88-145
+        _, cl = self.set.uncovered_clusters(0.8, 5, 50000)  # clusteringPointCloud :147-190 + findClusterBB :218-246
+        return len(ids), [(c["grid_start"].copy(), c["grid_size"].copy()) for c in cl]
+
 
 def adaptive_loop(backend, model, grid_center, grid_size, start_res=4.5, res_dec=1.5, world=1, rank=0,
                   gather_counts=None, max_iters=8, log=None):
@@ -168,18 +146,20 @@ def adaptive_loop(backend, model, grid_center, grid_size, start_res=4.5, res_dec
             accepted_total = gather_counts(accepted_total)
         bits = backend.covered_voxels()
         covered = bits_to_ids(bits, model.n)
-        uncovered = np.setdiff1d(np.arange(model.n), covered)
-        pct = (len(uncovered) / float(model.n)) * 100.0  # heuristic.cpp:143
+        n_uncovered, regions = backend.uncovered_regions()
+        pct = (n_uncovered / float(model.n)) * 100.0  # heuristic.cpp:143
         trace.append({"iter": it, "res": res, "candidates": cand_total, "accepted": accepted_total,
-                      "covered_voxels": int(len(covered)), "uncovered_pct": pct, "bits": bits.copy()})
+                      "covered_voxels": int(len(covered)), "uncovered_pct": pct, "bits": bits.copy(),
+                      "clusters": len(regions)})
         if log:
-            log("iter %d res %.2f candidates %d accepted %d covered %d uncovered %.3f%%"
-                % (it, res, cand_total, accepted_total, len(covered), pct))
+            log("iter %d res %.2f candidates %d accepted %d covered %d uncovered %.3f%% clusters %d"
+                % (it, res, cand_total, accepted_total, len(covered), pct, len(regions)))
         if pct <= 0.01:          # pathplanner.cpp:776
             break
-        clusters = model.clusters(uncovered)
         res -= res_dec           # pathplanner.cpp:792
-        if res <= 0 or not clusters:
+        if res <= 0 or not regions:
             break
-        boxes = [model.cluster_box(c) for c in clusters]
+        # findClusterBB's gridStart is handed to generateRegularGrid, which treats it as the grid CENTRE
+        # (pathplanner.cpp:122-126, 802-806): kept as the reference does it
+        boxes = regions
     return trace

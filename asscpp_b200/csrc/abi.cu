@@ -103,6 +103,12 @@ struct AsscppCtx {
   bool last_had_acc = false;
   int64_t last_nviews = -1;
   std::vector<AsscppViewResult> h_results;
+  // uncovered regions (allocated on first use)
+  int32_t* d_region = nullptr;
+  int32_t* d_region_ids = nullptr;
+  float* d_region_ctr = nullptr;
+  int64_t* d_region_total = nullptr;
+  int3* d_region_offs = nullptr;
   // staging
   uint32_t* d_tmp_bits = nullptr;  // pts_words, original-index space staging
   int64_t idx_cap = 0;
@@ -824,6 +830,113 @@ int asscpp_eval_kernel_ms(AsscppCtx* c, float* ms, int64_t* launches) {
   if (!c) return ASSCPP_EINVAL;
   if (ms) *ms = c->last_kernel_ms;
   if (launches) *launches = c->last_kernel_launches;
+  return ASSCPP_OK;
+}
+
+// ---- uncovered regions ---------------------------------------------------------------------------
+static int ensure_region_buffers(AsscppCtx* c) {
+  if (c->d_region) return ASSCPP_OK;
+  const int64_t n = std::max<int64_t>(c->m.n_cov, 1);
+  // [wcount n/32+1 | parent n | root n | size n | box 6n] int32, ids n int32, centres 3n float, total int64
+  int rc;
+  if ((rc = dev_alloc(c, &c->d_region, (n + 31) / 32 + 1 + 9 * n))) return rc;
+  if ((rc = dev_alloc(c, &c->d_region_ids, n))) return rc;
+  if ((rc = dev_alloc(c, &c->d_region_ctr, 3 * n))) return rc;
+  if ((rc = dev_alloc(c, &c->d_region_total, 1))) return rc;
+  if ((rc = dev_alloc(c, &c->d_region_offs, 343))) return rc;
+  return ASSCPP_OK;
+}
+
+int asscpp_uncovered_voxels(AsscppCtx* c, int set, int32_t* ids, float* centres, int64_t cap, int64_t* n_out) {
+  if (!c || !valid_set(c, set) || cap < 0 || !n_out) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = ensure_region_buffers(c);
+  if (rc) return rc;
+  const int64_t n = c->m.n_cov;
+  launch_uncovered(set_dev(c, set).vox, n, c->d_region, c->d_region_total, c->d_cov_keys, c->cov_min_b, c->cov_div,
+                   c->params.cov_leaf, c->d_region_ids, c->d_region_ctr, n, c->stream);
+  c->launches += 3;
+  CU(c, cudaGetLastError());
+  int64_t total = 0;
+  CU(c, cudaMemcpyAsync(&total, c->d_region_total, sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  *n_out = total;
+  const int64_t take = std::min(total, cap);
+  if (ids && take > 0) CU(c, cudaMemcpy(ids, c->d_region_ids, (size_t)take * 4, cudaMemcpyDeviceToHost));
+  if (centres && take > 0) CU(c, cudaMemcpy(centres, c->d_region_ctr, (size_t)take * 12, cudaMemcpyDeviceToHost));
+  return ASSCPP_OK;
+}
+
+int asscpp_uncovered_clusters(AsscppCtx* c, int set, double tolerance, int32_t min_size, int32_t max_size,
+                              int32_t* labels, AsscppCluster* clusters, int64_t cap, int64_t* n_clusters) {
+  if (!c || !valid_set(c, set) || !(tolerance > 0) || cap < 0 || !n_clusters || (cap > 0 && !clusters)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = ensure_region_buffers(c);
+  if (rc) return rc;
+  const int64_t n = c->m.n_cov;
+  *n_clusters = 0;
+  if (n == 0) return ASSCPP_OK;
+  // lattice offsets whose centres are closer than the tolerance: <FLANN radiusSearch> keeps squared float32
+  // distances strictly below float(tol * tol); centre differences on the lattice are float(d) * leaf
+  const float leaf = c->params.cov_leaf, r2 = (float)(tolerance * tolerance);
+  const int R = (int)std::floor(tolerance / (double)leaf) + 1;
+  if (R > 3) { c->err = "cluster tolerance spans more than 3 coverage voxels"; return ASSCPP_ERANGE; }
+  std::vector<int3> offs;
+  for (int dz = -R; dz <= R; ++dz)
+    for (int dy = -R; dy <= R; ++dy)
+      for (int dx = -R; dx <= R; ++dx) {
+        if (!dx && !dy && !dz) continue;
+        const float fx = (float)dx * leaf, fy = (float)dy * leaf, fz = (float)dz * leaf;
+        const float d2 = fx * fx + fy * fy + fz * fz;
+        if (d2 < r2) offs.push_back(make_int3(dx, dy, dz));
+      }
+  int32_t* wcount = c->d_region;
+  int32_t* parent = wcount + (n + 31) / 32 + 1;
+  int32_t *root = parent + n, *size = root + n, *box = size + n;
+  if (!offs.empty())
+    CU(c, cudaMemcpyAsync(c->d_region_offs, offs.data(), offs.size() * sizeof(int3), cudaMemcpyHostToDevice, c->stream));
+  launch_clusters(set_dev(c, set).vox, n, c->d_cov_keys, c->cov_min_b, c->cov_div, c->d_region_offs, (int)offs.size(),
+                  parent, root, size, box, c->stream);
+  c->launches += 4;
+  CU(c, cudaGetLastError());
+  std::vector<int32_t> h_root((size_t)n), h_size((size_t)n), h_box((size_t)6 * n);
+  CU(c, cudaMemcpyAsync(h_root.data(), root, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(h_size.data(), size, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(h_box.data(), box, (size_t)n * 24, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  // clusters = roots whose size is in range (heuristic.cpp:157-158), largest first (<PCL> sorts by size)
+  std::vector<int32_t> roots;
+  for (int64_t i = 0; i < n; ++i)
+    if (h_root[(size_t)i] == (int32_t)i && h_size[(size_t)i] >= min_size && h_size[(size_t)i] <= max_size) roots.push_back((int32_t)i);
+  std::stable_sort(roots.begin(), roots.end(), [&](int32_t a, int32_t b) { return h_size[(size_t)a] > h_size[(size_t)b]; });
+  *n_clusters = (int64_t)roots.size();
+  std::vector<int32_t> rank((size_t)n, -1);
+  for (size_t k = 0; k < roots.size(); ++k) rank[(size_t)roots[k]] = (int32_t)k;
+  if (labels)
+    for (int64_t i = 0; i < n; ++i) labels[i] = h_root[(size_t)i] >= 0 ? rank[(size_t)h_root[(size_t)i]] : -1;
+  const int64_t take = std::min<int64_t>(cap, (int64_t)roots.size());
+  for (int64_t k = 0; k < take; ++k) {
+    AsscppCluster& o = clusters[k];
+    const int32_t r = roots[(size_t)k];
+    o.size = h_size[(size_t)r];
+    o.first_id = r;  // roots are the smallest id of their component (hooking is always larger -> smaller)
+    float cmin[3], cmax[3];
+    for (int a = 0; a < 3; ++a) {
+      o.min_ijk[a] = h_box[(size_t)6 * r + a];
+      o.max_ijk[a] = h_box[(size_t)6 * r + 3 + a];
+      // findClusterBB :224-233: the cluster's own voxel grid; centres of its min and max cells
+      const float b_min = (float)o.min_ijk[a] * leaf;
+      cmin[a] = (b_min + leaf * 0.5f) + (float)0 * leaf;
+      cmax[a] = (b_min + leaf * 0.5f) + (float)(o.max_ijk[a] - o.min_ijk[a]) * leaf;
+    }
+    const double maximizeSizeXY = 5, maximizeSizeZ = 3;  // :236-237
+    o.grid_size[0] = std::abs(cmax[0] - cmin[0]) + maximizeSizeXY;
+    o.grid_size[1] = std::abs(cmax[1] - cmin[1]) + maximizeSizeXY;
+    o.grid_size[2] = std::abs(cmax[2] - cmin[2]) + maximizeSizeZ;
+    o.grid_start[0] = cmin[0] - double(maximizeSizeXY / 2);
+    o.grid_start[1] = cmin[1] - double(maximizeSizeXY / 2);
+    o.grid_start[2] = cmin[2];
+  }
   return ASSCPP_OK;
 }
 

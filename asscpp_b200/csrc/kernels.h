@@ -22,6 +22,13 @@ void launch_permute_bits(const uint32_t* src, uint32_t* dst, const int32_t* map,
 void launch_or_points(CoveredDev set, const int32_t* idx, int64_t n, const ModelDev& m, cudaStream_t s);
 void launch_cloud_cover(const float* xyz, int64_t n, float inv_cov, const int32_t cmin[3], const int32_t cdiv[3],
                         const int64_t* keys, int64_t nkeys, uint32_t* marks, cudaStream_t s);
+// regions.cu
+void launch_uncovered(const uint32_t* vox_bits, int64_t n_cov, int32_t* wcount, int64_t* d_total, const int64_t* keys,
+                      const int32_t cmin[3], const int32_t cdiv[3], float leaf, int32_t* ids, float* centres,
+                      int64_t cap, cudaStream_t s);
+void launch_clusters(const uint32_t* vox_bits, int64_t n_cov, const int64_t* keys, const int32_t cmin[3],
+                     const int32_t cdiv[3], const int3* offs, int noffs, int32_t* parent, int32_t* root, int32_t* size,
+                     int32_t* box, cudaStream_t s);
 void launch_fill_bytes(uint8_t* p, int64_t n, uint8_t v, cudaStream_t s);
 
 }  // namespace asscpp

@@ -161,6 +161,27 @@ int asscpp_coverage_percent(AsscppCtx* ctx, int set, float* pct);
 /* calcCoveragePercent of an arbitrary cloud (n x xyz float32, host memory) */
 int asscpp_coverage_percent_cloud(AsscppCtx* ctx, const float* xyz, int64_t n, float* pct);
 
+/* -- uncovered regions of the adaptive loop (coverage_path_planning_heuristic.cpp:88-246) ------------------ */
+/* pointCloudDiff (:88-145) in bitset form: the model's coverage voxels NOT in the set, in the reference's k, j, i
+ * scan order (= ascending compact id), with their cell centres (getCentroidCoordinate).  ids / centres_xyz may be
+ * NULL; at most cap entries are written; *n_out receives the full count (uncovered % = 100 * n / n_cov_voxels). */
+int asscpp_uncovered_voxels(AsscppCtx* ctx, int set, int32_t* ids, float* centres_xyz, int64_t cap, int64_t* n_out);
+
+/* clusteringPointCloud (:147-190, pcl::EuclideanClusterExtraction: tolerance 0.8, sizes 5..50000 in the reference)
+ * over those voxel centres + findClusterBB (:218-246) per cluster.  Clusters come largest first (equal sizes: by
+ * smallest member id).  labels: n_cov_voxels entries, cluster index or -1 (covered, or cluster size out of range);
+ * may be NULL. */
+typedef struct AsscppCluster {
+  int32_t size;        /* voxels in the cluster                                   */
+  int32_t first_id;    /* smallest compact coverage-voxel id of the cluster       */
+  int32_t min_ijk[3];  /* lattice box of the cluster                              */
+  int32_t max_ijk[3];
+  double grid_start[3]; /* findClusterBB gridStart.position (:242-244)            */
+  double grid_size[3];  /* findClusterBB gridSize (:238-240)                      */
+} AsscppCluster;
+int asscpp_uncovered_clusters(AsscppCtx* ctx, int set, double tolerance, int32_t min_size, int32_t max_size,
+                              int32_t* labels, AsscppCluster* clusters, int64_t cap, int64_t* n_clusters);
+
 /* -- streams / timing -------------------------------------------------------------------------- */
 int asscpp_sync(AsscppCtx* ctx);
 void* asscpp_get_stream(AsscppCtx* ctx); /* cudaStream_t all kernels are launched on */

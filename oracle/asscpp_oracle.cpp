@@ -30,6 +30,8 @@ struct Ctx {
   int64_t n_cov = 0;
   int64_t n_occ = 0;
   int32_t min_b[3] = {0, 0, 0}, max_b[3] = {0, 0, 0};  // occlusion-lattice model box
+  int32_t cov_min_b[3] = {0, 0, 0};
+  std::vector<int32_t> cov_ijk;  // 3*n_cov lattice coordinates of the coverage voxels, compact-id order
 };
 
 inline int32_t ifloor(f32 v) { return static_cast<int32_t>(std::floor(v)); }
@@ -591,7 +593,8 @@ int orc_create(const float* xyz, int64_t n, const OrcParams* p, OrcCtx** out) {
   c.inv_cov = 1.0f / p->cov_leaf;
   // model grids (occlusion_culling.cpp:41-65): only occupancy on a lattice matters; compact ids in
   // ascending (k, j, i) order of the linearised model grid.
-  auto build = [&](f32 inv, std::vector<int32_t>* ids, int64_t* count, int32_t* mnb, int32_t* mxb) -> int {
+  auto build = [&](f32 inv, std::vector<int32_t>* ids, int64_t* count, int32_t* mnb, int32_t* mxb,
+                   std::vector<int32_t>* vox_ijk) -> int {
     if (n == 0) { *count = 0; return 0; }
     int32_t lo[3] = {INT32_MAX, INT32_MAX, INT32_MAX}, hi[3] = {INT32_MIN, INT32_MIN, INT32_MIN};
     for (int64_t i = 0; i < n; ++i)
@@ -616,11 +619,19 @@ int orc_create(const float* xyz, int64_t n, const OrcParams* p, OrcCtx** out) {
       for (int64_t i = 0; i < n; ++i)
         (*ids)[i] = (int32_t)(std::lower_bound(uniq.begin(), uniq.end(), key[i]) - uniq.begin());
     }
-    if (mnb) for (int k = 0; k < 3; ++k) { mnb[k] = lo[k]; mxb[k] = hi[k]; }
+    if (mnb) for (int k = 0; k < 3; ++k) { mnb[k] = lo[k]; if (mxb) mxb[k] = hi[k]; }
+    if (vox_ijk) {
+      vox_ijk->resize(3 * uniq.size());
+      for (size_t u = 0; u < uniq.size(); ++u) {
+        (*vox_ijk)[3 * u] = (int32_t)(uniq[u] % dx) + lo[0];
+        (*vox_ijk)[3 * u + 1] = (int32_t)((uniq[u] / dx) % dy) + lo[1];
+        (*vox_ijk)[3 * u + 2] = (int32_t)(uniq[u] / (dx * dy)) + lo[2];
+      }
+    }
     return 0;
   };
-  int rc = build(c.inv_cov, &c.cov_id, &c.n_cov, nullptr, nullptr);
-  if (rc == 0) rc = build(c.inv_leaf, nullptr, &c.n_occ, c.min_b, c.max_b);
+  int rc = build(c.inv_cov, &c.cov_id, &c.n_cov, c.cov_min_b, nullptr, &c.cov_ijk);
+  if (rc == 0) rc = build(c.inv_leaf, nullptr, &c.n_occ, c.min_b, c.max_b, nullptr);
   if (rc != 0) { delete o; return rc; }
   *out = o;
   return 0;
@@ -755,6 +766,111 @@ void orc_accuracy_idx(const OrcCtx* c, const double pose[7], const int32_t* idx,
     hi = std::max(hi, q[0]);
   }
   *err_sum_depth = sd; *err_sum_z = sz; *depth_min = lo; *depth_max = hi;
+}
+
+int64_t orc_uncovered(const OrcCtx* oc, const uint64_t* covered_vox, int32_t* ids, float* centres) {
+  // pointCloudDiff (coverage_path_planning_heuristic.cpp:88-145): scan the model's coverage grid in k, j, i order
+  // (= ascending compact id) and keep the occupied cells whose centre falls in no covered voxel.  Both grids share
+  // the lattice floor(x * inv_leaf), so "centre not in a covered voxel" is "bit not set".  Centre =
+  // getCentroidCoordinate (voxel_grid_occlusion_estimation.h:143-157) on the model grid.
+  const Ctx& c = oc->c;
+  const f32 leaf = c.p.cov_leaf;
+  int64_t n = 0;
+  for (int64_t u = 0; u < c.n_cov; ++u) {
+    if (covered_vox && ((covered_vox[u >> 6] >> (u & 63)) & 1ull)) continue;
+    if (ids) ids[n] = (int32_t)u;
+    if (centres)
+      for (int k = 0; k < 3; ++k) {
+        f32 b_min = (f32)c.cov_min_b[k] * leaf;
+        centres[3 * n + k] = (b_min + leaf * 0.5f) + (f32)(c.cov_ijk[3 * u + k] - c.cov_min_b[k]) * leaf;
+      }
+    ++n;
+  }
+  return n;
+}
+
+int32_t orc_euclidean_clusters(const float* xyz, int64_t n, double tol, int32_t min_size, int32_t max_size,
+                               int32_t* labels, int64_t* ties) {
+  // clusteringPointCloud (coverage_path_planning_heuristic.cpp:147-190) = <PCL extractEuclideanClusters>: for every
+  // unprocessed point in index order grow a region breadth-first through radius searches; keep it when
+  // min <= size <= max; finally sort the clusters largest first.  <FLANN radiusSearch>: squared float32 distance
+  // strictly below float(tol * tol).  Restated from the published algorithms (PCL / FLANN are not vendored).
+  // The neighbour search is a uniform hash grid of cell size tol; the distance test is literal.
+  const f32 r2 = (f32)(tol * tol);
+  if (ties) *ties = 0;
+  for (int64_t i = 0; i < n; ++i) labels[i] = -1;
+  if (n == 0) return 0;
+  f32 lo[3] = {xyz[0], xyz[1], xyz[2]};
+  for (int64_t i = 0; i < n; ++i)
+    for (int k = 0; k < 3; ++k) lo[k] = std::min(lo[k], xyz[3 * i + k]);
+  auto cell = [&](int64_t i, int k) { return (int64_t)std::floor(((double)xyz[3 * i + k] - lo[k]) / tol); };
+  std::vector<std::pair<uint64_t, int32_t>> grid(n);
+  auto pack = [](int64_t a, int64_t b, int64_t c) {
+    return ((uint64_t)(a + 1) << 42) | ((uint64_t)(b + 1) << 21) | (uint64_t)(c + 1);
+  };
+  for (int64_t i = 0; i < n; ++i) grid[i] = std::make_pair(pack(cell(i, 0), cell(i, 1), cell(i, 2)), (int32_t)i);
+  std::sort(grid.begin(), grid.end());
+  std::vector<char> processed(n, 0);
+  std::vector<std::vector<int32_t>> clusters;
+  std::vector<int32_t> queue;
+  for (int64_t s = 0; s < n; ++s) {
+    if (processed[s]) continue;
+    queue.clear();
+    queue.push_back((int32_t)s);
+    processed[s] = 1;
+    for (size_t q = 0; q < queue.size(); ++q) {
+      const int32_t i = queue[q];
+      const int64_t ca = cell(i, 0), cb = cell(i, 1), cc = cell(i, 2);
+      for (int64_t a = ca - 1; a <= ca + 1; ++a)
+        for (int64_t b = cb - 1; b <= cb + 1; ++b)
+          for (int64_t c = cc - 1; c <= cc + 1; ++c) {
+            if (a < 0 || b < 0 || c < 0) continue;
+            const uint64_t key = pack(a, b, c);
+            auto it = std::lower_bound(grid.begin(), grid.end(), std::make_pair(key, (int32_t)INT32_MIN));
+            for (; it != grid.end() && it->first == key; ++it) {
+              const int32_t j = it->second;
+              f32 d0 = xyz[3 * i] - xyz[3 * j], d1 = xyz[3 * i + 1] - xyz[3 * j + 1], d2 = xyz[3 * i + 2] - xyz[3 * j + 2];
+              f32 dist = d0 * d0 + d1 * d1 + d2 * d2;  // <FLANN L2_Simple<float>>
+              if (ties && dist == r2 && i < j) ++*ties;
+              if (!(dist < r2) || processed[j]) continue;
+              processed[j] = 1;
+              queue.push_back(j);
+            }
+          }
+    }
+    if ((int64_t)queue.size() >= min_size && (int64_t)queue.size() <= max_size) clusters.push_back(queue);
+  }
+  // largest first (PCL's comparePointClusters); equal sizes: by first member, which PCL leaves unspecified
+  std::stable_sort(clusters.begin(), clusters.end(),
+                   [](const std::vector<int32_t>& a, const std::vector<int32_t>& b) { return a.size() > b.size(); });
+  for (size_t k = 0; k < clusters.size(); ++k)
+    for (int32_t i : clusters[k]) labels[i] = (int32_t)k;
+  return (int32_t)clusters.size();
+}
+
+void orc_cluster_bb(const float* xyz, int64_t n, float leaf, double grid_start[3], double grid_size[3]) {
+  // findClusterBB (coverage_path_planning_heuristic.cpp:218-246): voxel grid over the cluster at `leaf`, centres of
+  // its min and max cells, box grown by 5 m in x, y and 3 m in z
+  const f32 inv = 1.0f / leaf;
+  int32_t mn[3] = {INT32_MAX, INT32_MAX, INT32_MAX}, mx[3] = {INT32_MIN, INT32_MIN, INT32_MIN};
+  for (int64_t i = 0; i < n; ++i)
+    for (int k = 0; k < 3; ++k) {
+      int32_t v = ifloor(xyz[3 * i + k] * inv);
+      mn[k] = std::min(mn[k], v); mx[k] = std::max(mx[k], v);
+    }
+  f32 cmin[3], cmax[3];
+  for (int k = 0; k < 3; ++k) {
+    f32 b_min = (f32)mn[k] * leaf;
+    cmin[k] = (b_min + leaf * 0.5f) + (f32)0 * leaf;
+    cmax[k] = (b_min + leaf * 0.5f) + (f32)(mx[k] - mn[k]) * leaf;
+  }
+  const double maximizeSizeXY = 5, maximizeSizeZ = 3;
+  grid_size[0] = std::abs(cmax[0] - cmin[0]) + maximizeSizeXY;
+  grid_size[1] = std::abs(cmax[1] - cmin[1]) + maximizeSizeXY;
+  grid_size[2] = std::abs(cmax[2] - cmin[2]) + maximizeSizeZ;
+  grid_start[0] = cmin[0] - double(maximizeSizeXY / 2);
+  grid_start[1] = cmin[1] - double(maximizeSizeXY / 2);
+  grid_start[2] = cmin[2];
 }
 
 }  // extern "C"

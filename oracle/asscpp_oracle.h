@@ -111,6 +111,16 @@ void orc_viewport_transform(const double pose[7], const float* xyz, int64_t n, f
 void orc_accuracy_idx(const OrcCtx* c, const double pose[7], const int32_t* idx, int64_t n, double* err_sum_depth,
                       double* err_sum_z, float* depth_min, float* depth_max);
 
+/* pointCloudDiff (coverage_path_planning_heuristic.cpp:88-145) in bitset form: uncovered coverage voxels in the
+ * reference's k, j, i scan order (= ascending compact id) with their cell centres; returns their number */
+int64_t orc_uncovered(const OrcCtx* c, const uint64_t* covered_vox, int32_t* ids, float* centres);
+/* clusteringPointCloud (:147-190), <PCL EuclideanClusterExtraction>: labels[i] = cluster rank (largest first) or -1;
+ * ties (optional) counts point pairs at squared distance exactly float(tol*tol) */
+int32_t orc_euclidean_clusters(const float* xyz, int64_t n, double tol, int32_t min_size, int32_t max_size,
+                               int32_t* labels, int64_t* ties);
+/* findClusterBB (:218-246) */
+void orc_cluster_bb(const float* xyz, int64_t n, float leaf, double grid_start[3], double grid_size[3]);
+
 /* 64-bit mix used for the order-independent set hashes (sum of mix(idx)) */
 uint64_t orc_mix64(uint64_t x);
 

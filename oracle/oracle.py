@@ -93,6 +93,12 @@ def lib():
         L.orc_viewport_transform.restype = None
         L.orc_accuracy_idx.argtypes = [vp, f64p, i32p, i64, f64p, f64p, f32p, f32p]
         L.orc_accuracy_idx.restype = None
+        L.orc_uncovered.argtypes = [vp, u64p, i32p, f32p]
+        L.orc_uncovered.restype = i64
+        L.orc_euclidean_clusters.argtypes = [f32p, i64, C.c_double, C.c_int32, C.c_int32, i32p, i64p]
+        L.orc_euclidean_clusters.restype = C.c_int32
+        L.orc_cluster_bb.argtypes = [f32p, i64, C.c_float, f64p, f64p]
+        L.orc_cluster_bb.restype = None
         L.orc_mix64.argtypes = [C.c_uint64]
         L.orc_mix64.restype = C.c_uint64
         _lib = L
@@ -183,6 +189,13 @@ class Oracle:
         idx = np.ascontiguousarray(idx, dtype=np.int32)
         return float(self.L.orc_coverage_percent_idx(self.h, _p(idx, C.c_int32), idx.shape[0]))
 
+    def uncovered(self, covered_vox=None):
+        """pointCloudDiff (heuristic.cpp:88-145): (ids, centres) of the uncovered coverage voxels."""
+        ids = np.zeros(max(self.n_cov, 1), np.int32)
+        ctr = np.zeros((max(self.n_cov, 1), 3), np.float32)
+        n = lib().orc_uncovered(self.h, _p(covered_vox, C.c_uint64), _p(ids, C.c_int32), _p(ctr, C.c_float))
+        return ids[:n].copy(), ctr[:n].copy()
+
     def accuracy_idx(self, pose, idx):
         """(err_sum_depth, err_sum_z, depth_min, depth_max) over the points idx in that order:
         calcAvgAccuracy(cloud, pose) = err_sum_depth / n, calcAvgAccuracy(cloud) = err_sum_z / n."""
@@ -213,6 +226,24 @@ def viewport_transform(pose, xyz):
     out = np.zeros_like(xyz)
     lib().orc_viewport_transform(_p(pose, C.c_double), _p(xyz, C.c_float), len(xyz), _p(out, C.c_float))
     return out
+
+
+def euclidean_clusters(xyz, tol=0.8, min_size=5, max_size=50000):
+    """clusteringPointCloud (heuristic.cpp:147-190): labels (cluster rank, largest first, or -1), count, exact ties."""
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    labels = np.zeros(len(xyz), np.int32)
+    ties = C.c_int64(0)
+    k = lib().orc_euclidean_clusters(_p(xyz, C.c_float), len(xyz), tol, min_size, max_size, _p(labels, C.c_int32),
+                                     C.byref(ties))
+    return labels, int(k), ties.value
+
+
+def cluster_bb(xyz, leaf=0.5):
+    """findClusterBB (heuristic.cpp:218-246): (grid_start[3], grid_size[3])."""
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    start, size = np.zeros(3), np.zeros(3)
+    lib().orc_cluster_bb(_p(xyz, C.c_float), len(xyz), leaf, _p(start, C.c_double), _p(size, C.c_double))
+    return start, size
 
 
 def robot2sensor(robot_pose, offset, rpy):

@@ -27,3 +27,8 @@ class OracleBackend:
 
     def covered_voxels(self):
         return self.cv
+
+    def uncovered_regions(self):
+        ids, ctr = self.o.uncovered(self.cv)
+        labels, k, _ = self.O.euclidean_clusters(ctr, 0.8, 5, 50000)
+        return len(ids), [self.O.cluster_bb(ctr[labels == c], 0.5) for c in range(k)]

@@ -291,7 +291,7 @@ def test_config4_adaptive_loop(A, oracle_mod, etihad):
     for a, b in zip(tg, to):
         assert a["candidates"] == b["candidates"] and a["accepted"] == b["accepted"]
         assert np.array_equal(a["bits"], b["bits"])
-        assert a["uncovered_pct"] == b["uncovered_pct"]
+        assert a["uncovered_pct"] == b["uncovered_pct"] and a["clusters"] == b["clusters"]
     assert tg[-1]["uncovered_pct"] < 1.0
     ctx.close()
 
@@ -380,3 +380,39 @@ def test_accuracy_terms_synthetic_fine_grid(A, oracle_mod):
             assert abs(acc["err_sum_depth"][v] - sd) <= tol * sd and abs(acc["err_sum_z"][v] - sz) <= tol * sz + 1e-300
             assert np.float32(lo) == acc["depth_min"][v] and np.float32(hi) == acc["depth_max"][v]
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_uncovered_regions(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
+    """§8f rank 2: pointCloudDiff, clusteringPointCloud and findClusterBB (heuristic.cpp:88-246) on the device
+    against the oracle's literal restatement (itself pinned against scipy in tests/test_oracle.py)."""
+    O = oracle_mod
+    poses = np.ascontiguousarray(np.concatenate([space_2p5["cam0"][::7], space_2p5["cam1"][::7]]))
+    s = etihad_ctx.new_set()
+    for cut in (0, 40, len(poses)):  # nothing covered, a little covered, the whole sample
+        s.clear()
+        cv = np.zeros(etihad_oracle.vox_words(), np.uint64)
+        cp = np.zeros(etihad_oracle.pts_words(), np.uint64)
+        if cut:
+            s.or_views(poses[:cut], 5)
+            etihad_oracle.accumulate(poses[:cut], cp, cv, min_visible=5, nthreads=NTHREADS)
+        ids, ctr = s.uncovered()
+        ids_o, ctr_o = etihad_oracle.uncovered(cv)
+        assert np.array_equal(ids, ids_o)
+        assert np.array_equal(ctr.view(np.uint32), ctr_o.view(np.uint32))
+        labels, clusters = s.uncovered_clusters(0.8, 5, 50000)
+        lab_o, k, ties = O.euclidean_clusters(ctr_o, 0.8, 5, 50000)
+        assert ties == 0 and len(clusters) == k
+        # same partition and same sizes, largest first; ties in size may be ordered differently
+        mine = labels[ids]
+        assert np.array_equal(mine >= 0, lab_o >= 0)
+        pairs = set(zip(mine[mine >= 0].tolist(), lab_o[lab_o >= 0].tolist()))
+        assert len(pairs) == k == len(set(a for a, _ in pairs)) == len(set(b for _, b in pairs))
+        assert np.all(np.diff(clusters["size"]) <= 0)
+        assert np.array_equal(clusters["size"], np.bincount(lab_o[lab_o >= 0], minlength=k)[:k]) or k == 0
+        assert np.all(labels[np.setdiff1d(np.arange(etihad_ctx.n_cov_voxels), ids)] == -1)
+        for c in range(k):
+            start, size = O.cluster_bb(ctr_o[mine == c], 0.5)
+            assert np.array_equal(clusters["grid_start"][c], start) and np.array_equal(clusters["grid_size"][c], size)
+            assert clusters["first_id"][c] == ids[mine == c].min()
+    s.free()

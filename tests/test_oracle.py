@@ -231,3 +231,46 @@ def test_accuracy_terms_literal(oracle_mod, etihad, space_2p5):
         assert sd == ed and sz == ez
         assert lo == t[:, 0].min() and hi == t[:, 0].max()
     assert seen >= 3
+
+
+def test_uncovered_clusters_against_scipy(oracle_mod, etihad, space_2p5):
+    """pointCloudDiff + clusteringPointCloud + findClusterBB (heuristic.cpp:88-246) restated literally, pinned
+    against an independent implementation: on a 0.5 m lattice a 0.8 m Euclidean tolerance links exactly the face
+    and edge neighbours (0.5, 0.707 < 0.8 < 0.866), i.e. scipy's 18-connected labelling of the dense grid."""
+    from scipy import ndimage
+    O = oracle_mod
+    xyz, _ = etihad
+    o = O.Oracle(xyz)
+    cv = np.zeros(o.vox_words(), np.uint64)
+    cp = np.zeros(o.pts_words(), np.uint64)
+    poses = np.concatenate([space_2p5["cam0"][::7], space_2p5["cam1"][::7]])
+    o.accumulate(poses, cp, cv, min_visible=5, nthreads=4)
+    ids, ctr = o.uncovered(cv)
+    covered = int(np.unpackbits(cv.view(np.uint8)).sum())
+    assert len(ids) == o.n_cov - covered and 0 < len(ids) < o.n_cov
+    assert np.all(np.diff(ids) > 0)
+    labels, k, ties = O.euclidean_clusters(ctr, 0.8, 5, 50000)
+    assert ties == 0 and k > 1
+    # independent: dense grid + 18-connectivity
+    ijk = np.floor(ctr * np.float32(2.0)).astype(np.int64)
+    lo = ijk.min(0)
+    dense = np.zeros(ijk.max(0) - lo + 1, bool)
+    dense[tuple((ijk - lo).T)] = True
+    struct = ndimage.generate_binary_structure(3, 2)
+    lab, nlab = ndimage.label(dense, structure=struct)
+    mine = lab[tuple((ijk - lo).T)]
+    sizes = np.bincount(mine)
+    keep = (sizes[mine] >= 5) & (sizes[mine] <= 50000)
+    assert np.array_equal(labels >= 0, keep)
+    # same partition: one oracle label per scipy label and vice versa
+    pairs = set(zip(labels[keep].tolist(), mine[keep].tolist()))
+    assert len(pairs) == k == len(set(a for a, _ in pairs)) == len(set(b for _, b in pairs))
+    # largest first
+    csz = np.bincount(labels[labels >= 0])
+    assert np.all(np.diff(csz) <= 0)
+    # findClusterBB: centres of the extreme cells, +5 m in x, y and +3 m in z
+    for c in range(min(k, 4)):
+        pts = ctr[labels == c]
+        start, size = O.cluster_bb(pts, 0.5)
+        assert np.allclose(start, [pts[:, 0].min() - 2.5, pts[:, 1].min() - 2.5, pts[:, 2].min()])
+        assert np.allclose(size, [np.ptp(pts[:, 0]) + 5, np.ptp(pts[:, 1]) + 5, np.ptp(pts[:, 2]) + 3])
