@@ -8,6 +8,8 @@
 // is fed by ViewpointBatcher::prefetch(), which pushes the sensor poses of ALL children of an expansion
 // through one asscpp_eval_batch launch and caches the per-view results by node id.
 #pragma once
+#include <algorithm>
+#include <climits>
 #include <cmath>
 #include <map>
 #include <vector>
@@ -160,7 +162,13 @@ class CoverageHeuristicB200 {
     std::vector<geometry_msgs::Pose> flat;
     for (size_t i = 0; i < sensorPoses.size(); ++i) flat.insert(flat.end(), sensorPoses[i].begin(), sensorPoses[i].end());
     std::vector<AsscppViewResult> res;
-    oc_->evalBatch(flat, res, -1, 0);
+    std::vector<AsscppViewAccuracy> acc;
+    oc_->evalBatch(flat, res, -1, 0, &acc);
+    // :347-352: sensor clouds of more than 5 points whose average accuracy error reaches the threshold become
+    // extra clusters of the next resampling round (their poses are kept; clusterBoxOfView gives the box)
+    for (size_t k = 0; k < flat.size(); ++k)
+      if (res[k].visible > 5 && acc[k].err_sum_depth / (double)acc[k].visible >= accuracyThreshhold)
+        accuracyClusterViews.push_back(flat[k]);
     std::vector<double> p(7 * flat.size());
     for (size_t k = 0; k < flat.size(); ++k) OcclusionCulling::pack(flat[k], &p[7 * k]);
     oc_->check(asscpp_covered_or_views(oc_->context(), global_set, p.data(), (int64_t)flat.size(), 5));  // :344-346
@@ -171,6 +179,45 @@ class CoverageHeuristicB200 {
       for (size_t s = 0; s < sensorPoses[i].size(); ++s) total += res[k++].visible;
       accepted[i] = total > 5;  // :357
     }
+  }
+
+  double accuracyThreshhold = 1e300;                      // heuristic.cpp accuracyThreshhold; off unless set
+  std::vector<geometry_msgs::Pose> accuracyClusterViews;  // :350 accuracyClusters, as the views that produced them
+
+  // clusteringPointCloud (:147-190) + findClusterBB (:218-246) of the uncovered part of the model, on the device
+  void clusterUncovered(int global_set, std::vector<AsscppCluster>& clusters, double tolerance = 0.8, int minSize = 5,
+                        int maxSize = 50000) {
+    AsscppModelInfo info;
+    asscpp_model_info(oc_->context(), &info);
+    clusters.resize((size_t)std::max<int64_t>(info.n_cov_voxels, 1));
+    int64_t n = 0;
+    oc_->check(asscpp_uncovered_clusters(oc_->context(), global_set, tolerance, minSize, maxSize, nullptr,
+                                         clusters.data(), (int64_t)clusters.size(), &n));
+    clusters.resize((size_t)n);
+  }
+  // findClusterBB (:218-246) of one view's visible cloud (an accuracy cluster, pathplanner.cpp:783-786)
+  void clusterBoxOfView(const geometry_msgs::Pose& view, double gridStart[3], double gridSize[3], float leaf = 0.5f) {
+    std::vector<int32_t> idx;
+    oc_->visibleIndices(view, idx);
+    const float inv = 1.0f / leaf;
+    int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
+    for (size_t k = 0; k < idx.size(); ++k) {
+      const pcl::PointXYZ& p = oc_->cloudCopy->points[(size_t)idx[k]];
+      const float v[3] = {p.x, p.y, p.z};
+      for (int a = 0; a < 3; ++a) {
+        int c = (int)std::floor(v[a] * inv);
+        mn[a] = std::min(mn[a], c); mx[a] = std::max(mx[a], c);
+      }
+    }
+    float cmin[3], cmax[3];
+    for (int a = 0; a < 3; ++a) {
+      const float b_min = (float)mn[a] * leaf;
+      cmin[a] = (b_min + leaf * 0.5f) + (float)0 * leaf;
+      cmax[a] = (b_min + leaf * 0.5f) + (float)(mx[a] - mn[a]) * leaf;
+    }
+    gridSize[0] = std::abs(cmax[0] - cmin[0]) + 5.0; gridSize[1] = std::abs(cmax[1] - cmin[1]) + 5.0;
+    gridSize[2] = std::abs(cmax[2] - cmin[2]) + 3.0;
+    gridStart[0] = cmin[0] - 2.5; gridStart[1] = cmin[1] - 2.5; gridStart[2] = cmin[2];
   }
 
   // pointCloudDiff (:88-145): uncovered model voxels / model voxels * 100 (double arithmetic, :143)

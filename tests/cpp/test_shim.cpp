@@ -90,6 +90,15 @@ int main(int argc, char** argv) {
   int nacc = 0;
   for (size_t i = 0; i < accepted.size(); ++i) nacc += accepted[i];
   std::printf("accepted %d of %zu uncovered %.17g\n", nacc, accepted.size(), heur.uncoveredPercent(global_set));
+  {
+    std::vector<AsscppCluster> cl;
+    heur.clusterUncovered(global_set, cl);
+    std::printf("clusters %zu", cl.size());
+    for (size_t k = 0; k < cl.size() && k < 3; ++k)
+      std::printf(" | %d %.17g %.17g %.17g %.17g %.17g %.17g", cl[k].size, cl[k].grid_start[0], cl[k].grid_start[1],
+                  cl[k].grid_start[2], cl[k].grid_size[0], cl[k].grid_size[1], cl[k].grid_size[2]);
+    std::printf("\n");
+  }
   // 4. accuracy terms: the two calcAvgAccuracy overloads per view and SSMaxMinAccuracy over all poses
   oc.accumulateOcclusionFreeCloud = false;
   for (size_t k = 0; k < poses.size(); ++k) {

@@ -93,6 +93,15 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
     m = re.search(r"accepted (\d+) of (\d+) uncovered (\S+)", out)
     assert int(m.group(1)) == int((vis.sum(1) > 5).sum()) and int(m.group(2)) == len(rows)
     assert float(m.group(3)) == pytest.approx((o.n_cov - nvox) / o.n_cov * 100, rel=1e-12)
+    ids_u, ctr_u = o.uncovered(cv)
+    lab_u, k_u, _ = O.euclidean_clusters(ctr_u, 0.8, 5, 50000)
+    m = re.search(r"clusters (\d+)(.*)", out)
+    assert int(m.group(1)) == k_u
+    for c, chunk in enumerate(x for x in m.group(2).split("|") if x.strip()):
+        t = chunk.split()
+        start, size = O.cluster_bb(ctr_u[lab_u == c], 0.5)
+        assert int(t[0]) == int((lab_u == c).sum())
+        assert [float(x) for x in t[1:4]] == start.tolist() and [float(x) for x in t[4:7]] == size.tolist()
     # 4. accuracy terms (occlusion_culling.cpp:445-520): the shim's host loops are the reference's loops on the same
     #    float32 depths, so the averages are bit-identical; SSMaxMinAccuracy comes from the batched GPU extrema
     accs = dict((int(k), (float(a), float(b))) for k, a, b in re.findall(r"accuracy (\d+) pose (\S+) z (\S+)", out))
