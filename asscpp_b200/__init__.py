@@ -15,7 +15,7 @@ from ._abi import (ACCURACY_DTYPE, CLUSTER_DTYPE, EVAL_ACCURACY, EVAL_BRUTE, EVA
                    VS_GRID_GLOBAL, VS_GRID_SHARED, VS_ORDERED, ModelInfo, Params)
 
 __all__ = [
-    "CoverageContext", "CoveredSet", "AsscppError", "default_params", "synth_structure", "synth_views",
+    "CoverageContext", "CoveredSet", "Mesh", "AsscppError", "default_params", "synth_structure", "synth_views",
     "robot2sensor", "frustum_planes", "pose_rpy", "viewport_transform", "EVAL_HASH", "EVAL_BRUTE",
     "EVAL_FORCE_GLOBAL", "EVAL_ACCURACY", "RESULT_DTYPE", "ACCURACY_DTYPE",
 ]
@@ -105,6 +105,52 @@ def viewport_transform(pose, xyz):
     if rc:
         raise AsscppError(rc, "viewport_transform")
     return out
+
+
+class Mesh:
+    """Triangle mesh of the structure on the device: the CGAL sample filters of the adaptive loop
+    (coverage_path_planning_heuristic.cpp:300-335)."""
+
+    def __init__(self, vertices, triangles, device=0):
+        self.L = _abi.load()
+        v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+        t = np.ascontiguousarray(triangles, np.int32).reshape(-1, 3)
+        h = C.c_void_p()
+        rc = self.L.asscpp_mesh_create(device, _ptr(v, C.c_float), len(v), _ptr(t, C.c_int32), len(t), C.byref(h))
+        if rc:
+            raise AsscppError(rc, (self.L.asscpp_mesh_last_error(None) or b"").decode())
+        self.h = h
+        self.n_triangles = self.L.asscpp_mesh_num_triangles(self.h)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.asscpp_mesh_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _ck(self, rc):
+        if rc:
+            raise AsscppError(rc, (self.L.asscpp_mesh_last_error(self.h) or b"").decode())
+
+    def filter(self, positions, through=(100.0, 10.0, 56.0), min_dist=1.0, max_dist=4.0):
+        """(crossings of the inside-test ray, squared distance to the mesh, pass) per position."""
+        pos = np.ascontiguousarray(positions, np.float64).reshape(-1, 3)
+        thr = np.ascontiguousarray(through, np.float64)
+        hits = np.zeros(len(pos), np.int32)
+        sqd = np.zeros(len(pos), np.float64)
+        ok = np.zeros(len(pos), np.uint8)
+        self._ck(self.L.asscpp_mesh_filter(self.h, _ptr(pos, C.c_double), len(pos), _ptr(thr, C.c_double), min_dist,
+                                           max_dist, _ptr(hits, C.c_int32), _ptr(sqd, C.c_double), _ptr(ok, C.c_uint8)))
+        return hits, sqd, ok.astype(bool)
+
+    def segments_free(self, a, b):
+        a = np.ascontiguousarray(a, np.float64).reshape(-1, 3)
+        b = np.ascontiguousarray(b, np.float64).reshape(-1, 3)
+        out = np.zeros(len(a), np.uint8)
+        self._ck(self.L.asscpp_mesh_segments_free(self.h, _ptr(a, C.c_double), _ptr(b, C.c_double), len(a),
+                                                  _ptr(out, C.c_uint8)))
+        return out.astype(bool)
 
 
 class CoveredSet:

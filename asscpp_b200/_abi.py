@@ -100,6 +100,8 @@ SYMBOLS = [
     "asscpp_comm_destroy", "asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor",
     "asscpp_frustum_planes", "asscpp_get_accuracy", "asscpp_pose_rpy", "asscpp_viewport_transform",
     "asscpp_uncovered_voxels", "asscpp_uncovered_clusters",
+    "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
+    "asscpp_mesh_last_error", "asscpp_mesh_filter", "asscpp_mesh_segments_free",
 ]
 
 _lib = None
@@ -164,6 +166,13 @@ def load():
         "asscpp_get_accuracy": (i32, [vp, vp, i64]),
         "asscpp_pose_rpy": (i32, [f64p, f64p]),
         "asscpp_viewport_transform": (i32, [f64p, f32p, i64, f32p]),
+        "asscpp_mesh_create": (i32, [i32, f32p, i64, i32p, i64, C.POINTER(vp)]),
+        "asscpp_mesh_destroy": (i32, [vp]),
+        "asscpp_mesh_num_triangles": (i64, [vp]),
+        "asscpp_mesh_launch_count": (i64, [vp]),
+        "asscpp_mesh_last_error": (C.c_char_p, [vp]),
+        "asscpp_mesh_filter": (i32, [vp, f64p, i64, f64p, C.c_double, C.c_double, i32p, f64p, u8p]),
+        "asscpp_mesh_segments_free": (i32, [vp, f64p, f64p, i64, u8p]),
         "asscpp_uncovered_voxels": (i32, [vp, i32, i32p, f32p, i64, i64p]),
         "asscpp_uncovered_clusters": (i32, [vp, i32, C.c_double, C.c_int32, C.c_int32, i32p, vp, i64, i64p]),
     }

@@ -8,8 +8,10 @@ Restates the skeleton of PathPlanner::dynamicNodesGenerationAndConnection (sspp/
   * evaluate + accept    = isFilteringConditionSatisfied's coverage part (heuristic.cpp:339-357), batched
   * uncovered percentage = pointCloudDiff (heuristic.cpp:88-145) on the covered voxel bitset
   * clusters + boxes     = clusteringPointCloud / findClusterBB (heuristic.cpp:147-246)
-Deviation (stated in DESIGN.md): the CGAL inside-mesh / distance filters are replaced by a stand-off test
-against the model's voxel grid, on the host.  Viewpoint evaluation, the covered-set union, the uncovered
+  * sample filters      = isFilteringConditionSatisfied's geometric part (heuristic.cpp:317-335) through the
+                           backend's triangle mesh (asscpp_mesh_filter); a backend built without a mesh falls
+                           back to a stand-off test against the voxel lattice (synthetic models have no mesh)
+Viewpoint evaluation, the covered-set union, the uncovered
 voxel extraction, the Euclidean clustering (tolerance 0.8 m, sizes 5..50000) and the cluster boxes run on the
 GPUs (asscpp_uncovered_voxels / asscpp_uncovered_clusters), viewpoints sharded over ranks with ONE
 covered-bitset OR-allreduce per iteration.
@@ -87,14 +89,18 @@ def bits_to_ids(bits, n):
 class GpuBackend:
     """CUDA path: evaluation, union and reduction all through the C ABI."""
 
-    def __init__(self, ctx, comm=False):
-        self.ctx, self.comm = ctx, comm
+    def __init__(self, ctx, comm=False, mesh=None):
+        self.ctx, self.comm, self.mesh = ctx, comm, mesh
         self.set = ctx.new_set()
         self.n_cov = ctx.n_cov_voxels
 
     def robot2sensor(self, rp, off, rpy):
         from . import robot2sensor
         return robot2sensor(rp, off, rpy)
+
+    def filter_samples(self, positions):
+        """heuristic.cpp:317-335: outside the mesh and 1..4 m from it; None when there is no mesh."""
+        return None if self.mesh is None else self.mesh.filter(positions, (100.0, 10.0, 56.0), 1.0, 4.0)[2]
 
     def evaluate_and_accumulate(self, poses, min_visible=5):
         """visible count per pose; every view with more than min_visible points joins the covered set."""
@@ -134,7 +140,9 @@ def adaptive_loop(backend, model, grid_center, grid_size, start_res=4.5, res_dec
             robots, sensors = generate_grid(center, size, res, backend.robot2sensor)
             if len(robots) == 0:
                 continue
-            keep = model.standoff_ok(robots[:, :3])  # stand-in for heuristic.cpp:320-335
+            keep = backend.filter_samples(robots[:, :3])  # heuristic.cpp:320-335
+            if keep is None:
+                keep = model.standoff_ok(robots[:, :3])
             robots, sensors = robots[keep], sensors[keep]
             lo, hi = shard_range(len(robots), world, rank)
             flat = sensors[lo:hi].reshape(-1, 7)

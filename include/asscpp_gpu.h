@@ -182,6 +182,26 @@ typedef struct AsscppCluster {
 int asscpp_uncovered_clusters(AsscppCtx* ctx, int set, double tolerance, int32_t min_size, int32_t max_size,
                               int32_t* labels, AsscppCluster* clusters, int64_t cap, int64_t* n_clusters);
 
+/* -- geometric sample filters against the structure's triangle mesh (coverage_path_planning_heuristic.cpp:300-335;
+ *    the reference uses a CGAL AABB tree over Simple_cartesian<double> triangles) ------------------------------- */
+typedef struct AsscppMesh AsscppMesh;
+/* vertices: nv x {x y z} float32 as parsed by loadOBJFile (:1355-1451); triangles: nt x 3 vertex indices (0-based).
+ * Collinear triangles are dropped as the loader does (:1409, :1430). */
+int asscpp_mesh_create(int device, const float* vertices, int64_t nv, const int32_t* triangles, int64_t nt,
+                       AsscppMesh** out);
+int asscpp_mesh_destroy(AsscppMesh* mesh);
+int64_t asscpp_mesh_num_triangles(const AsscppMesh* mesh);
+int64_t asscpp_mesh_launch_count(const AsscppMesh* mesh);
+const char* asscpp_mesh_last_error(const AsscppMesh* mesh);
+/* isFilteringConditionSatisfied's geometric part (:319-333) for n candidate positions (n x 3 doubles, host):
+ * n_hits = triangles crossed by the ray from the position through ray_through (the reference uses (100, 10, 56)),
+ * sq_dist = squared distance to the mesh, pass = n_hits even && min_dist^2 <= sq_dist <= max_dist^2.
+ * Any output may be NULL. */
+int asscpp_mesh_filter(AsscppMesh* mesh, const double* positions, int64_t n, const double ray_through[3],
+                       double min_dist, double max_dist, int32_t* n_hits, double* sq_dist, uint8_t* pass);
+/* isConnectionConditionSatisfied (:300-315): free_out[i] = the segment a[i] -> b[i] crosses no triangle */
+int asscpp_mesh_segments_free(AsscppMesh* mesh, const double* a, const double* b, int64_t n, uint8_t* free_out);
+
 /* -- streams / timing -------------------------------------------------------------------------- */
 int asscpp_sync(AsscppCtx* ctx);
 void* asscpp_get_stream(AsscppCtx* ctx); /* cudaStream_t all kernels are launched on */

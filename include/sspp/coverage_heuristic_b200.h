@@ -12,6 +12,8 @@
 #include <climits>
 #include <cmath>
 #include <map>
+#include <stdexcept>
+#include <string>
 #include <vector>
 
 #include "../cscpp/occlusion_culling_b200.h"
@@ -220,6 +222,50 @@ class CoverageHeuristicB200 {
     gridStart[0] = cmin[0] - 2.5; gridStart[1] = cmin[1] - 2.5; gridStart[2] = cmin[2];
   }
 
+  // loadOBJFile (:1379-1437) hands vertices and faces here instead of building the CGAL AABB tree (:35-37)
+  void setMesh(const std::vector<float>& vertices_xyz, const std::vector<int32_t>& triangles, int device = 0) {
+    if (mesh_) asscpp_mesh_destroy(mesh_);
+    mesh_ = nullptr;
+    oc_->check(asscpp_mesh_create(device, vertices_xyz.data(), (int64_t)vertices_xyz.size() / 3, triangles.data(),
+                                  (int64_t)triangles.size() / 3, &mesh_));
+  }
+  ~CoverageHeuristicB200() { if (mesh_) asscpp_mesh_destroy(mesh_); }
+
+  // geometric part of isFilteringConditionSatisfied (:319-335) for a batch of robot positions: the sample is
+  // outside the mesh (ray towards (100, 10, 56) crosses it an even number of times) and minDist..maxDist from it
+  void filterPositions(const std::vector<geometry_msgs::Pose>& robotPoses, double minDist, double maxDist,
+                       std::vector<char>& pass) {
+    std::vector<double> p(3 * robotPoses.size());
+    for (size_t i = 0; i < robotPoses.size(); ++i) {
+      p[3 * i] = robotPoses[i].position.x; p[3 * i + 1] = robotPoses[i].position.y; p[3 * i + 2] = robotPoses[i].position.z;
+    }
+    const double through[3] = {100.0, 10.0, 56.0};  // :321
+    std::vector<uint8_t> ok(robotPoses.size());
+    if (asscpp_mesh_filter(mesh_, p.data(), (int64_t)robotPoses.size(), through, minDist, maxDist, nullptr, nullptr,
+                           ok.data()) != ASSCPP_OK)
+      throw std::runtime_error(std::string("asscpp_mesh_filter: ") + asscpp_mesh_last_error(mesh_));
+    pass.assign(ok.begin(), ok.end());
+  }
+
+  // isConnectionConditionSatisfied (:300-315) for a batch of candidate edges a[i] -> b[i]
+  void connectionsFree(const std::vector<geometry_msgs::Pose>& a, const std::vector<geometry_msgs::Pose>& b,
+                       std::vector<char>& free_out) {
+    std::vector<double> pa(3 * a.size()), pb(3 * a.size());
+    for (size_t i = 0; i < a.size(); ++i) {
+      pa[3 * i] = a[i].position.x; pa[3 * i + 1] = a[i].position.y; pa[3 * i + 2] = a[i].position.z;
+      pb[3 * i] = b[i].position.x; pb[3 * i + 1] = b[i].position.y; pb[3 * i + 2] = b[i].position.z;
+    }
+    std::vector<uint8_t> ok(a.size());
+    if (asscpp_mesh_segments_free(mesh_, pa.data(), pb.data(), (int64_t)a.size(), ok.data()) != ASSCPP_OK)
+      throw std::runtime_error(std::string("asscpp_mesh_segments_free: ") + asscpp_mesh_last_error(mesh_));
+    free_out.assign(ok.begin(), ok.end());
+  }
+  bool isConnectionConditionSatisfied(const geometry_msgs::Pose& a, const geometry_msgs::Pose& b) {
+    std::vector<char> f;
+    connectionsFree(std::vector<geometry_msgs::Pose>(1, a), std::vector<geometry_msgs::Pose>(1, b), f);
+    return f[0] != 0;
+  }
+
   // pointCloudDiff (:88-145): uncovered model voxels / model voxels * 100 (double arithmetic, :143)
   double uncoveredPercent(int global_set) {
     int64_t npts = 0, nvox = 0;
@@ -234,6 +280,7 @@ class CoverageHeuristicB200 {
   ViewpointBatcher batcher_;
   double target_, tol_;
   int type_;
+  AsscppMesh* mesh_ = nullptr;
 };
 
 }  // namespace SSPP

@@ -873,4 +873,126 @@ void orc_cluster_bb(const float* xyz, int64_t n, float leaf, double grid_start[3
   grid_start[2] = cmin[2];
 }
 
+// ---- mesh filters (coverage_path_planning_heuristic.cpp:300-335) ------------------------------------------
+// The reference asks a CGAL AABB tree (Simple_cartesian<double>): number_of_intersected_primitives(ray | segment)
+// and squared_distance(point).  CGAL is not vendored; restated with textbook double-precision geometry: every
+// triangle is visited, a ray / segment hits a triangle when the division-free Moeller-Trumbore parameters are in
+// range with inclusive borders, the distance is to the closest point found by Voronoi regions.  Queries grazing
+// an edge or a vertex may count differently in CGAL: PARITY UNPINNED for those (reported by orc_mesh_grazing).
+struct OrcMesh { std::vector<double> tri; };  // 9 doubles per triangle
+
+static inline double mdot(const double* a, const double* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
+
+static bool mesh_hit(const double* o, const double* d, const double* t, bool segment, double* margin) {
+  double e1[3] = {t[3] - t[0], t[4] - t[1], t[5] - t[2]}, e2[3] = {t[6] - t[0], t[7] - t[1], t[8] - t[2]};
+  double h[3] = {d[1] * e2[2] - d[2] * e2[1], d[2] * e2[0] - d[0] * e2[2], d[0] * e2[1] - d[1] * e2[0]};
+  double det = mdot(e1, h);
+  if (det == 0.0) return false;
+  double sv[3] = {o[0] - t[0], o[1] - t[1], o[2] - t[2]};
+  double u = mdot(sv, h);
+  double q[3] = {sv[1] * e1[2] - sv[2] * e1[1], sv[2] * e1[0] - sv[0] * e1[2], sv[0] * e1[1] - sv[1] * e1[0]};
+  double v = mdot(d, q), w = mdot(e2, q);
+  if (det < 0.0) { det = -det; u = -u; v = -v; w = -w; }
+  if (margin) {
+    // normalised distance of the barycentric parameters from the triangle's border (for the grazing report)
+    double m = std::min(std::min(u, v), det - (u + v)) / det;
+    *margin = std::fabs(m);
+  }
+  if (u < 0.0 || v < 0.0 || u + v > det || w < 0.0) return false;
+  return !segment || w <= det;
+}
+
+static double mesh_sqdist(const double* p, const double* t) {
+  const double *a = t, *b = t + 3, *c = t + 6;
+  double ab[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, ac[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
+  double ap[3] = {p[0] - a[0], p[1] - a[1], p[2] - a[2]};
+  double cl[3];
+  double d1 = mdot(ab, ap), d2 = mdot(ac, ap);
+  auto fin = [&]() { double e[3] = {p[0] - cl[0], p[1] - cl[1], p[2] - cl[2]}; return mdot(e, e); };
+  if (d1 <= 0.0 && d2 <= 0.0) { cl[0] = a[0]; cl[1] = a[1]; cl[2] = a[2]; return fin(); }
+  double bp[3] = {p[0] - b[0], p[1] - b[1], p[2] - b[2]};
+  double d3 = mdot(ab, bp), d4 = mdot(ac, bp);
+  if (d3 >= 0.0 && d4 <= d3) { cl[0] = b[0]; cl[1] = b[1]; cl[2] = b[2]; return fin(); }
+  double vc = d1 * d4 - d3 * d2;
+  if (vc <= 0.0 && d1 >= 0.0 && d3 <= 0.0) {
+    double v = d1 / (d1 - d3);
+    for (int k = 0; k < 3; ++k) cl[k] = a[k] + v * ab[k];
+    return fin();
+  }
+  double cp[3] = {p[0] - c[0], p[1] - c[1], p[2] - c[2]};
+  double d5 = mdot(ab, cp), d6 = mdot(ac, cp);
+  if (d6 >= 0.0 && d5 <= d6) { cl[0] = c[0]; cl[1] = c[1]; cl[2] = c[2]; return fin(); }
+  double vb = d5 * d2 - d1 * d6;
+  if (vb <= 0.0 && d2 >= 0.0 && d6 <= 0.0) {
+    double w = d2 / (d2 - d6);
+    for (int k = 0; k < 3; ++k) cl[k] = a[k] + w * ac[k];
+    return fin();
+  }
+  double va = d3 * d6 - d5 * d4;
+  if (va <= 0.0 && (d4 - d3) >= 0.0 && (d5 - d6) >= 0.0) {
+    double w = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+    for (int k = 0; k < 3; ++k) cl[k] = b[k] + w * (c[k] - b[k]);
+    return fin();
+  }
+  double denom = 1.0 / (va + vb + vc);
+  double v = vb * denom, w = vc * denom;
+  for (int k = 0; k < 3; ++k) cl[k] = a[k] + ab[k] * v + ac[k] * w;
+  return fin();
+}
+
+OrcMesh* orc_mesh_create(const float* vertices, int64_t nv, const int32_t* triangles, int64_t nt) {
+  OrcMesh* m = new OrcMesh();
+  for (int64_t k = 0; k < nt; ++k) {
+    double t[9];
+    bool ok = true;
+    for (int c = 0; c < 3; ++c) {
+      int32_t vi = triangles[3 * k + c];
+      if (vi < 0 || vi >= nv) { ok = false; break; }
+      for (int a = 0; a < 3; ++a) t[3 * c + a] = (double)vertices[3 * (int64_t)vi + a];
+    }
+    if (!ok) { delete m; return nullptr; }
+    // loadOBJFile :1409 / :1430 skips collinear triangles
+    double u[3] = {t[3] - t[0], t[4] - t[1], t[5] - t[2]}, v[3] = {t[6] - t[0], t[7] - t[1], t[8] - t[2]};
+    if (u[1] * v[2] - u[2] * v[1] == 0.0 && u[2] * v[0] - u[0] * v[2] == 0.0 && u[0] * v[1] - u[1] * v[0] == 0.0) continue;
+    m->tri.insert(m->tri.end(), t, t + 9);
+  }
+  return m;
+}
+void orc_mesh_destroy(OrcMesh* m) { delete m; }
+int64_t orc_mesh_num_triangles(const OrcMesh* m) { return (int64_t)m->tri.size() / 9; }
+
+void orc_mesh_filter(const OrcMesh* m, const double* pos, int64_t n, const double through[3], double min_dist,
+                     double max_dist, int nthreads, int32_t* hits, double* sqd, uint8_t* pass, double* graze) {
+  // isFilteringConditionSatisfied :319-333
+  const int64_t nt = (int64_t)m->tri.size() / 9;
+  parallel_views(n, nthreads, [&](Workspace&, int64_t i) {
+    const double* a = pos + 3 * i;
+    double d[3] = {through[0] - a[0], through[1] - a[1], through[2] - a[2]};
+    int32_t cnt = 0;
+    double best = INFINITY, gz = INFINITY;
+    for (int64_t k = 0; k < nt; ++k) {
+      double mg = INFINITY;
+      if (mesh_hit(a, d, &m->tri[9 * k], false, &mg)) ++cnt;
+      gz = std::min(gz, mg);
+      best = std::min(best, mesh_sqdist(a, &m->tri[9 * k]));
+    }
+    if (hits) hits[i] = cnt;
+    if (sqd) sqd[i] = best;
+    if (graze) graze[i] = gz;
+    if (pass) pass[i] = (cnt % 2 != 1) && best >= (min_dist * min_dist) && best <= (max_dist * max_dist);
+  });
+}
+
+void orc_mesh_segments_free(const OrcMesh* m, const double* a, const double* b, int64_t n, int nthreads, uint8_t* out) {
+  // isConnectionConditionSatisfied :300-315
+  const int64_t nt = (int64_t)m->tri.size() / 9;
+  parallel_views(n, nthreads, [&](Workspace&, int64_t i) {
+    double d[3] = {b[3 * i] - a[3 * i], b[3 * i + 1] - a[3 * i + 1], b[3 * i + 2] - a[3 * i + 2]};
+    int32_t cnt = 0;
+    for (int64_t k = 0; k < nt; ++k)
+      if (mesh_hit(a + 3 * i, d, &m->tri[9 * k], true, nullptr)) ++cnt;
+    out[i] = cnt == 0;
+  });
+}
+
 }  // extern "C"

@@ -121,6 +121,16 @@ int32_t orc_euclidean_clusters(const float* xyz, int64_t n, double tol, int32_t 
 /* findClusterBB (:218-246) */
 void orc_cluster_bb(const float* xyz, int64_t n, float leaf, double grid_start[3], double grid_size[3]);
 
+/* mesh filters of the adaptive loop (coverage_path_planning_heuristic.cpp:300-335); CGAL restated, see the .cpp */
+typedef struct OrcMesh OrcMesh;
+OrcMesh* orc_mesh_create(const float* vertices, int64_t nv, const int32_t* triangles, int64_t nt);
+void orc_mesh_destroy(OrcMesh* m);
+int64_t orc_mesh_num_triangles(const OrcMesh* m);
+/* graze (optional): smallest normalised distance of the ray's crossing parameters from a triangle border */
+void orc_mesh_filter(const OrcMesh* m, const double* pos, int64_t n, const double through[3], double min_dist,
+                     double max_dist, int nthreads, int32_t* hits, double* sqd, uint8_t* pass, double* graze);
+void orc_mesh_segments_free(const OrcMesh* m, const double* a, const double* b, int64_t n, int nthreads, uint8_t* out);
+
 /* 64-bit mix used for the order-independent set hashes (sum of mix(idx)) */
 uint64_t orc_mix64(uint64_t x);
 

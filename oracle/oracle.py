@@ -99,6 +99,17 @@ def lib():
         L.orc_euclidean_clusters.restype = C.c_int32
         L.orc_cluster_bb.argtypes = [f32p, i64, C.c_float, f64p, f64p]
         L.orc_cluster_bb.restype = None
+        u8p = C.POINTER(C.c_uint8)
+        L.orc_mesh_create.argtypes = [f32p, i64, i32p, i64]
+        L.orc_mesh_create.restype = vp
+        L.orc_mesh_destroy.argtypes = [vp]
+        L.orc_mesh_destroy.restype = None
+        L.orc_mesh_num_triangles.argtypes = [vp]
+        L.orc_mesh_num_triangles.restype = i64
+        L.orc_mesh_filter.argtypes = [vp, f64p, i64, f64p, C.c_double, C.c_double, C.c_int, i32p, f64p, u8p, f64p]
+        L.orc_mesh_filter.restype = None
+        L.orc_mesh_segments_free.argtypes = [vp, f64p, f64p, i64, C.c_int, u8p]
+        L.orc_mesh_segments_free.restype = None
         L.orc_mix64.argtypes = [C.c_uint64]
         L.orc_mix64.restype = C.c_uint64
         _lib = L
@@ -226,6 +237,41 @@ def viewport_transform(pose, xyz):
     out = np.zeros_like(xyz)
     lib().orc_viewport_transform(_p(pose, C.c_double), _p(xyz, C.c_float), len(xyz), _p(out, C.c_float))
     return out
+
+
+class Mesh:
+    """Mesh filters of the adaptive loop (heuristic.cpp:300-335), CPU restatement."""
+
+    def __init__(self, vertices, triangles):
+        v = np.ascontiguousarray(vertices, np.float32).reshape(-1, 3)
+        t = np.ascontiguousarray(triangles, np.int32).reshape(-1, 3)
+        self.h = lib().orc_mesh_create(_p(v, C.c_float), len(v), _p(t, C.c_int32), len(t))
+        if not self.h:
+            raise ValueError("bad mesh")
+        self.n_triangles = lib().orc_mesh_num_triangles(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            lib().orc_mesh_destroy(self.h)
+            self.h = None
+
+    def filter(self, positions, through=(100.0, 10.0, 56.0), min_dist=1.0, max_dist=4.0, nthreads=1):
+        pos = np.ascontiguousarray(positions, np.float64).reshape(-1, 3)
+        thr = np.ascontiguousarray(through, np.float64)
+        hits = np.zeros(len(pos), np.int32)
+        sqd = np.zeros(len(pos), np.float64)
+        ok = np.zeros(len(pos), np.uint8)
+        graze = np.zeros(len(pos), np.float64)
+        lib().orc_mesh_filter(self.h, _p(pos, C.c_double), len(pos), _p(thr, C.c_double), min_dist, max_dist, nthreads,
+                              _p(hits, C.c_int32), _p(sqd, C.c_double), _p(ok, C.c_uint8), _p(graze, C.c_double))
+        return hits, sqd, ok.astype(bool), graze
+
+    def segments_free(self, a, b, nthreads=1):
+        a = np.ascontiguousarray(a, np.float64).reshape(-1, 3)
+        b = np.ascontiguousarray(b, np.float64).reshape(-1, 3)
+        out = np.zeros(len(a), np.uint8)
+        lib().orc_mesh_segments_free(self.h, _p(a, C.c_double), _p(b, C.c_double), len(a), nthreads, _p(out, C.c_uint8))
+        return out.astype(bool)
 
 
 def euclidean_clusters(xyz, tol=0.8, min_size=5, max_size=50000):

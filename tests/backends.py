@@ -3,8 +3,8 @@ import numpy as np
 
 
 class OracleBackend:
-    def __init__(self, orc, O, nthreads=1):
-        self.o, self.O, self.nthreads = orc, O, nthreads
+    def __init__(self, orc, O, nthreads=1, mesh=None):
+        self.o, self.O, self.nthreads, self.mesh = orc, O, nthreads, mesh
         self.cp = np.zeros(orc.pts_words(), np.uint64)
         self.cv = np.zeros(orc.vox_words(), np.uint64)
         self.n_cov = orc.n_cov
@@ -12,6 +12,11 @@ class OracleBackend:
 
     def robot2sensor(self, rp, off, rpy):
         return self.O.robot2sensor(rp, off, rpy)
+
+    def filter_samples(self, positions):
+        if self.mesh is None:
+            return None
+        return self.mesh.filter(positions, (100.0, 10.0, 56.0), 1.0, 4.0, nthreads=self.nthreads)[2]
 
     def evaluate_and_accumulate(self, poses, min_visible=5):
         if len(poses) == 0:

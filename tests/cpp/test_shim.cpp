@@ -124,5 +124,30 @@ int main(int argc, char** argv) {
       std::printf("acc_child %zu coverage %.17g f %.17g\n", i, kid.coverage, kid.f_value);
     }
   }
+  // 6. mesh sample filters (heuristic.cpp:300-335): <mesh.txt> = "v x y z" / "f a b c" lines (0-based)
+  if (argc > 3) {
+    std::vector<float> vtx;
+    std::vector<int32_t> tri;
+    std::ifstream mf(argv[3]);
+    while (std::getline(mf, line)) {
+      std::istringstream ss(line);
+      char tag;
+      ss >> tag;
+      if (tag == 'v') { float x, y, z; ss >> x >> y >> z; vtx.push_back(x); vtx.push_back(y); vtx.push_back(z); }
+      if (tag == 'f') { int a, b, c; ss >> a >> b >> c; tri.push_back(a); tri.push_back(b); tri.push_back(c); }
+    }
+    SSPP::CoverageHeuristicB200 hm(&oc, 100.0, 1.0);
+    hm.setMesh(vtx, tri);
+    std::vector<char> pass, conn;
+    hm.filterPositions(poses, 1.0, 4.0, pass);
+    std::vector<geometry_msgs::Pose> nxt(poses.begin() + 2, poses.end());
+    nxt.push_back(poses[0]); nxt.push_back(poses[1]);
+    hm.connectionsFree(poses, nxt, conn);
+    std::printf("mesh pass");
+    for (size_t k = 0; k < pass.size(); ++k) std::printf(" %d", (int)pass[k]);
+    std::printf("\nmesh free");
+    for (size_t k = 0; k < conn.size(); ++k) std::printf(" %d", (int)conn[k]);
+    std::printf("\nmesh single %d\n", (int)hm.isConnectionConditionSatisfied(poses[0], nxt[0]));
+  }
   return 0;
 }

@@ -44,7 +44,13 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
     rows = [600, 610, 633, 700, 742, 815, 900, 1010]
     poses = np.stack([space_2p5[c][k] for k in rows for c in ("cam0", "cam1")])
     np.savetxt(str(tmp_path / "poses.txt"), poses, fmt="%.17g")
-    out = subprocess.check_output([exe, pcd, str(tmp_path / "poses.txt")], text=True)
+    g = np.load(os.path.join(ROOT, "tests", "golden", "etihad_mesh.npz"))
+    with open(str(tmp_path / "mesh.txt"), "w") as f:
+        for v in g["vertices"]:
+            f.write("v %.9g %.9g %.9g\n" % tuple(v))
+        for t in g["triangles"]:
+            f.write("f %d %d %d\n" % tuple(t))
+    out = subprocess.check_output([exe, pcd, str(tmp_path / "poses.txt"), str(tmp_path / "mesh.txt")], text=True)
     o = O.Oracle(xyz)
     assert re.search(r"model %d points OriginalVoxelsSize 2759" % len(xyz), out)
     # 1. per-view visible set and calcCoveragePercent
@@ -142,3 +148,11 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
         avg = float(np.sum(0.0000285 * z * z)) / len(both)
         a = (max_err - avg) / max_err
         assert float(f_s) == pytest.approx(cov0 + (1 / d) * (cov_i - cov0) * a, rel=1e-12, abs=1e-12)
+    # 6. mesh sample filters (heuristic.cpp:300-335)
+    om = O.Mesh(g["vertices"], g["triangles"])
+    nxt = np.concatenate([poses[2:], poses[:2]])
+    assert [int(x) for x in re.search(r"mesh pass(.*)", out).group(1).split()] == \
+        om.filter(poses[:, :3], (100.0, 10.0, 56.0), 1.0, 4.0)[2].astype(int).tolist()
+    free = om.segments_free(poses[:, :3], nxt[:, :3]).astype(int).tolist()
+    assert [int(x) for x in re.search(r"mesh free(.*)", out).group(1).split()] == free
+    assert int(re.search(r"mesh single (\d)", out).group(1)) == free[0]

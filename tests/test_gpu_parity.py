@@ -274,9 +274,12 @@ def test_full_size_properties_10m(A):
     ctx.close()
 
 
-def test_config4_adaptive_loop(A, oracle_mod, etihad):
+@pytest.mark.parametrize("with_mesh", [True, False])
+def test_config4_adaptive_loop(A, oracle_mod, etihad, with_mesh):
     """Config 4: the ASSCPP adaptive loop (pathplanner.cpp:729-850 skeleton) driven by the CUDA path and by
-    the oracle: identical candidate lists, identical covered bitset and acceptance count per iteration."""
+    the oracle: identical candidate lists, identical covered bitset and acceptance count per iteration.
+    with_mesh: samples filtered by the structure's triangle mesh (heuristic.cpp:317-335, asscpp_mesh_filter);
+    without: the voxel stand-off fallback used for models that have no mesh."""
     import sys
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
     from asscpp_b200 import adaptive as AD
@@ -285,14 +288,22 @@ def test_config4_adaptive_loop(A, oracle_mod, etihad):
     model = AD.VoxelModel(xyz, 0.5)
     ctx = A.CoverageContext(xyz, A.default_params())
     assert model.n == ctx.n_cov_voxels
-    tg = AD.adaptive_loop(AD.GpuBackend(ctx), model, (0, 0, 4.5), (36, 50, 9))
-    to = AD.adaptive_loop(OracleBackend(oracle_mod.Oracle(xyz), oracle_mod, NTHREADS), model, (0, 0, 4.5), (36, 50, 9))
+    gmesh = omesh = None
+    if with_mesh:
+        g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "etihad_mesh.npz"))
+        gmesh, omesh = A.Mesh(g["vertices"], g["triangles"]), oracle_mod.Mesh(g["vertices"], g["triangles"])
+    tg = AD.adaptive_loop(AD.GpuBackend(ctx, mesh=gmesh), model, (0, 0, 4.5), (36, 50, 9))
+    to = AD.adaptive_loop(OracleBackend(oracle_mod.Oracle(xyz), oracle_mod, NTHREADS, mesh=omesh), model, (0, 0, 4.5),
+                          (36, 50, 9))
     assert len(tg) == len(to) >= 3
     for a, b in zip(tg, to):
         assert a["candidates"] == b["candidates"] and a["accepted"] == b["accepted"]
         assert np.array_equal(a["bits"], b["bits"])
         assert a["uncovered_pct"] == b["uncovered_pct"] and a["clusters"] == b["clusters"]
     assert tg[-1]["uncovered_pct"] < 1.0
+    if with_mesh:
+        assert [t["candidates"] for t in tg[:3]] == [480, 184, 472]
+        gmesh.close()
     ctx.close()
 
 
