@@ -277,6 +277,14 @@ class CoverageContext:
     def eval_batch(self, poses, covered=None, flags=0):
         return self.results(self.eval_async(poses, covered, flags))
 
+    def eval_groups(self, poses, group_size, covered=None, flags=0):
+        """One A* expansion (astar.cpp:311-330): poses [n_candidates * group_size, 7], the sensors of a candidate
+        consecutive.  gain_vox summed over a group = coverage voxels the candidate adds to `covered`."""
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        self._ck(self.L.asscpp_eval_groups(self.h, _ptr(poses, C.c_double), poses.shape[0], int(group_size),
+                                           -1 if covered is None else covered.handle, flags))
+        return self.results(poses.shape[0])
+
     def accuracy(self, nviews):
         """Accuracy terms of the last evaluation issued with EVAL_ACCURACY (AsscppViewAccuracy per view)."""
         out = np.zeros(nviews, ACCURACY_DTYPE)

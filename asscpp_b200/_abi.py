@@ -100,7 +100,7 @@ SYMBOLS = [
     "asscpp_comm_destroy", "asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor",
     "asscpp_frustum_planes", "asscpp_get_accuracy", "asscpp_pose_rpy", "asscpp_viewport_transform",
     "asscpp_uncovered_voxels", "asscpp_uncovered_clusters",
-    "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
+    "asscpp_eval_groups", "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
     "asscpp_mesh_last_error", "asscpp_mesh_filter", "asscpp_mesh_segments_free",
 ]
 
@@ -130,6 +130,7 @@ def load():
         "asscpp_model_info": (i32, [vp, C.POINTER(ModelInfo)]),
         "asscpp_default_params": (None, [C.POINTER(Params)]),
         "asscpp_eval_batch": (i32, [vp, f64p, i64, i32, C.c_uint32]),
+        "asscpp_eval_groups": (i32, [vp, f64p, i64, i32, i32, C.c_uint32]),
         "asscpp_get_results": (i32, [vp, vp, i64]),
         "asscpp_get_counts": (i32, [vp, u32p, u32p, u32p, i64]),
         "asscpp_get_gain": (i32, [vp, u32p, u32p, i64]),

@@ -217,8 +217,9 @@ int ensure_views(AsscppCtx* c, int64_t nviews) {
 
 // planes -> eval -> ordered, all on the context's stream
 int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_set, int accum_set,
-             int64_t accum_min_visible, uint32_t flags, const double* h_poses = nullptr) {
+             int64_t accum_min_visible, uint32_t flags, const double* h_poses = nullptr, int group = 1) {
   if (nviews < 0 || nviews > 0x7fffffffLL) { c->err = "nviews out of range"; return ASSCPP_EINVAL; }
+  if (group < 1) { c->err = "group size must be at least 1"; return ASSCPP_EINVAL; }
   if (covered_set != -1 && !valid_set(c, covered_set)) { c->err = "bad covered set handle"; return ASSCPP_EINVAL; }
   if (accum_set != -1 && !valid_set(c, accum_set)) { c->err = "bad accumulator set handle"; return ASSCPP_EINVAL; }
   c->last_nviews = nviews;
@@ -262,12 +263,13 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.walk_thresh = c->walk_thresh;
   a.grid_scratch = c->d_grid_scratch; a.grid_cap_words = c->grid_cap_words;
   a.cov_scratch = c->d_cov_scratch; a.cov_words = c->cov_words;
+  a.group = group; a.cov_direct = (c->m.cov_same && group == 1) ? 1 : 0;
   a.vstate = c->d_vstate;
   a.ordered_list = c->d_ordered_list;
   a.ordered_count = c->d_counters + 1;
   a.smem_grid_words = c->smem_grid_words;
   a.phase_cycles = c->d_phase;
-  int ctas = (int)std::min<int64_t>(c->ctas, nviews);
+  int ctas = (int)std::min<int64_t>(c->ctas, (nviews + group - 1) / group);
   std::pair<cudaEvent_t, cudaEvent_t>* evp = nullptr;
   if (c->timing) {
     if (c->kernel_events_used == c->kernel_events.size()) {
@@ -516,6 +518,17 @@ int asscpp_eval_batch(AsscppCtx* c, const double* poses, int64_t nviews, int cov
   if (nviews > 0)
     CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   return run_eval(c, c->d_poses, nviews, covered_set, -1, 0, flags, poses);
+}
+
+int asscpp_eval_groups(AsscppCtx* c, const double* poses, int64_t nviews, int group_size, int covered_set,
+                       uint32_t flags) {
+  if (!c || (!poses && nviews > 0) || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = ensure_views(c, nviews);
+  if (rc) return rc;
+  if (nviews > 0)
+    CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  return run_eval(c, c->d_poses, nviews, covered_set, -1, 0, flags, poses, group_size);
 }
 
 int asscpp_get_results(AsscppCtx* c, AsscppViewResult* out, int64_t nviews) {

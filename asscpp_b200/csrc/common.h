@@ -95,6 +95,8 @@ struct EvalArgs {
   int64_t grid_cap_words;
   uint32_t* cov_scratch;     // [ctas][cov_words] per-view coverage-voxel marks
   int64_t cov_words;
+  int group;                 // views per candidate (sensors of one node): cov_scratch is kept across a group
+  int cov_direct;            // coverage lattice == occlusion lattice and group == 1: no marks needed
   uint8_t* vstate;           // [ordered ctas][n_vox] per-voxel state for the ordered (Q5) path
   int32_t* ordered_list;     // views that saw a Q5 carry
   int32_t* ordered_count;

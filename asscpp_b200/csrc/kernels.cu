@@ -797,7 +797,7 @@ __device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const View
     const uint32_t id = (uint32_t)vcov, bit = 1u << (id & 31);
     if (mode == 0) {
       // several occlusion voxels share a coverage voxel: cov_scratch marks the ones already counted for this view
-      uint32_t old = m.cov_same ? 0u : atomicOr(&cov_scratch[id >> 5], bit);
+      uint32_t old = A.cov_direct ? 0u : atomicOr(&cov_scratch[id >> 5], bit);
       if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
     } else {
       atomicOr(&A.accum.vox[id >> 5], bit);
@@ -1355,14 +1355,34 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
   uint32_t* glob_grid = A.grid_scratch + (int64_t)blockIdx.x * A.grid_cap_words;
   uint32_t* cov_scratch = A.cov_scratch + (int64_t)blockIdx.x * A.cov_words;
   uint32_t* vis_list = A.vis_list + (int64_t)blockIdx.x * A.vis_cap;
-  __shared__ int s_view;
+  // views are handed out in groups of A.group consecutive views (the sensors of one candidate); within a group
+  // the coverage-voxel marks are kept, so gain_vox of a later view counts only voxels no earlier view of the
+  // group has seen: the group's gain_vox sum is the gain of the union (heuristic.cpp:439-445, 473-483)
+  __shared__ int s_view, s_end, s_first, s_dirty;
+  if (threadIdx.x == 0) { s_view = -1; s_end = 0; s_dirty = 0; }
   const long long k_start = clock64();
   for (;;) {
     __syncthreads();
-    if (threadIdx.x == 0) s_view = atomicAdd(A.work_counter, 1);
+    if (threadIdx.x == 0) {
+      int nv = s_view + 1;
+      s_first = 0;
+      if (nv >= s_end) {
+        const long long g = atomicAdd(A.work_counter, 1);
+        const long long b = g * A.group;
+        nv = (int)(b < A.nviews ? b : A.nviews);
+        s_end = (int)(b + A.group < A.nviews ? b + A.group : A.nviews);
+        s_first = 1;
+      }
+      s_view = nv;
+    }
     __syncthreads();
     const int v = s_view;
     if (v >= A.nviews) break;
+    if (s_first && s_dirty) {
+      for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
+      __syncthreads();
+      if (threadIdx.x == 0) s_dirty = 0;
+    }
     long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
     const bool prof = A.phase_cycles != nullptr && threadIdx.x == 0;
     if (prof) t0 = clock64();
@@ -1437,9 +1457,7 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
       acc_commit(sh, acc);
       __syncthreads();
     }
-    if (!m.cov_same && sh.visible) {
-      for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
-    }
+    if (!A.cov_direct && sh.visible && threadIdx.x == 0) s_dirty = 1;  // marks are cleared before the next group
     if (sh.carry) {
       // quirk Q5: at least one ray failed; the sticky `state` makes the result order dependent.
       // Hand the view to ordered_views_kernel, which replays the reference loop exactly.
@@ -1469,6 +1487,8 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
       atomicAdd(&A.phase_cycles[4], 1ull);
     }
   }
+  if (s_dirty)  // ordered_views_kernel expects clean marks
+    for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
   if (A.phase_cycles != nullptr && threadIdx.x == 0) atomicAdd(&A.phase_cycles[5], (unsigned long long)clock64() - (unsigned long long)k_start);
 }
 

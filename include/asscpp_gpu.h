@@ -125,6 +125,15 @@ void asscpp_default_params(AsscppParams* p);
  * covered_set: handle from asscpp_covered_new to score gains against, or -1 for the empty set.
  * Asynchronous on the context's stream; results are fetched with asscpp_get_results. */
 int asscpp_eval_batch(AsscppCtx* ctx, const double* poses, int64_t nviews, int covered_set, uint32_t flags);
+/* Child scoring for one A* expansion (sspp/src/astar.cpp:311-330): views [g * group_size, (g + 1) * group_size)
+ * are the sensor poses of candidate g (Node::senPoses).  Same evaluation as asscpp_eval_batch, except that
+ * gain_vox of a view counts only coverage voxels that are neither in covered_set nor seen by an earlier view
+ * of its group, so the sum over a group is the gain of the union of the sensors' visible clouds
+ * (calculateHeuristic's visibleCloud, heuristic.cpp:439-445, scored as :473-483).  gain_pts stays per view.
+ * A group containing a view with ASSCPP_VS_ORDERED set (quirk Q5 replay) is not union-exact: score it with
+ * asscpp_covered_clone + asscpp_covered_or_views instead. */
+int asscpp_eval_groups(AsscppCtx* ctx, const double* poses, int64_t nviews, int group_size, int covered_set,
+                       uint32_t flags);
 int asscpp_get_results(AsscppCtx* ctx, AsscppViewResult* out, int64_t nviews); /* synchronises */
 int asscpp_get_counts(AsscppCtx* ctx, uint32_t* survivors, uint32_t* visible, uint32_t* carry, int64_t nviews);
 int asscpp_get_gain(AsscppCtx* ctx, uint32_t* gain_pts, uint32_t* gain_vox, int64_t nviews);

@@ -34,18 +34,25 @@ struct NodeB200 {
 class ViewpointBatcher {
  public:
   explicit ViewpointBatcher(OcclusionCulling* oc) : oc_(oc) {}
-  // One launch for every sensor pose of every child; scored against the parent's covered set.
+  // One launch for every sensor pose of every child, scored against the parent's covered set
+  // (asscpp_eval_groups: a child's gain_vox sum is the gain of the union of its sensors' visible clouds).
+  // Children must carry the same number of sensors (they do: Robot::sensors, sspp/src/astar.cpp:420-433).
   void prefetch(NodeB200* const* children, int n, int parent_set) {
-    std::vector<geometry_msgs::Pose> poses;
+    std::vector<double> p;
     std::vector<std::pair<int, int> > owner;  // (node id, sensor)
+    const size_t per = n > 0 ? children[0]->senPoses.size() : 0;
     for (int i = 0; i < n; ++i)
       for (size_t s = 0; s < children[i]->senPoses.size(); ++s) {
-        poses.push_back(children[i]->senPoses[s]);
+        p.resize(p.size() + 7);
+        OcclusionCulling::pack(children[i]->senPoses[s], &p[p.size() - 7]);
         owner.push_back(std::make_pair(children[i]->id, (int)s));
       }
-    std::vector<AsscppViewResult> res;
-    oc_->evalBatch(poses, res, parent_set, 0);
+    if (owner.empty() || per == 0) return;
+    oc_->check(asscpp_eval_groups(oc_->context(), p.data(), (int64_t)owner.size(), (int)per, parent_set, 0));
+    std::vector<AsscppViewResult> res(owner.size());
+    oc_->check(asscpp_get_results(oc_->context(), res.data(), (int64_t)res.size()));
     for (size_t k = 0; k < res.size(); ++k) cache_[owner[k]] = res[k];
+    parent_set_ = parent_set;
     launches_++;
   }
   bool lookup(int node_id, int sensor, AsscppViewResult* out) const {
@@ -54,12 +61,26 @@ class ViewpointBatcher {
     *out = it->second;
     return true;
   }
-  void clear() { cache_.clear(); }
+  // voxels the node adds to the set it was prefetched against; false when not cached or when one of its views
+  // took the ordered replay (quirk Q5), whose group sum is not union-exact
+  bool groupGain(const NodeB200* node, int parent_set, unsigned long long* gain) const {
+    if (parent_set != parent_set_ || node->senPoses.empty()) return false;
+    unsigned long long g = 0;
+    for (size_t s = 0; s < node->senPoses.size(); ++s) {
+      AsscppViewResult r;
+      if (!lookup(node->id, (int)s, &r) || (r.status & ASSCPP_VS_ORDERED)) return false;
+      g += r.gain_vox;
+    }
+    *gain = g;
+    return true;
+  }
+  void clear() { cache_.clear(); parent_set_ = -2; }
   int launches() const { return launches_; }
 
  private:
   OcclusionCulling* oc_;
   std::map<std::pair<int, int>, AsscppViewResult> cache_;
+  int parent_set_ = -2;
   int launches_ = 0;
 };
 
@@ -86,20 +107,18 @@ class CoverageHeuristicB200 {
   void calculateHeuristic(NodeB200* node) {
     if (!node) return;
     AsscppCtx* c = oc_->context();
-    if (node->covered_set < 0) {
-      if (node->parent && node->parent->covered_set >= 0)
-        oc_->check(asscpp_covered_clone(c, node->parent->covered_set, &node->covered_set));  // :473 parent's cloud
-      else
-        oc_->check(asscpp_covered_new(c, &node->covered_set));
-    }
-    std::vector<double> p(7 * node->senPoses.size());
-    for (size_t s = 0; s < node->senPoses.size(); ++s) OcclusionCulling::pack(node->senPoses[s], &p[7 * s]);
-    // visibleCloud += extractVisibleSurface(senPoses[i]) for every sensor (:439-445); union into the set (:474-480)
-    oc_->check(asscpp_covered_or_views(c, node->covered_set, p.data(), (int64_t)node->senPoses.size(), -1));
+    // children of an expansion that went through batcher().prefetch() are scored from the cached group gains:
+    // no launch here, and the child's covered set is only made if the node is expanded later (ensureSet)
+    unsigned long long cachedGain = 0;
+    const bool cached = node->parent && type_ != SurfaceCoveragewithAccuracyH && node->covered_set < 0 &&
+                        node->parent->covered_set >= 0 && batcher_.groupGain(node, node->parent->covered_set, &cachedGain);
+    if (!cached) ensureSet(node);
     double a = 1.0;
     if (type_ == SurfaceCoveragewithAccuracyH && node->parent) {
       // a = (maxAccuracyError - calcAvgAccuracy(visibleCloud)) / maxAccuracyError (:493-494, :836-838); the
       // one-argument overload averages 0.0000285 z^2 over the concatenated sensor clouds
+      std::vector<double> p(7 * node->senPoses.size());
+      for (size_t s = 0; s < node->senPoses.size(); ++s) OcclusionCulling::pack(node->senPoses[s], &p[7 * s]);
       oc_->check(asscpp_eval_batch(c, p.data(), (int64_t)node->senPoses.size(), -1, ASSCPP_EVAL_ACCURACY));
       std::vector<AsscppViewAccuracy> acc(node->senPoses.size());
       oc_->check(asscpp_get_accuracy(c, acc.data(), (int64_t)acc.size()));
@@ -110,7 +129,15 @@ class CoverageHeuristicB200 {
       a = (oc_->maxAccuracyError - avgAcc) / oc_->maxAccuracyError;
     }
     float pct = 0;
-    oc_->check(asscpp_coverage_percent(c, node->covered_set, &pct));  // :482
+    if (cached) {
+      int64_t npts = 0, nvox = 0;
+      oc_->check(asscpp_covered_popcount(c, node->parent->covered_set, &npts, &nvox));
+      AsscppModelInfo info;
+      asscpp_model_info(c, &info);
+      pct = (float)(nvox + (int64_t)cachedGain) / (float)info.n_cov_voxels * 100.0f;  // occlusion_culling.cpp:431-432
+    } else {
+      oc_->check(asscpp_coverage_percent(c, node->covered_set, &pct));  // :482
+    }
     node->coverage = pct;
     if (node->parent) {
       double dx = node->pose.position.x - node->parent->pose.position.x,
@@ -147,6 +174,25 @@ class CoverageHeuristicB200 {
       node->distance = 0; node->h_value = 0; node->g_value = 0;
       node->f_value = node->coverage;  // root: :1232-1238
     }
+  }
+
+  // Node::cloud_filtered in covered-set form: the parent's set OR the node's own sensor views (:439-445, :473-480).
+  // calculateHeuristic calls it for nodes that were not prefetched; a prefetched node gets its set here when it is
+  // taken from the open list for expansion (sspp/src/astar.cpp:262), one launch per EXPANDED node instead of one per
+  // child.  The parent chain must still be alive (it is: closed-list nodes are kept until the search ends).
+  void ensureSet(NodeB200* node) {
+    if (node->covered_set >= 0) return;
+    AsscppCtx* c = oc_->context();
+    if (node->parent) {
+      ensureSet(node->parent);
+      oc_->check(asscpp_covered_clone(c, node->parent->covered_set, &node->covered_set));  // :473 parent's cloud
+    } else {
+      oc_->check(asscpp_covered_new(c, &node->covered_set));
+    }
+    std::vector<double> p(7 * node->senPoses.size());
+    for (size_t s = 0; s < node->senPoses.size(); ++s) OcclusionCulling::pack(node->senPoses[s], &p[7 * s]);
+    // visibleCloud += extractVisibleSurface(senPoses[i]) for every sensor (:439-445); union into the set (:474-480)
+    oc_->check(asscpp_covered_or_views(c, node->covered_set, p.data(), (int64_t)node->senPoses.size(), -1));
   }
 
   // coverage_path_planning_heuristic.cpp:253-283

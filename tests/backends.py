@@ -37,3 +37,31 @@ class OracleBackend:
         ids, ctr = self.o.uncovered(self.cv)
         labels, k, _ = self.O.euclidean_clusters(ctr, 0.8, 5, 50000)
         return len(ids), [self.O.cluster_bb(ctr[labels == c], 0.5) for c in range(k)]
+
+
+class OracleScorer:
+    """Oracle-side scorer of asscpp_b200.search.astar_search: calculateHeuristic's SurfaceCoverageH blocks
+    (heuristic.cpp:439-445, 470-488) literally -- visible cloud of every sensor, union with the parent's covered
+    voxels, coverage percent -- one child at a time."""
+
+    def __init__(self, orc, O, accumulate=False):
+        self.o, self.O, self.accumulate = orc, O, accumulate
+        self.ids = orc.cov_ids()
+        self.cache = {}
+
+    def _voxels(self, pose):
+        key = pose.tobytes()
+        if key not in self.cache:
+            self.cache[key] = np.unique(self.ids[self.o.eval_view(pose)["visible"]])
+        return self.cache[key]
+
+    def score(self, parent_state, sensors):
+        from asscpp_b200.search import coverage_percent
+        cov, states = [], []
+        for sen in np.asarray(sensors, np.float64):
+            own = [self._voxels(p) for p in sen]
+            base = parent_state if (self.accumulate and parent_state is not None) else np.zeros(0, np.int64)
+            u = np.unique(np.concatenate([base] + own))
+            cov.append(coverage_percent(len(u), self.o.n_cov))
+            states.append(u)
+        return cov, states

@@ -76,10 +76,12 @@ int main(int argc, char** argv) {
     }
     std::printf("step %d best %d coverage %.17g f %.17g\n", step, kids[(size_t)best].id, kids[(size_t)best].coverage,
                 kids[(size_t)best].f_value);
+    heur.ensureSet(&kids[(size_t)best]);  // the chosen node is the next one expanded (astar.cpp:262)
     path.push_back(kids[(size_t)best]);
     path.back().parent = nullptr;  // the walk keeps only coverage / f / set of the chosen node
     path.back().distance = 0;
   }
+  std::printf("walk launches %d\n", heur.batcher().launches());
   // 3. ASSCPP acceptance rule + uncovered percentage
   int global_set = -1;
   oc.check(asscpp_covered_new(oc.context(), &global_set));

@@ -89,6 +89,7 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
         assert int(best) == ibest, (s, best, ibest)
         assert float(c_s) == pytest.approx(cbest, abs=1e-6) and float(f_s) == pytest.approx(fbest, rel=1e-12, abs=1e-9)
         covered, cov, fval, cur = ubest, cbest, fbest, ibest
+    assert int(re.search(r"walk launches (\d+)", out).group(1)) == 4  # one scoring launch per expansion
     # 3. acceptance rule (:339-357) and uncovered percentage (:143)
     st = o.eval_batch(poses, memo=True)
     vis = st[:, O.ST_VISIBLE].reshape(-1, 2)
