@@ -274,6 +274,34 @@ def test_full_size_properties_10m(A):
     ctx.close()
 
 
+def test_config3_parity_subset_10m(A, oracle_mod):
+    """BASELINE config 3 (10M points, 100k-view pool, 0.05 m grid): a random 1 024-view subset against the oracle,
+    every integer field and both set hashes bit-exact."""
+    xyz = A.synth_structure(10_000_000)
+    pool = A.synth_views(100_000)
+    sub = pool[np.random.default_rng(3).choice(len(pool), 1024, replace=False)]
+    ctx = A.CoverageContext(xyz, A.default_params(leaf=0.05, cov_leaf=0.5))
+    orc = oracle_mod.Oracle(xyz, oracle_mod.make_params(leaf=0.05, cov_leaf=0.5))
+    res = ctx.eval_batch(sub, flags=A.EVAL_HASH)
+    st = orc.eval_batch(sub, memo=True, nthreads=NTHREADS)
+    assert_results_equal(oracle_mod, res, st, "config 3 subset")
+    assert res["visible"].sum() > 0
+    ctx.close()
+
+
+def test_config5_parity_subset_50m(A, oracle_mod):
+    """BASELINE config 5 size (50M points, 0.05 m grid): 256 views of the sweep against the oracle."""
+    xyz = A.synth_structure(50_000_000)
+    sub = A.synth_views(1_000_000)[np.random.default_rng(5).choice(1_000_000, 256, replace=False)]
+    ctx = A.CoverageContext(xyz, A.default_params(leaf=0.05, cov_leaf=0.5))
+    orc = oracle_mod.Oracle(xyz, oracle_mod.make_params(leaf=0.05, cov_leaf=0.5))
+    res = ctx.eval_batch(sub, flags=A.EVAL_HASH)
+    st = orc.eval_batch(sub, memo=True, nthreads=NTHREADS)
+    assert_results_equal(oracle_mod, res, st, "config 5 subset")
+    assert res["visible"].sum() > 0
+    ctx.close()
+
+
 @pytest.mark.parametrize("with_mesh", [True, False])
 def test_config4_adaptive_loop(A, oracle_mod, etihad, with_mesh):
     """Config 4: the ASSCPP adaptive loop (pathplanner.cpp:729-850 skeleton) driven by the CUDA path and by
