@@ -85,6 +85,7 @@ struct AsscppCtx {
   uint4* d_ray_buf = nullptr;
   int64_t ray_cap = 0;
   int walk_thresh = 16;
+  int setup_iters = 1, halo_iters = 3;
   uint8_t* d_vstate = nullptr;
   int32_t* d_counters = nullptr;  // [0] work counter, [1] ordered count
   unsigned long long* d_pop = nullptr;  // 2 popcount cells
@@ -261,6 +262,7 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.vis_list = c->d_vis_list; a.vis_cap = c->vis_cap;
   a.ray_buf = c->d_ray_buf; a.ray_cap = c->ray_cap;
   a.walk_thresh = c->walk_thresh;
+  a.setup_iters = c->setup_iters; a.halo_iters = c->halo_iters;
   a.grid_scratch = c->d_grid_scratch; a.grid_cap_words = c->grid_cap_words;
   a.cov_scratch = c->d_cov_scratch; a.cov_words = c->cov_words;
   a.group = group; a.cov_direct = (c->m.cov_same && group == 1) ? 1 : 0;
@@ -455,6 +457,8 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = dev_alloc(c, &c->d_vis_list, c->vis_cap * c->ctas))) return fail(rc);
   c->ray_cap = ray_queue_cap();  // records per warp queue; 32 warps per CTA
   if ((rc = dev_alloc(c, &c->d_ray_buf, 3 * c->ray_cap * 32 * c->ctas))) return fail(rc);
+  if (const char* e = getenv("ASSCPP_HALO_ITERS")) c->halo_iters = std::max(0, std::min(64, atoi(e)));
+  if (const char* e = getenv("ASSCPP_SETUP_ITERS")) c->setup_iters = std::max(1, std::min(64, atoi(e)));
   if (const char* wt = getenv("ASSCPP_WALK_THRESH")) c->walk_thresh = std::max(1, std::min(32, atoi(wt)));
   if ((rc = dev_alloc(c, &c->d_grid_scratch, c->grid_cap_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_cov_scratch, c->cov_words * c->ctas))) return fail(rc);

@@ -95,6 +95,8 @@ struct EvalArgs {
   int64_t grid_cap_words;
   uint32_t* cov_scratch;     // [ctas][cov_words] per-view coverage-voxel marks
   int64_t cov_words;
+  int halo_iters;            // ... plus at most this many more while the ray is still in the halo layer
+  int setup_iters;           // DDA iterations done in the converged ray setup before a ray is queued
   int group;                 // views per candidate (sensors of one node): cov_scratch is kept across a group
   int cov_direct;            // coverage lattice == occlusion lattice and group == 1: no marks needed
   uint8_t* vstate;           // [ordered ctas][n_vox] per-voxel state for the ordered (Q5) path

@@ -934,7 +934,7 @@ struct RayQueue {
 template <bool SMEM>
 __device__ __forceinline__ int setup_ray(const ModelDev& m, const GridView& g, const GridMem& gm, const float origin[3],
                                          uint32_t u, uint4& ra, float4& rb, float4& rc, unsigned& steps,
-                                         unsigned& fails) {
+                                         unsigned& fails, int setup_iters, int halo_iters) {
   if (u == 0xffffffffu) return 0;
   const int4 vx = m.vox[u & kVoxMask];
   const int rt[3] = {vx.x - g.min_b[0], vx.y - g.min_b[1], vx.z - g.min_b[2]};
@@ -959,18 +959,38 @@ __device__ __forceinline__ int setup_ray(const ModelDev& m, const GridView& g, c
   if (!((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
         (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1)))
     return 1;                                // :538-540 false on entry: result 0, no iteration
-  // first iteration; rays that go on are counted in the walk from their start cell
-  if (r[0] == rt[0] && r[1] == rt[1] && r[2] == rt[2]) { ++steps; return 1; }  // :551-552
-  if (cell_occupied<SMEM>(g, gm, r[0], r[1], r[2]) && is_occluder(g, r[0], r[1], r[2], rt[0], rt[1], rt[2])) {
-    ++steps;                                 // occluded by its start cell
-    return 0;
-  }
+  // the first iterations (:538-579) here, where the cell coordinates are at hand and all lanes are converged: at
+  // least one, then on while the walk is still in the halo layer (a cell outside the survivors' box, the expensive
+  // case for the walk) or has done fewer than setup_iters.  Short rays never reach the queue.  Rays that end here
+  // count their iterations; rays that go on are counted in the walk from their start cell.
   const int P0 = g.P0, P01 = g.P01;
-  int p = (r[0] + 2) + (r[1] + 2) * P0 + (r[2] + 2) * P01;
+  const int rs[3] = {r[0], r[1], r[2]};
   float tx = t_max[0], ty = t_max[1], tz = t_max[2];
-  dda_step(tx, ty, tz, p, t_delta[0], t_delta[1], t_delta[2], step[0], step[1] * P0, step[2] * P01);
-  ra = make_uint4((unsigned)p, u, (unsigned)(r[0] + 2) | ((unsigned)(r[1] + 2) << 16),
-                  (unsigned)(r[2] + 2) | ((unsigned)(rt[2] + 2) << 16));
+#pragma unroll 1
+  for (int it = 0;; ++it) {
+    if (r[0] == rt[0] && r[1] == rt[1] && r[2] == rt[2]) { steps += it + 1; return 1; }  // :551-552
+    if (cell_occupied<SMEM>(g, gm, r[0], r[1], r[2]) && is_occluder(g, r[0], r[1], r[2], rt[0], rt[1], rt[2])) {
+      steps += it + 1;                       // occluded (early exit: the result stays 1)
+      return 0;
+    }
+    // :565-579, ties x -> y -> z by <=; NaN compares false and falls through to z
+    const bool sx = (tx <= ty) & (tx <= tz);
+    const bool sy = (!sx) & (ty <= tz) & (ty <= tx);
+    if (sx) { tx = fadd(tx, t_delta[0]); r[0] += step[0]; }
+    else if (sy) { ty = fadd(ty, t_delta[1]); r[1] += step[1]; }
+    else { tz = fadd(tz, t_delta[2]); r[2] += step[2]; }
+    if (!((unsigned)(r[0] + 1) <= (unsigned)(g.div[0] + 1) && (unsigned)(r[1] + 1) <= (unsigned)(g.div[1] + 1) &&
+          (unsigned)(r[2] + 1) <= (unsigned)(g.div[2] + 1))) {
+      steps += it + 1;                       // :538-540 false: left the expanded box, result 0
+      return 1;
+    }
+    const bool interior = (unsigned)r[0] < (unsigned)g.div[0] && (unsigned)r[1] < (unsigned)g.div[1] &&
+                          (unsigned)r[2] < (unsigned)g.div[2];
+    if ((interior && it + 1 >= setup_iters) || it + 1 >= setup_iters + halo_iters) break;
+  }
+  const int p = (r[0] + 2) + (r[1] + 2) * P0 + (r[2] + 2) * P01;
+  ra = make_uint4((unsigned)p, u, (unsigned)(rs[0] + 2) | ((unsigned)(rs[1] + 2) << 16),
+                  (unsigned)(rs[2] + 2) | ((unsigned)(rt[2] + 2) << 16));
   rb = make_float4(tx, ty, tz, __uint_as_float((unsigned)(rt[0] + 2) | ((unsigned)(rt[1] + 2) << 16)));
   rc = make_float4(__uint_as_float(__float_as_uint(t_delta[0]) & 0x7fffffffu | (step[0] < 0 ? 0x80000000u : 0u)),
                    __uint_as_float(__float_as_uint(t_delta[1]) & 0x7fffffffu | (step[1] < 0 ? 0x80000000u : 0u)),
@@ -1182,7 +1202,7 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
           const uint32_t uu = e < e1 ? vox_list[e] : 0xffffffffu;
           uint4 ra = make_uint4(0, 0, 0, 0);
           float4 rb = make_float4(0, 0, 0, 0), rc = make_float4(0, 0, 0, 0);
-          const int kind = setup_ray<SMEM>(m, g, gm, origin, uu, ra, rb, rc, steps_lo, fails);
+          const int kind = setup_ray<SMEM>(m, g, gm, origin, uu, ra, rb, rc, steps_lo, fails, A.setup_iters, A.halo_iters);
           const unsigned cb = __ballot_sync(0xffffffffu, kind == 1);
           if (cb) {
             unsigned base = 0;
