@@ -264,7 +264,7 @@ def astar_search(space, start, scorer, coverage_target, coverage_tolerance, max_
     root.id, root.ss, root.pose, root.parent, root.depth, root.distance = 0, best, R[best], None, 0, 0.0
     cov, st = scorer.score(None, SEN[best][None])
     root.coverage, root.state = cov[0], st[0]
-    root.f = root.coverage  # heuristic.cpp:1227-1240
+    root.f = 0.0  # root: coverage from its own views (heuristic.cpp:1227-1240), f zeroed (:1243-1247)
     open_list, closed = [root], []
     global_id, expanded = 0, 0
     while open_list:

@@ -85,7 +85,7 @@ class ViewpointBatcher {
 };
 
 // heuristic types of cscpp/include/cscpp/coverage_path_planning_heuristic.h:72 that live on the hot path
-enum { SurfaceCoverageH = 0, SurfaceCoveragewithOrientationH = 1, SurfaceCoveragewithAccuracyH = 2 };
+enum { SurfaceCoverageH = 0, SurfaceCoveragewithOrientationH = 1, SurfaceCoveragewithAccuracyH = 2, VolumetricCoverageH = 4 };
 
 class CoverageHeuristicB200 {
  public:
@@ -110,11 +110,12 @@ class CoverageHeuristicB200 {
     // children of an expansion that went through batcher().prefetch() are scored from the cached group gains:
     // no launch here, and the child's covered set is only made if the node is expanded later (ensureSet)
     unsigned long long cachedGain = 0;
-    const bool cached = node->parent && type_ != SurfaceCoveragewithAccuracyH && node->covered_set < 0 &&
+    const bool cached = node->parent && type_ != SurfaceCoveragewithAccuracyH && type_ != VolumetricCoverageH &&
+                        node->covered_set < 0 &&
                         node->parent->covered_set >= 0 && batcher_.groupGain(node, node->parent->covered_set, &cachedGain);
     if (!cached) ensureSet(node);
     double a = 1.0;
-    if (type_ == SurfaceCoveragewithAccuracyH && node->parent) {
+    if ((type_ == SurfaceCoveragewithAccuracyH || type_ == VolumetricCoverageH) && node->parent) {
       // a = (maxAccuracyError - calcAvgAccuracy(visibleCloud)) / maxAccuracyError (:493-494, :836-838); the
       // one-argument overload averages 0.0000285 z^2 over the concatenated sensor clouds
       std::vector<double> p(7 * node->senPoses.size());
@@ -139,6 +140,33 @@ class CoverageHeuristicB200 {
       oc_->check(asscpp_coverage_percent(c, node->covered_set, &pct));  // :482
     }
     node->coverage = pct;
+    if (type_ == VolumetricCoverageH) {
+      // :581-641 (moved), :911-971 (same position), root :1111-1126.  node->voxels = VoxelGrid(volumetricVoxelRes) of
+      // the parent's voxels + the visible cloud: in covered-set form the voxel bits of the set, on the context's
+      // coverage lattice (cov_leaf = volumetricVoxelRes = 0.5).  Counts and percentages are doubles here.
+      AsscppModelInfo info;
+      asscpp_model_info(c, &info);
+      int64_t npts = 0, nvox = 0, pvox = 0;
+      oc_->check(asscpp_covered_popcount(c, node->covered_set, &npts, &nvox));
+      node->coverage = ((double)nvox / (double)info.n_cov_voxels) * 100;  // :629
+      if (node->parent) {
+        oc_->check(asscpp_covered_popcount(c, node->parent->covered_set, &npts, &pvox));
+        const double dx = node->pose.position.x - node->parent->pose.position.x,
+                     dy = node->pose.position.y - node->parent->pose.position.y,
+                     dz = node->pose.position.z - node->parent->pose.position.z;
+        const double d = std::sqrt(dx * dx + dy * dy + dz * dz);
+        node->distance = node->parent->distance + d;
+        node->h_value = 0; node->g_value = 0;
+        const double extraVoxelsNum = (double)nvox - (double)pvox;             // :615
+        const double normAngle = 1 - shortestAngle(node->parent->pose, node->pose) / (2 * M_PI);  // :584-588
+        const double normDist = (2.5 - d) / 2.5;                               // :631, 2.5 = max connection radius
+        node->f_value = d != 0.0 ? node->parent->f_value + ((accW * a) + (distW * normDist) + (angleW * normAngle)) * extraVoxelsNum  // :640
+                                 : node->parent->f_value + ((accW * a) + (angleW * normAngle)) * extraVoxelsNum;                       // :970
+      } else {
+        node->distance = 0; node->h_value = 0; node->g_value = 0; node->f_value = 0;  // :1243-1247
+      }
+      return;
+    }
     if (node->parent) {
       double dx = node->pose.position.x - node->parent->pose.position.x,
              dy = node->pose.position.y - node->parent->pose.position.y,
@@ -149,17 +177,8 @@ class CoverageHeuristicB200 {
       node->h_value = 0; node->g_value = 0;
       double normAngle = 1.0;
       if (d == 0.0 && type_ != SurfaceCoverageH) {
-        // <tf Quaternion::angleShortestPath> between parent and node orientation (:785-790, :813-817)
-        const geometry_msgs::Pose &pp = node->parent->pose, &pn = node->pose;
-        const double l2p = pp.orientation.x * pp.orientation.x + pp.orientation.y * pp.orientation.y +
-                           pp.orientation.z * pp.orientation.z + pp.orientation.w * pp.orientation.w;
-        const double l2n = pn.orientation.x * pn.orientation.x + pn.orientation.y * pn.orientation.y +
-                           pn.orientation.z * pn.orientation.z + pn.orientation.w * pn.orientation.w;
-        const double sq = std::sqrt(l2n * l2p);
-        const double dt = pp.orientation.x * pn.orientation.x + pp.orientation.y * pn.orientation.y +
-                          pp.orientation.z * pn.orientation.z + pp.orientation.w * pn.orientation.w;
-        const double angle = dt < 0 ? std::acos(-dt / sq) * 2.0 : std::acos(dt / sq) * 2.0;
-        normAngle = 1 - angle / (2 * M_PI);
+        // turning angle between parent and node orientation (:785-790, :813-817)
+        normAngle = 1 - shortestAngle(node->parent->pose, node->pose) / (2 * M_PI);
       }
       if (type_ == SurfaceCoveragewithAccuracyH)
         node->f_value = d != 0.0 ? node->parent->f_value + ((1 / d) * cgain * a)   // :512
@@ -172,9 +191,22 @@ class CoverageHeuristicB200 {
                                  : node->parent->f_value + cgain;            // :780
     } else {
       node->distance = 0; node->h_value = 0; node->g_value = 0;
-      node->f_value = node->coverage;  // root: :1232-1238
+      node->f_value = 0;  // root: coverage from its own views (:1227-1240), f and g zeroed (:1243-1247)
     }
   }
+
+  // <tf Quaternion::angleShortestPath>
+  static double shortestAngle(const geometry_msgs::Pose& pp, const geometry_msgs::Pose& pn) {
+    const double l2p = pp.orientation.x * pp.orientation.x + pp.orientation.y * pp.orientation.y +
+                       pp.orientation.z * pp.orientation.z + pp.orientation.w * pp.orientation.w;
+    const double l2n = pn.orientation.x * pn.orientation.x + pn.orientation.y * pn.orientation.y +
+                       pn.orientation.z * pn.orientation.z + pn.orientation.w * pn.orientation.w;
+    const double sq = std::sqrt(l2n * l2p);
+    const double dt = pp.orientation.x * pn.orientation.x + pp.orientation.y * pn.orientation.y +
+                      pp.orientation.z * pn.orientation.z + pp.orientation.w * pn.orientation.w;
+    return dt < 0 ? std::acos(-dt / sq) * 2.0 : std::acos(dt / sq) * 2.0;
+  }
+  double accW = 0.8, distW = 0.5, angleW = 0.2;  // heuristic.cpp:50-53
 
   // Node::cloud_filtered in covered-set form: the parent's set OR the node's own sensor views (:439-445, :473-480).
   // calculateHeuristic calls it for nodes that were not prefetched; a prefetched node gets its set here when it is

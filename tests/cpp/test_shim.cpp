@@ -126,6 +126,20 @@ int main(int argc, char** argv) {
       std::printf("acc_child %zu coverage %.17g f %.17g\n", i, kid.coverage, kid.f_value);
     }
   }
+  // 7. VolumetricCoverageH: one expansion from waypoint 0 (heuristic.cpp:581-641)
+  {
+    SSPP::CoverageHeuristicB200 hv(&oc, 100.0, 1.0, SSPP::VolumetricCoverageH);
+    hv.setMaxMinSensorAccuracy(std::vector<geometry_msgs::PoseArray>(1, pa));
+    SSPP::NodeB200 r0 = nodes[0];
+    hv.calculateHeuristic(&r0);
+    std::printf("vol_root coverage %.17g f %.17g\n", r0.coverage, r0.f_value);
+    for (size_t i = 1; i < nodes.size(); ++i) {
+      SSPP::NodeB200 kid = nodes[i];
+      kid.parent = &r0;
+      hv.calculateHeuristic(&kid);
+      std::printf("vol_child %zu coverage %.17g f %.17g\n", i, kid.coverage, kid.f_value);
+    }
+  }
   // 6. mesh sample filters (heuristic.cpp:300-335): <mesh.txt> = "v x y z" / "f a b c" lines (0-based)
   if (argc > 3) {
     std::vector<float> vtx;

@@ -71,7 +71,7 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
         return float(np.float32(np.float32(np.float32(len(s)) / np.float32(o.n_cov)) * np.float32(100)))
 
     covered = set(vox[0].tolist())
-    cov, fval, cur = pct(covered), pct(covered), 0
+    cov, fval, cur = pct(covered), 0.0, 0  # root f = 0 (heuristic.cpp:1243-1247)
     m = re.search(r"root coverage (\S+) f (\S+)", out)
     assert float(m.group(1)) == pytest.approx(cov, abs=0) and float(m.group(2)) == pytest.approx(fval, abs=0)
     steps = re.findall(r"step (\d+) best (\d+) coverage (\S+) f (\S+)", out)
@@ -132,7 +132,7 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
     max_err = 0.0000285 * dmax * dmax
     m = re.search(r"acc_root coverage (\S+) f (\S+) maxDepth (\S+)", out)
     cov0 = pct(set(vox[0].tolist()))
-    assert float(m.group(1)) == cov0 and float(m.group(2)) == cov0
+    assert float(m.group(1)) == cov0 and float(m.group(2)) == 0.0
     assert float(m.group(3)) == pytest.approx(np.sqrt(max_err / 0.0000285), rel=1e-15)
     kids = re.findall(r"acc_child (\d+) coverage (\S+) f (\S+)", out)
     assert len(kids) == len(rows) - 1
@@ -148,7 +148,31 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
         z = xyz[both, 2].astype(np.float64)
         avg = float(np.sum(0.0000285 * z * z)) / len(both)
         a = (max_err - avg) / max_err
-        assert float(f_s) == pytest.approx(cov0 + (1 / d) * (cov_i - cov0) * a, rel=1e-12, abs=1e-12)
+        assert float(f_s) == pytest.approx((1 / d) * (cov_i - cov0) * a, rel=1e-12, abs=1e-12)
+    # 7. VolumetricCoverageH (heuristic.cpp:581-641): f = parent.f + (accW a + distW normDist + angleW normAngle) * extra voxels
+    m = re.search(r"vol_root coverage (\S+) f (\S+)", out)
+    assert float(m.group(1)) == len(vox[0]) / o.n_cov * 100 and float(m.group(2)) == 0.0
+    vkids = re.findall(r"vol_child (\d+) coverage (\S+) f (\S+)", out)
+    assert len(vkids) == len(rows) - 1
+    for i, c_s, f_s in vkids:
+        i = int(i)
+        both = np.concatenate([o.eval_view(poses[2 * i])["visible"], o.eval_view(poses[2 * i + 1])["visible"]])
+        union = set(vox[0].tolist()) | set(vox[i].tolist())
+        assert float(c_s) == len(union) / o.n_cov * 100
+        extra = float(len(union) - len(vox[0]))
+        d = float(np.linalg.norm(pos[i] - pos[0]))
+        if len(both) == 0:
+            assert np.isnan(float(f_s))
+            continue
+        z = xyz[both, 2].astype(np.float64)
+        a = (max_err - float(np.sum(0.0000285 * z * z)) / len(both)) / max_err
+        qa, qb = poses[0][3:], poses[2 * i][3:]
+        dt = float(qa @ qb)
+        ang = 2 * np.arccos(abs(dt) / np.sqrt(float(qa @ qa) * float(qb @ qb)))
+        norm_angle = 1 - ang / (2 * np.pi)
+        want = ((0.8 * a) + (0.5 * (2.5 - d) / 2.5) + (0.2 * norm_angle)) * extra if d != 0 else \
+            ((0.8 * a) + (0.2 * norm_angle)) * extra
+        assert float(f_s) == pytest.approx(want, rel=1e-11, abs=1e-11)
     # 6. mesh sample filters (heuristic.cpp:300-335)
     om = O.Mesh(g["vertices"], g["triangles"])
     nxt = np.concatenate([poses[2:], poses[:2]])
