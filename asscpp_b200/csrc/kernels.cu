@@ -691,16 +691,28 @@ __device__ __forceinline__ bool build_grid(const EvalArgs& A, ViewShared& sh, ui
   if (sh.words == 0) return use_smem;
   const GridView& g = sh.g;
   const int P0 = g.P0, P1 = g.P1, P2 = g.P2, P01 = g.P01;
-  // interior: occupancy of the survivors' voxels
+  // interior: occupancy of the survivors' voxels (four independent voxel-table loads in flight per thread: the
+  // gather from L2 / HBM is what this loop waits for)
   unsigned uniq = 0;
-  for (unsigned e = threadIdx.x; e < sh.list_count; e += blockDim.x) {
-    uint32_t u = vox_list[e] & kVoxMask;
-    int4 vx = m.vox[u];
-    int p = (vx.x - g.min_b[0] + 2) + (vx.y - g.min_b[1] + 2) * P0 + (vx.z - g.min_b[2] + 2) * P01;
-    uint32_t bit = 1u << (p & 31);
-    uint32_t old = atomicOr(&grid[p >> 5], bit);
-    if (old & bit) vox_list[e] = 0xffffffffu;  // same voxel emitted by another 32-point load
-    else ++uniq;
+  const unsigned nlist = sh.list_count;
+  for (unsigned e0 = threadIdx.x; e0 < nlist; e0 += 4 * blockDim.x) {
+    int4 vx[4];
+    bool on[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const unsigned e = e0 + k * blockDim.x;
+      on[k] = e < nlist;
+      vx[k] = on[k] ? m.vox[vox_list[e] & kVoxMask] : make_int4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (!on[k]) continue;
+      int p = (vx[k].x - g.min_b[0] + 2) + (vx[k].y - g.min_b[1] + 2) * P0 + (vx[k].z - g.min_b[2] + 2) * P01;
+      uint32_t bit = 1u << (p & 31);
+      uint32_t old = atomicOr(&grid[p >> 5], bit);
+      if (old & bit) vox_list[e0 + k * blockDim.x] = 0xffffffffu;  // same voxel emitted by another 32-point load
+      else ++uniq;
+    }
   }
   // halo + sentinel layers: every cell with a padded coordinate in {0, 1, P-2, P-1}
   auto orw = [&](unsigned w, uint32_t mask) { atomicOr(&grid[w], mask); };
