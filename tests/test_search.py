@@ -193,4 +193,14 @@ def test_eval_groups_union_gain(oracle_mod, etihad, space_2p5, model):
         if group == 1:
             assert np.array_equal(res["gain_vox"], plain["gain_vox"])
     assert got.sum() > 0
+    # ragged tail (the last group is short), a group larger than the batch, empty batch, bad group size
+    r7 = ctx.eval_groups(poses[:7], 3, covered=covered)
+    assert np.array_equal(r7["gain_vox"][:6], ctx.eval_groups(poses[:6], 3, covered=covered)["gain_vox"])
+    assert r7["gain_vox"][6] == ctx.eval_batch(poses[6:7], covered=covered)["gain_vox"][0]
+    big = ctx.eval_groups(poses[:5], 64, covered=covered)
+    u = np.unique(np.concatenate([np.unique(ids[o.eval_view(p)["visible"]]) for p in poses[:5]]))
+    assert int(big["gain_vox"].sum()) == int((~in_cov[u]).sum())
+    assert len(ctx.eval_groups(poses[:0], 2)) == 0
+    with pytest.raises(A.AsscppError):
+        ctx.eval_groups(poses[:4], 0)
     ctx.close()
