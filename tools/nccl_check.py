@@ -52,6 +52,31 @@ def main():
         ok = False
         print("rank %d: OR-allreduce mismatch" % rank)
     npts, nvox = s.popcount()
+    # config 4: the adaptive loop with the candidates sharded over the ranks and one covered-bitset OR-allreduce
+    # per iteration, against the same loop run on this rank's GPU alone
+    mg = np.load(os.path.join(g, "etihad_mesh.npz"))
+    mesh = A.Mesh(mg["vertices"], mg["triangles"], device=local)
+    model = AD.VoxelModel(xyz, 0.5)
+
+    def gather_counts(n):
+        t = torch.tensor([n], device="cuda", dtype=torch.int64)
+        dist.all_reduce(t)
+        return int(t.item())
+
+    solo = AD.adaptive_loop(AD.GpuBackend(ctx, comm=False, mesh=mesh), model, (0, 0, 4.5), (36, 50, 9))
+    shard = AD.adaptive_loop(AD.GpuBackend(ctx, comm=True, mesh=mesh), model, (0, 0, 4.5), (36, 50, 9), world=world,
+                             rank=rank, gather_counts=gather_counts)
+    if len(solo) != len(shard):
+        ok = False
+        print("rank %d: adaptive loop length %d vs %d" % (rank, len(shard), len(solo)))
+    for a, b in zip(shard, solo):
+        if not (np.array_equal(a["bits"], b["bits"]) and a["accepted"] == b["accepted"]
+                and a["candidates"] == b["candidates"] and a["clusters"] == b["clusters"]):
+            ok = False
+            print("rank %d: adaptive loop iteration %d differs" % (rank, a["iter"]))
+    if rank == 0:
+        print("adaptive loop world=%d: %d iterations, uncovered %s" % (
+            world, len(shard), " ".join("%.3f%%" % t["uncovered_pct"] for t in shard)))
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
