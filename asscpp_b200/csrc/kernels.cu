@@ -878,8 +878,8 @@ __device__ __forceinline__ void trace_rays(const EvalArgs& A, ViewShared& sh, co
 // P4a, fast path: the same rays as trace_rays, reorganised so that lanes stay busy.
 //
 //   setup_ray    one thread per occupied voxel, fully converged (a warp prepares kRayBatch list entries at a time): direction, slab test, start cell, t_max /
-//                t_delta (:99-128, :410-519) and the FIRST loop iteration (:538-579) on the start cell, whose
-//                coordinates are still at hand (it is the cell that most often lies in the halo layer).
+//                t_delta (:99-128, :410-519) and the first loop iterations (:538-579): the start cell, whose
+//                coordinates are still at hand, and up to three more while the ray is in the halo layer.
 //                Rays that are already decided leave here (failed / free / occluded); the others are written
 //                as 48-byte records to the warp's private queue (7.5 KB per warp, L2-resident).
 //   walk         lanes pull records from the queue; a lane that finishes its ray takes the next record instead
@@ -892,7 +892,7 @@ __device__ __forceinline__ void trace_rays(const EvalArgs& A, ViewShared& sh, co
 //                and resolved for all parked lanes together.  DDA step counts come from the Manhattan
 //                distance between start and end cell (every iteration moves one cell along one axis).
 //
-// Record: a = {p, u, qs0 | qs1 << 16, qs2 | qt2 << 16}   p = padded linear index after the first step,
+// Record: a = {p, u, qs0 | qs1 << 16, qs2 | qt2 << 16}   p = padded linear index the walk starts on,
 //         b = {t_max x y z, qt0 | qt1 << 16}              qs / qt = padded start / target coordinates,
 //         c = {t_delta x y z with the step sign in the (otherwise unused) sign bit, 0}
 // ------------------------------------------------------------------------------------------------
