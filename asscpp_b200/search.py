@@ -91,26 +91,36 @@ class SearchSpace:
         """children[i] for every node; `segments_free(a[m, 3], b[m, 3]) -> bool[m]` is the collision test between
         different positions (None: no mesh, every segment is free).  One batched call per block of nodes."""
         R = self.robots
-        pos = R[:, :3]
+        pos = np.ascontiguousarray(R[:, :3])
         n = len(R)
         self.children = [None] * n
         total = 0
+        # candidate pairs from a k-d tree (a superset: slightly larger radius), then the reference's own test
+        # Dist(S, temp) <= radius in double on every candidate
+        from scipy.spatial import cKDTree
+        tree = cKDTree(pos)
         for lo in range(0, n, block):
             hi = min(lo + block, n)
-            d = pos[lo:hi, None, :] - pos[None, :, :]
-            dd = np.sqrt(d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1] + d[..., 2] * d[..., 2])  # Dist()
-            near = dd <= radius
-            near[np.arange(hi - lo), np.arange(lo, hi)] = False  # S != temp
+            cand = tree.query_ball_point(pos[lo:hi], radius * (1.0 + 1e-9) + 1e-9)
+            ti = np.repeat(np.arange(hi - lo), [len(c) for c in cand])
+            si = np.fromiter((j for c in cand for j in c), np.int64, count=len(ti))
+            d = pos[lo + ti] - pos[si]
+            dd = np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2])  # Dist()
+            sel = (dd <= radius) & (si != lo + ti)  # S != temp
+            ti, si, d = ti[sel], si[sel], d[sel]
             same = (d == 0).all(-1)
-            ti, si = np.nonzero(near & ~same)
-            ok = np.ones(len(ti), bool)
-            if segments_free is not None and len(ti):
-                ok = np.asarray(segments_free(pos[lo + ti], pos[si]), bool)
-            keep = near & same
-            keep[ti[ok], si[ok]] = True
+            ok = same.copy()  # same position, other orientation: always connected (:553-561)
+            if segments_free is not None and (~same).any():
+                ok[~same] = np.asarray(segments_free(pos[lo + ti[~same]], pos[si[~same]]), bool)
+            else:
+                ok[:] = True
+            ti, si = ti[ok], si[ok]
+            order = np.lexsort((si, ti))  # children of a node in ascending S = list order
+            ti, si = ti[order], si[order]
+            cuts = np.searchsorted(ti, np.arange(hi - lo + 1))
             for t in range(hi - lo):
-                self.children[lo + t] = np.nonzero(keep[t])[0]  # ascending S = list order
-                total += len(self.children[lo + t])
+                self.children[lo + t] = si[cuts[t]:cuts[t + 1]]
+            total += len(si)
         self.n_connections = total  # MAXNODES (:568)
         return total
 
@@ -241,8 +251,11 @@ def _llist_add(lst, node):
 
 
 def _llist_find(lst, node):
+    """LList::find: first element with an equal pose (Node::operator==, node.cpp:75-78).  Every node carries the
+    pose of a search-space waypoint and those are unique (insertNode drops duplicates), so equal pose <=> same
+    waypoint index."""
     for k, p in enumerate(lst):
-        if _pose_equal(p.pose, node.pose):
+        if p.ss == node.ss:
             return k
     return -1
 
@@ -253,13 +266,10 @@ def astar_search(space, start, scorer, coverage_target, coverage_tolerance, max_
     R, SEN = space.robots, space.sensors
     start = np.asarray(start, np.float64)
     # findRoot (:74-133): nearest node, first one wins ties
-    best, best_d = -1, np.finfo(np.float64).max
-    for i in range(space.n):
-        d = dist(R[i], start)
-        if d < best_d:
-            best, best_d = i, d
-    if best < 0:
+    if space.n == 0:
         return None
+    dx, dy, dz = R[:, 0] - start[0], R[:, 1] - start[1], R[:, 2] - start[2]
+    best = int(np.argmin(np.sqrt(dx * dx + dy * dy + dz * dz)))  # first minimum = strict `<` in list order
     root = _Node()
     root.id, root.ss, root.pose, root.parent, root.depth, root.distance = 0, best, R[best], None, 0, 0.0
     cov, st = scorer.score(None, SEN[best][None])
@@ -281,12 +291,8 @@ def astar_search(space, start, scorer, coverage_target, coverage_tolerance, max_
             return {"path": [p.ss for p in path], "coverage": [p.coverage for p in path], "f": [p.f for p in path],
                     "distance": current.distance, "expanded": expanded, "created": global_id}
         # makeChildrenNodes (:375-458): locate the node by pose, children linked in reverse
-        ss = -1
-        for i in range(space.n):
-            if _pose_equal(R[i], current.pose):
-                ss = i
-                break
-        kids = [] if ss < 0 else list(space.children[ss])
+        # (the reference scans the list for the first node with this pose: poses are unique, so it is the node itself)
+        kids = list(space.children[current.ss])
         nodes = []
         for c in kids:
             nd = _Node()
