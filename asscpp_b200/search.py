@@ -97,13 +97,19 @@ class SearchSpace:
         total = 0
         # candidate pairs from a k-d tree (a superset: slightly larger radius), then the reference's own test
         # Dist(S, temp) <= radius in double on every candidate
-        from scipy.spatial import cKDTree
-        tree = cKDTree(pos)
+        try:
+            from scipy.spatial import cKDTree
+            tree = cKDTree(pos)
+        except ImportError:  # all pairs of the block instead
+            tree = None
         for lo in range(0, n, block):
             hi = min(lo + block, n)
-            cand = tree.query_ball_point(pos[lo:hi], radius * (1.0 + 1e-9) + 1e-9)
-            ti = np.repeat(np.arange(hi - lo), [len(c) for c in cand])
-            si = np.fromiter((j for c in cand for j in c), np.int64, count=len(ti))
+            if tree is not None:
+                cand = tree.query_ball_point(pos[lo:hi], radius * (1.0 + 1e-9) + 1e-9)
+                ti = np.repeat(np.arange(hi - lo), [len(c) for c in cand])
+                si = np.fromiter((j for c in cand for j in c), np.int64, count=len(ti))
+            else:
+                ti, si = (a.ravel() for a in np.meshgrid(np.arange(hi - lo), np.arange(n), indexing="ij"))
             d = pos[lo + ti] - pos[si]
             dd = np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2])  # Dist()
             sel = (dd <= radius) & (si != lo + ti)  # S != temp
