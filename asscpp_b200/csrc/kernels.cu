@@ -1133,7 +1133,8 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
           if (q0 == 0 || q0 == P0 - 1 || q1 == 0 || q1 == g.P1 - 1 || q2 == 0 || q2 == g.P2 - 1) {
             steps_lo += walked;                                            // left the expanded box (:538-540): result 0
             freed = 1;
-          } else if (cell_occupied<SMEM>(g, gm, q0 - 2, q1 - 2, q2 - 2) &&
+          } else if (((q0 > 1 && q0 < P0 - 2 && q1 > 1 && q1 < g.P1 - 2 && q2 > 1 && q2 < g.P2 - 2) ||  // interior: the set bit IS the occupancy
+                      cell_occupied<SMEM>(g, gm, q0 - 2, q1 - 2, q2 - 2)) &&                              // halo: aliased lookup (Q3)
                      is_occluder(g, q0 - 2, q1 - 2, q2 - 2, qt0 - 2, qt1 - 2, qt2 - 2)) {
             steps_lo += walked + 1;                                        // :561-562 result 1
           } else {
