@@ -1000,6 +1000,7 @@ __device__ __forceinline__ int setup_ray(const ModelDev& m, const GridView& g, c
                           (unsigned)r[2] < (unsigned)g.div[2];
     if ((interior && it + 1 >= setup_iters) || it + 1 >= setup_iters + halo_iters) break;
   }
+  if (tx != tx) ty = tx;  // tx NaN: the reference steps z from here on; see dda_burst for why ty says so too
   const int p = (r[0] + 2) + (r[1] + 2) * P0 + (r[2] + 2) * P01;
   ra = make_uint4((unsigned)p, u, (unsigned)(rs[0] + 2) | ((unsigned)(rs[1] + 2) << 16),
                   (unsigned)(rs[2] + 2) | ((unsigned)(rt[2] + 2) << 16));
@@ -1013,21 +1014,32 @@ __device__ __forceinline__ int setup_ray(const ModelDev& m, const GridView& g, c
 
 // The burst loop in PTX: two DDA iterations per lane, then a warp vote; leaves when fewer than `thresh`
 // lanes are still walking.  A lane stops walking at the first set bit (pbit then addresses that cell).
-// Branch-free per iteration: bit test, the x -> y -> z `<=` cascade of :565-579 as predicates (sy and sz
-// use pw ^ px = pw & !px, valid because px implies pw), predicated FADD (add.rn: never fused) and index
-// updates.  pbit = padded linear index (+ 8 * shared byte address of the grid in the SMEM variant, which
-// is a multiple of 32 bits, so pbit & 31 is still the bit number).
+// Branch-free per iteration: bit test, the x -> y -> z `<=` cascade of :565-579 as predicates, predicated FADD
+// (add.rn: never fused) and index updates.  pbit = padded linear index (+ 8 * shared byte address of the grid in
+// the SMEM variant, so pbit >> 3 is the address of the cell's byte and pbit & 7 its bit).
+//
+// The loop is bound by the ALU pipe (integer / logic / compare: half the rate of the FMA pipe), so it is kept to
+// eight ALU instructions per iteration:
+//   * the cell's BYTE is loaded (no word-address mask) and replicated into the four bytes of a register by an
+//     integer multiply (FMA pipe), so that the funnel shift by pbit (mod 32) finds bit pbit & 7;
+//   * `walking` is not carried from one iteration to the next: a lane that is not walking rests on a set bit (a
+//     parked ray on the bit that stopped it, a lane without a ray on that bit or on padded cell 0, which is in the
+//     sentinel layer), so the bit test alone says whether the lane walks -- every caller keeps that invariant;
+//   * sy = !sx & (ty <= tz) & (ty <= tx) is evaluated without its last term.  With sx false and ty <= tz, either
+//     tx > ty (the term holds) or tx <= ty and tx > tz, which contradicts ty <= tz -- unless tx is NaN, where the
+//     reference takes z for ever; rays are handed to the walk with ty = NaN in that case (setup_ray), which
+//     forces the same choice, and tx cannot become NaN later (it only grows by a t_delta that is NaN itself or
+//     leaves -inf + inf to the very first step, which setup_ray takes).
 #define ASSCPP_DDA_ITER(LOAD)                          \
-  " shr.u32 a, %0, 3;\n"                               \
-  " and.b32 a, a, 0xfffffffc;\n" LOAD                  \
+  " shr.u32 a, %0, 3;\n" LOAD                          \
+  " mul.lo.u32 word, word, 0x01010101;\n"              \
   " shf.r.wrap.b32 b, word, word, %0;\n"               \
   " and.b32 b, b, 1;\n"                                \
-  " setp.eq.and.u32 pw, b, 0, pw;\n"                   \
+  " setp.eq.u32 pw, b, 0;\n"                           \
   " setp.le.and.f32 q1, %1, %2, pw;\n"                 \
   " setp.le.and.f32 px, %1, %3, q1;\n"                 \
   " xor.pred pn, pw, px;\n"                            \
-  " setp.le.and.f32 q2, %2, %3, pn;\n"                 \
-  " setp.le.and.f32 py, %2, %1, q2;\n"                 \
+  " setp.le.and.f32 py, %2, %3, pn;\n"                 \
   " xor.pred pz, pn, py;\n"                            \
   " @px add.rn.f32 %1, %1, %5;\n"                      \
   " @py add.rn.f32 %2, %2, %6;\n"                      \
@@ -1043,12 +1055,11 @@ __device__ __forceinline__ void dda_burst(unsigned& pbit, float& tx, float& ty, 
   if constexpr (SMEM) {
     asm volatile(
         "{\n"
-        " .reg .pred pw, px, py, pz, pn, q1, q2, pc;\n"
+        " .reg .pred pw, px, py, pz, pn, q1, pc;\n"
         " .reg .u32 a, word, b, bal, cnt;\n"
-        " setp.ne.u32 pw, %4, 0;\n"
         "LB_%=:\n"
-        ASSCPP_DDA_ITER(" ld.shared.u32 word, [a];\n")
-        ASSCPP_DDA_ITER(" ld.shared.u32 word, [a];\n")
+        ASSCPP_DDA_ITER(" ld.shared.u8 word, [a];\n")
+        ASSCPP_DDA_ITER(" ld.shared.u8 word, [a];\n")
         " vote.sync.ballot.b32 bal, pw, 0xffffffff;\n"
         " popc.b32 cnt, bal;\n"
         " setp.ge.u32 pc, cnt, %11;\n"
@@ -1061,13 +1072,12 @@ __device__ __forceinline__ void dda_burst(unsigned& pbit, float& tx, float& ty, 
   } else {
     asm volatile(
         "{\n"
-        " .reg .pred pw, px, py, pz, pn, q1, q2, pc;\n"
+        " .reg .pred pw, px, py, pz, pn, q1, pc;\n"
         " .reg .u32 a, word, b, bal, cnt;\n"
         " .reg .u64 ga;\n"
-        " setp.ne.u32 pw, %4, 0;\n"
         "LB_%=:\n"
-        ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u32 word, [ga];\n")
-        ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u32 word, [ga];\n")
+        ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u8 word, [ga];\n")
+        ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u8 word, [ga];\n")
         " vote.sync.ballot.b32 bal, pw, 0xffffffff;\n"
         " popc.b32 cnt, bal;\n"
         " setp.ge.u32 pc, cnt, %11;\n"
