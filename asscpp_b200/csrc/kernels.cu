@@ -522,13 +522,17 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           if (!cin[b]) {
             const float cx = ((float)vx[b].x + 0.5f) * m.leaf, cy = ((float)vx[b].y + 0.5f) * m.leaf,
                         cz = ((float)vx[b].z + 0.5f) * m.leaf;
+            // conservative classifier (bounds in sh.vox_hi), not reference arithmetic: FMA allowed; the verdict is
+            // accumulated in two predicates (compare instructions run on the ALU pipe, the busiest one)
+            bool out = false, cut = false;
 #pragma unroll
             for (int k = 0; k < 6; ++k) {
-              const float v = sh.planes[4 * k] * cx + sh.planes[4 * k + 1] * cy + sh.planes[4 * k + 2] * cz +
-                              sh.planes[4 * k + 3];
-              if (v > sh.vox_hi[k]) cls = 0;
-              else if (!(v < -sh.vox_hi[k]) && cls == 2) cls = 1;
+              const float v = __fmaf_rn(sh.planes[4 * k], cx, __fmaf_rn(sh.planes[4 * k + 1], cy,
+                              __fmaf_rn(sh.planes[4 * k + 2], cz, sh.planes[4 * k + 3])));
+              out |= v > sh.vox_hi[k];
+              cut |= !(v < -sh.vox_hi[k]);
             }
+            cls = out ? 0 : (cut ? 1 : 2);
           }
           if (cls == 2) {
             const uint32_t q0 = (uint32_t)vx[b].w;
@@ -1012,7 +1016,7 @@ __device__ __forceinline__ int setup_ray(const ModelDev& m, const GridView& g, c
   return 2;
 }
 
-// The burst loop in PTX: two DDA iterations per lane, then a warp vote; leaves when fewer than `thresh`
+// The burst loop in PTX: three DDA iterations per lane, then a warp vote; leaves when fewer than `thresh`
 // lanes are still walking.  A lane stops walking at the first set bit (pbit then addresses that cell).
 // Branch-free per iteration: bit test, the x -> y -> z `<=` cascade of :565-579 as predicates, predicated FADD
 // (add.rn: never fused) and index updates.  pbit = padded linear index (+ 8 * shared byte address of the grid in
@@ -1060,6 +1064,7 @@ __device__ __forceinline__ void dda_burst(unsigned& pbit, float& tx, float& ty, 
         "LB_%=:\n"
         ASSCPP_DDA_ITER(" ld.shared.u8 word, [a];\n")
         ASSCPP_DDA_ITER(" ld.shared.u8 word, [a];\n")
+        ASSCPP_DDA_ITER(" ld.shared.u8 word, [a];\n")
         " vote.sync.ballot.b32 bal, pw, 0xffffffff;\n"
         " popc.b32 cnt, bal;\n"
         " setp.ge.u32 pc, cnt, %11;\n"
@@ -1076,6 +1081,7 @@ __device__ __forceinline__ void dda_burst(unsigned& pbit, float& tx, float& ty, 
         " .reg .u32 a, word, b, bal, cnt;\n"
         " .reg .u64 ga;\n"
         "LB_%=:\n"
+        ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u8 word, [ga];\n")
         ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u8 word, [ga];\n")
         ASSCPP_DDA_ITER(" cvt.u64.u32 ga, a;\n add.u64 ga, ga, %12;\n ld.global.u8 word, [ga];\n")
         " vote.sync.ballot.b32 bal, pw, 0xffffffff;\n"

@@ -129,6 +129,40 @@ def test_epsilon_classes_reported(A, oracle_mod, etihad_ctx, etihad_oracle, spac
     assert total[0] > 0  # some points do sit within 1e-4 of a plane
 
 
+def test_zero_direction_components(A, oracle_mod):
+    """Quirk Q8: rays with exactly zero direction components (t_delta = inf, t_max = +-inf) and the x -> y -> z
+    `<=` cascade on infinities (voxel_grid_occlusion_estimation.cpp:513-519, 565-579).  A lattice of points at
+    exact cell centres and cameras at exact cell centres / faces, looking along each axis: whole planes of targets
+    share a coordinate with the origin.  The device step loop evaluates the cascade without its last comparison
+    (kernels.cu: dda_burst), which this scene would expose if the stated invariant did not hold."""
+    for leaf, near in ((0.5, 0.7), (0.25, 0.3), (1.0, 0.1)):
+        g = (np.arange(-8, 9, dtype=np.float32) + 0.5) * np.float32(leaf)
+        X, Y, Z = np.meshgrid(g, g, g, indexing="ij")
+        keep = ((np.abs(X) + np.abs(Y) + np.abs(Z)) / leaf).astype(np.int64) % 3 != 0   # holes: free and occluded rays
+        xyz = np.stack([X[keep], Y[keep], Z[keep]], 1).astype(np.float32)
+        pa = A.default_params(leaf=leaf, cov_leaf=leaf, near_dist=near, far_dist=near + 12 * leaf)
+        po = oracle_mod.make_params(leaf=leaf, cov_leaf=leaf, near=near, far=near + 12 * leaf)
+        c = float(np.float32(0.5 * leaf))
+        s = float(np.sqrt(0.5))
+        quats = [(0, 0, 0, 1.0), (0, 0, 1.0, 0), (0, 0, s, s), (0, 0, -s, s), (0, s, 0, s), (0, -s, 0, s)]  # +-x +-y +-z
+        poses = []
+        for q in quats:
+            for o in ((c, c, c), (0.0, c, c), (c, 0.0, c), (c, c, 0.0), (-c, c, -c), (c + 4 * leaf, c, c - 2 * leaf)):
+                poses.append(o + q)
+        poses = np.array(poses, np.float64)
+        ctx = A.CoverageContext(xyz, pa)
+        orc = oracle_mod.Oracle(xyz, po)
+        for flags in (A.EVAL_HASH, A.EVAL_HASH | A.EVAL_FORCE_GLOBAL):
+            res = ctx.eval_batch(poses, flags=flags)
+            st = orc.eval_batch(poses, memo=True)   # step counts with the early exit at the first occluder
+            assert_results_equal(oracle_mod, res, st, "lattice leaf %g flags %d" % (leaf, flags))
+            lit = orc.eval_batch(poses, memo=False)  # the literal per-point loop: same sets and counts
+            for col in (oracle_mod.ST_VISIBLE, oracle_mod.ST_SURVIVORS):
+                assert np.array_equal(lit[:, col], st[:, col])
+        assert res["visible"].sum() > 0 and (res["visible"] < res["survivors"]).any()
+        ctx.close()
+
+
 def test_sticky_state_carry_path(A, oracle_mod):
     """Quirk Q5 (occlusion_culling.cpp:308,332-335): same scene as tests/test_oracle.py; the GPU hands
     such views to ordered_views_kernel, which replays the reference loop in original index order."""
