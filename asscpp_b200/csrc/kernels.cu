@@ -460,11 +460,17 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           u = __ldcg(cut + i);
           const int4 vx = m.vox[u];
           const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
-          for (uint32_t q = q0; q < q1; ++q) {
-            const float4 p = m.pts[q];
-            if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
-            ++cnt;
-            if (want_hash) shash += mix64((uint64_t)(uint32_t)m.orig[q]);
+          // the points of a voxel four at a time: the loads, not the plane tests, are what this loop waits for
+          for (uint32_t qb = q0; qb < q1; qb += 4) {
+            float4 p[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) p[k] = m.pts[min(qb + k, q1 - 1)];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if (qb + k >= q1 || !point_in_frustum(sh.planes, p[k].x, p[k].y, p[k].z)) continue;
+              ++cnt;
+              if (want_hash) shash += mix64((uint64_t)(uint32_t)m.orig[qb + k]);
+            }
           }
           if (cnt) {
             surv_in += cnt;
