@@ -493,26 +493,41 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     j_begin = __shfl_sync(0xffffffffu, j_begin, 0);
     if (j_begin >= total) break;
     const unsigned j_end = min(total, j_begin + kCullClaim);
-    unsigned c = 0;  // descriptor of this lane's current candidate; only ever moves forward within a claim
+    // c0 / d0: the last descriptor starting at or before the current block of 32 candidates (warp-uniform)
+    unsigned c0 = 0;
     {
       unsigned lo = 0, hi = ndesc;  // last descriptor starting at or before j_begin
       while (hi - lo > 1) {
         const unsigned mid = (lo + hi) >> 1;
         if (desc(mid).y <= j_begin) lo = mid; else hi = mid;
       }
-      c = lo;
+      c0 = lo;
     }
+    uint2 d0 = desc(c0);
     for (unsigned jb = j_begin; jb < j_end; jb += 32 * kCullUnroll) {
       uint32_t uu[kCullUnroll], q1[kCullUnroll];
       int4 vx[kCullUnroll];
       bool on[kCullUnroll], cin[kCullUnroll];
 #pragma unroll
       for (int b = 0; b < kCullUnroll; ++b) {
-        const unsigned j = jb + b * 32 + lane;
+        const unsigned j0 = jb + b * 32, j = j0 + lane;
         on[b] = j < j_end; cin[b] = false; uu[b] = 0; q1[b] = 0; vx[b] = make_int4(0, 0, 0, 0);
+        // The chunk of every candidate of the block, found by the warp together: a chunk holds at least one voxel,
+        // so the chunks that start inside the block are among the 32 descriptors after c0, one per lane; the bit
+        // mask of their starting positions turns "my descriptor" into a population count and two shuffles.
+        const unsigned ci = c0 + 1 + lane;
+        const uint2 dl = ci < ndesc ? desc(ci) : make_uint2(0u, 0xffffffffu);
+        const unsigned rel = dl.y - j0;
+        const unsigned starts = __reduce_or_sync(0xffffffffu, rel < 32u ? 1u << rel : 0u);
+        const unsigned idx = (unsigned)__popc(starts & (0xffffffffu >> (31 - lane)));  // starts at or before j
+        const unsigned sx = __shfl_sync(0xffffffffu, dl.x, (idx - 1u) & 31u);
+        const unsigned sy = __shfl_sync(0xffffffffu, dl.y, (idx - 1u) & 31u);
+        const uint2 d = idx ? make_uint2(sx, sy) : d0;
+        const unsigned nst = (unsigned)__popc(starts);
+        const unsigned lx = __shfl_sync(0xffffffffu, dl.x, (nst - 1u) & 31u);
+        const unsigned ly = __shfl_sync(0xffffffffu, dl.y, (nst - 1u) & 31u);
+        if (nst) { d0 = make_uint2(lx, ly); c0 += nst; }
         if (on[b]) {
-          while (c + 1 < ndesc && desc(c + 1).y <= j) ++c;
-          const uint2 d = desc(c);
           uu[b] = (d.x & kVoxMask) + (j - d.y);
           cin[b] = (d.x & kVoxInside) != 0;
           vx[b] = m.vox[uu[b]];
