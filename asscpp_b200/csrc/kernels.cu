@@ -937,7 +937,8 @@ __device__ __forceinline__ void dda_step(float& tx, float& ty, float& tz, int& p
 template <bool SMEM>
 __device__ __forceinline__ bool cell_occupied(const GridView& g, const GridMem& gm, int c0, int c1, int c2) {
   int a0 = c0, a1 = c1, a2 = c2;
-  if (c0 < 0 || c0 == g.div[0] || c1 < 0 || c1 == g.div[1] || c2 < 0 || c2 == g.div[2]) {
+  // c in [-1, div]: halo <=> c == -1 or c == div <=> (unsigned)c >= div
+  if ((unsigned)c0 >= (unsigned)g.div[0] || (unsigned)c1 >= (unsigned)g.div[1] || (unsigned)c2 >= (unsigned)g.div[2]) {
     const int lin = c0 + c1 * g.mul1 + c2 * g.mul2;
     if ((unsigned)lin >= g.cells) return false;
     a2 = fast_div(lin, g.mul2, g.mD01);
@@ -1167,10 +1168,12 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
         } else {
           const int q2 = fast_div(p, P01, g.mP01), rm = p - q2 * P01, q1 = fast_div(rm, P0, g.mP0), q0 = rm - q1 * P0;
           const unsigned walked = (unsigned)(abs(q0 - qs0) + abs(q1 - qs1) + abs(q2 - qs2));
-          if (q0 == 0 || q0 == P0 - 1 || q1 == 0 || q1 == g.P1 - 1 || q2 == 0 || q2 == g.P2 - 1) {
+          // q in [0, P - 1]: sentinel layer <=> q == 0 or q == P - 1 <=> (unsigned)(q - 1) >= P - 2
+          if ((unsigned)(q0 - 1) >= (unsigned)(P0 - 2) || (unsigned)(q1 - 1) >= (unsigned)(g.P1 - 2) ||
+              (unsigned)(q2 - 1) >= (unsigned)(g.P2 - 2)) {
             steps_lo += walked;                                            // left the expanded box (:538-540): result 0
             freed = 1;
-          } else if (((q0 > 1 && q0 < P0 - 2 && q1 > 1 && q1 < g.P1 - 2 && q2 > 1 && q2 < g.P2 - 2) ||  // interior: the set bit IS the occupancy
+          } else if ((((unsigned)(q0 - 2) < (unsigned)(P0 - 4) && (unsigned)(q1 - 2) < (unsigned)(g.P1 - 4) && (unsigned)(q2 - 2) < (unsigned)(g.P2 - 4)) ||  // interior: the set bit IS the occupancy
                       cell_occupied<SMEM>(g, gm, q0 - 2, q1 - 2, q2 - 2)) &&                              // halo: aliased lookup (Q3)
                      is_occluder(g, q0 - 2, q1 - 2, q2 - 2, qt0 - 2, qt1 - 2, qt2 - 2)) {
             steps_lo += walked + 1;                                        // :561-562 result 1
