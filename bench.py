@@ -19,6 +19,9 @@ collective is the gain-score allgather (NCCL) at the end of each step.
            B_VE = 16 N + 20 S_v + G_v/8 + 2 N/8 + 36.  The kernel pre-culls voxel buckets, so it moves far
            fewer bytes than the reference algorithm nominally touches: frac > 1 is expected and
            `traffic` (ncu dram bytes per launch) is the figure to read next to it.
+           `roofline.issue` (default workload only) is the bound the kernel actually runs against: warp
+           instructions per launch from the committed ncu capture / this run's launch time / (SMs x sampled SM
+           clock), against 4 per cycle per SM.
 """
 import argparse
 import json
@@ -135,6 +138,28 @@ def ncu_traffic():
         except Exception:
             return None
     return None
+
+
+def issue_roofline(kern_ms, kern_launches, clocks, views_per_launch, n_points, device):
+    """What actually bounds eval_views_kernel: warp-instruction issue.  Instructions per launch come from the
+    committed ncu capture (valid for the default workload only); rate = that count / the launch time measured in
+    this run / (SMs x SM clock sampled in this run); peak = 4 warp instructions per cycle per SM."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        import torch
+        t = json.load(open(p))
+        inst = t.get("eval_views_kernel_warp_instructions_per_launch")
+        if not inst or t.get("views_per_launch") != views_per_launch or t.get("points") != n_points:
+            return None
+        sms = torch.cuda.get_device_properties(device).multi_processor_count
+        mhz = float(clocks.get("sm_mhz") or clocks.get("sm_max_mhz") or 0.0)
+        if mhz <= 0 or kern_launches <= 0:
+            return None
+        ipc = inst / (kern_ms / kern_launches * 1e-3) / (sms * mhz * 1e6)
+        return {"bound": "issue", "achieved": ipc, "peak": 4.0, "unit": "warp inst/cycle/SM", "frac": ipc / 4.0,
+                "warp_instructions_per_launch": inst, "source": "profiles/r01_ncu_eval_views_full.txt"}
+    except Exception:
+        return None
 
 
 def algorithmic_bytes(n_points, res):
@@ -349,6 +374,9 @@ def main():
                                  "not bandwidth; see traffic and DESIGN.md"},
             "create_seconds": t_create,
         }
+        iss = issue_roofline(kern_ms, kern_launches, clocks, B, a.points, local)
+        if iss is not None and not a.brute:
+            out["roofline"]["issue"] = iss
         if n_gpus == 1 and not a.no_cpu_baseline:
             nthreads = os.cpu_count() or 1
             _, cpu = cpu_leg(a, xyz, step_views(a.warmup), a.cpu_seconds, nthreads)
