@@ -12,7 +12,7 @@ import numpy as np
 
 from . import _abi
 from ._abi import (ACCURACY_DTYPE, CLUSTER_DTYPE, EVAL_ACCURACY, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, RESULT_DTYPE,
-                   VS_GRID_GLOBAL, VS_GRID_SHARED, VS_ORDERED, ModelInfo, Params)
+                   VS_GRID_GLOBAL, VS_GRID_SHARED, VS_ORDERED, EvalOpts, ModelInfo, Params)
 
 __all__ = [
     "CoverageContext", "CoveredSet", "Mesh", "AsscppError", "default_params", "synth_structure", "synth_views",
@@ -71,6 +71,19 @@ def robot2sensor(robot_pose, offset, rpy):
                                          _ptr(out, C.c_double))
     if rc:
         raise AsscppError(rc, "robot2sensor")
+    return out
+
+
+def robot2sensor_batch(robot_poses, offset, rpy):
+    """sspp/src/sensors.cpp:47-90 for a whole search space in one call ([n, 7] -> [n, 7])."""
+    rp = np.ascontiguousarray(robot_poses, np.float64).reshape(-1, 7)
+    off = np.ascontiguousarray(offset, np.float64)
+    r = np.ascontiguousarray(rpy, np.float64)
+    out = np.zeros_like(rp)
+    rc = _abi.load().asscpp_robot2sensor_batch(_ptr(rp, C.c_double), len(rp), _ptr(off, C.c_double),
+                                               _ptr(r, C.c_double), _ptr(out, C.c_double))
+    if rc:
+        raise AsscppError(rc, "robot2sensor_batch")
     return out
 
 
@@ -285,6 +298,25 @@ class CoverageContext:
                                            -1 if covered is None else covered.handle, flags))
         return self.results(poses.shape[0])
 
+    def eval_ex(self, poses, covered=None, accum=None, accum_min_visible=5, group_size=1, flags=0, nviews=None):
+        """asscpp_eval_ex: gains against `covered`, visible sets of views seeing more than accum_min_visible points
+        OR-ed into `accum`, in one launch.  poses: host array [n, 7], or an int (device pointer) with nviews."""
+        o = EvalOpts(-1 if covered is None else covered.handle, -1 if accum is None else accum.handle,
+                     int(accum_min_visible), int(group_size), int(flags), 0, 0)
+        if isinstance(poses, int):
+            o.poses_on_device = 1
+            self._ck(self.L.asscpp_eval_ex(self.h, C.c_void_p(poses), int(nviews), C.byref(o)))
+            return int(nviews)
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        self._ck(self.L.asscpp_eval_ex(self.h, poses.ctypes.data_as(C.c_void_p), poses.shape[0], C.byref(o)))
+        return poses.shape[0]
+
+    def gains(self, nviews):
+        """(gain_pts, gain_vox) of the last evaluation: 8 bytes per view device -> host."""
+        gp, gv = np.zeros(nviews, np.uint32), np.zeros(nviews, np.uint32)
+        self._ck(self.L.asscpp_get_gain(self.h, _ptr(gp, C.c_uint32), _ptr(gv, C.c_uint32), nviews))
+        return gp, gv
+
     def accuracy(self, nviews):
         """Accuracy terms of the last evaluation issued with EVAL_ACCURACY (AsscppViewAccuracy per view)."""
         out = np.zeros(nviews, ACCURACY_DTYPE)
@@ -367,6 +399,22 @@ class CoverageContext:
         out = np.zeros(nviews_local * self.nranks, RESULT_DTYPE)
         self._ck(self.L.asscpp_allgather_results(self.h, nviews_local, out.ctypes.data_as(C.c_void_p)))
         return out
+
+    def allgather_gain(self, nviews_local, to_host=True):
+        """gain-score allgather (8 bytes per view); to_host=False leaves the gathered scores on the device."""
+        if not to_host:
+            self._ck(self.L.asscpp_allgather_gain(self.h, nviews_local, None, None))
+            return None
+        gp = np.zeros(nviews_local * self.nranks, np.uint32)
+        gv = np.zeros(nviews_local * self.nranks, np.uint32)
+        self._ck(self.L.asscpp_allgather_gain(self.h, nviews_local, _ptr(gp, C.c_uint32), _ptr(gv, C.c_uint32)))
+        return gp, gv
+
+    def collective_ms(self):
+        """device time of (allgather, OR-allreduce) between the last timer_begin / timer_end, with call counts."""
+        a, b, na, nb = C.c_float(), C.c_float(), C.c_int64(), C.c_int64()
+        self._ck(self.L.asscpp_collective_ms(self.h, C.byref(a), C.byref(na), C.byref(b), C.byref(nb)))
+        return (a.value, na.value), (b.value, nb.value)
 
     def allreduce_or(self, covered):
         self._ck(self.L.asscpp_allreduce_or(self.h, covered.handle))

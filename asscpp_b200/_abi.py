@@ -41,6 +41,18 @@ class ModelInfo(C.Structure):
     ]
 
 
+class EvalOpts(C.Structure):
+    _fields_ = [
+        ("covered_set", C.c_int32),
+        ("accum_set", C.c_int32),
+        ("accum_min_visible", C.c_int64),
+        ("group_size", C.c_int32),
+        ("flags", C.c_uint32),
+        ("poses_on_device", C.c_uint32),
+        ("reserved", C.c_uint32),
+    ]
+
+
 # numpy mirror of AsscppViewResult
 RESULT_DTYPE = np.dtype(
     [
@@ -102,7 +114,12 @@ SYMBOLS = [
     "asscpp_uncovered_voxels", "asscpp_uncovered_clusters",
     "asscpp_eval_groups", "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
     "asscpp_mesh_last_error", "asscpp_mesh_filter", "asscpp_mesh_segments_free",
+    "asscpp_eval_ex", "asscpp_allgather_gain", "asscpp_collective_ms", "asscpp_robot2sensor_batch",
 ]
+
+# the host-only subset, also exported by lib/libasscpp_host.so (no CUDA inside)
+HOST_LIB_PATH = os.path.join(_HERE, "lib", "libasscpp_host.so")
+HOST_SYMBOLS = ["asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor", "asscpp_robot2sensor_batch"]
 
 _lib = None
 
@@ -176,6 +193,10 @@ def load():
         "asscpp_mesh_segments_free": (i32, [vp, f64p, f64p, i64, u8p]),
         "asscpp_uncovered_voxels": (i32, [vp, i32, i32p, f32p, i64, i64p]),
         "asscpp_uncovered_clusters": (i32, [vp, i32, C.c_double, C.c_int32, C.c_int32, i32p, vp, i64, i64p]),
+        "asscpp_eval_ex": (i32, [vp, vp, i64, C.POINTER(EvalOpts)]),
+        "asscpp_allgather_gain": (i32, [vp, i64, u32p, u32p]),
+        "asscpp_collective_ms": (i32, [vp, f32p, i64p, f32p, i64p]),
+        "asscpp_robot2sensor_batch": (i32, [f64p, i64, f64p, f64p, f64p]),
     }
     assert sorted(sig) == sorted(SYMBOLS)
     for name, (res, args) in sig.items():

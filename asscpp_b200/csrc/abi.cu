@@ -95,6 +95,8 @@ struct AsscppCtx {
   double* d_poses = nullptr;
   ViewDev* d_views = nullptr;
   AsscppViewResult* d_results = nullptr;
+  uint2* d_gains = nullptr;     // packed {gain_pts, gain_vox} per view (what asscpp_get_gain / asscpp_allgather_gain move)
+  std::vector<uint2> h_gains;
   int32_t* d_ordered_list = nullptr;
   ViewTrig* d_trig = nullptr;   // ASSCPP_EVAL_ACCURACY
   AccRaw* d_acc = nullptr;
@@ -121,16 +123,20 @@ struct AsscppCtx {
   // timing
   cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
   bool timing = false;
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kernel_events;
+  struct TimedSpan { int kind; cudaEvent_t e0, e1; };  // kind 0 eval_views_kernel, 1 allgather, 2 OR-allreduce
+  std::vector<TimedSpan> kernel_events;
   size_t kernel_events_used = 0;
   float last_kernel_ms = 0;
   int64_t last_kernel_launches = 0;
+  float last_coll_ms[2] = {0, 0};
+  int64_t last_coll_calls[2] = {0, 0};
   int64_t launches = 0;
   // nccl
   NcclComm comm = nullptr;
   int nranks = 1, rank = 0;
   void* d_gather = nullptr;
   size_t gather_bytes = 0;
+  int64_t* d_cnt = nullptr;  // [1 + nranks] equal-count check of the host-output allgathers
   std::string err;
 };
 
@@ -201,11 +207,12 @@ int ensure_views(AsscppCtx* c, int64_t nviews) {
   CU(c, cudaStreamSynchronize(c->stream));
   int64_t cap = std::max<int64_t>(nviews, c->view_cap * 2);
   cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
-  cudaFree(c->d_trig); cudaFree(c->d_acc);
+  cudaFree(c->d_trig); cudaFree(c->d_acc); cudaFree(c->d_gains);
   c->d_poses = nullptr; c->d_views = nullptr; c->d_results = nullptr; c->d_ordered_list = nullptr;
-  c->d_trig = nullptr; c->d_acc = nullptr;
+  c->d_trig = nullptr; c->d_acc = nullptr; c->d_gains = nullptr;
   c->view_cap = 0;
   int rc;
+  if ((rc = dev_alloc(c, &c->d_gains, cap, false))) return rc;
   if ((rc = dev_alloc(c, &c->d_poses, cap * 7, false))) return rc;
   if ((rc = dev_alloc(c, &c->d_views, cap, false))) return rc;
   if ((rc = dev_alloc(c, &c->d_results, cap, false))) return rc;
@@ -216,6 +223,24 @@ int ensure_views(AsscppCtx* c, int64_t nviews) {
   return ASSCPP_OK;
 }
 
+// between asscpp_timer_begin / _end: bracket a kernel or a collective with events on the context's stream
+AsscppCtx::TimedSpan* span_begin(AsscppCtx* c, int kind) {
+  if (!c->timing) return nullptr;
+  if (c->kernel_events_used == c->kernel_events.size()) {
+    AsscppCtx::TimedSpan t;
+    t.kind = kind;
+    if (cudaEventCreate(&t.e0) != cudaSuccess || cudaEventCreate(&t.e1) != cudaSuccess) return nullptr;
+    c->kernel_events.push_back(t);
+  }
+  AsscppCtx::TimedSpan* t = &c->kernel_events[c->kernel_events_used++];
+  t->kind = kind;
+  cudaEventRecord(t->e0, c->stream);
+  return t;
+}
+void span_end(AsscppCtx* c, AsscppCtx::TimedSpan* t) {
+  if (t) cudaEventRecord(t->e1, c->stream);
+}
+
 // planes -> eval -> ordered, all on the context's stream
 int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_set, int accum_set,
              int64_t accum_min_visible, uint32_t flags, const double* h_poses = nullptr, int group = 1) {
@@ -223,6 +248,10 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   if (group < 1) { c->err = "group size must be at least 1"; return ASSCPP_EINVAL; }
   if (covered_set != -1 && !valid_set(c, covered_set)) { c->err = "bad covered set handle"; return ASSCPP_EINVAL; }
   if (accum_set != -1 && !valid_set(c, accum_set)) { c->err = "bad accumulator set handle"; return ASSCPP_EINVAL; }
+  if (accum_set != -1 && accum_set == covered_set) {
+    c->err = "the accumulator must differ from the set scored against (gains would depend on the view order)";
+    return ASSCPP_EINVAL;
+  }
   c->last_nviews = nviews;
   c->last_had_acc = (flags & ASSCPP_EVAL_ACCURACY) != 0;
   if (nviews == 0) return ASSCPP_OK;
@@ -240,7 +269,7 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
       c->launches += 1;
     }
   }
-  CU(c, cudaMemsetAsync(c->d_counters, 0, 2 * sizeof(int32_t), c->stream));
+  CU(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(int32_t), c->stream));
   launch_planes(d_poses, nviews, c->fc, c->d_views, c->stream);
   EvalArgs a;
   a.m = c->m;
@@ -248,6 +277,8 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.nviews = nviews;
   a.work_counter = c->d_counters;
   a.results = c->d_results;
+  a.gains = c->d_gains;
+  a.error_count = c->d_counters + 2;
   a.covered.pts = nullptr; a.covered.vox = nullptr;
   if (covered_set >= 0) a.covered = set_dev(c, covered_set);
   a.accum.pts = nullptr; a.accum.vox = nullptr;
@@ -272,21 +303,11 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.smem_grid_words = c->smem_grid_words;
   a.phase_cycles = c->d_phase;
   int ctas = (int)std::min<int64_t>(c->ctas, (nviews + group - 1) / group);
-  std::pair<cudaEvent_t, cudaEvent_t>* evp = nullptr;
-  if (c->timing) {
-    if (c->kernel_events_used == c->kernel_events.size()) {
-      cudaEvent_t e0, e1;
-      CU(c, cudaEventCreate(&e0));
-      CU(c, cudaEventCreate(&e1));
-      c->kernel_events.push_back(std::make_pair(e0, e1));
-    }
-    evp = &c->kernel_events[c->kernel_events_used++];
-    CU(c, cudaEventRecord(evp->first, c->stream));
-  }
+  AsscppCtx::TimedSpan* evp = span_begin(c, 0);
   a.smem_grid_words = c->eval_grid_words;
   launch_eval(a, ctas, c->cta_threads, c->eval_smem_bytes_, c->stream);
   a.smem_grid_words = c->smem_grid_words;
-  if (evp) CU(c, cudaEventRecord(evp->second, c->stream));
+  span_end(c, evp);
   launch_ordered(a, c->ordered_ctas, c->smem_bytes, c->stream);
   c->launches += 3;
   CU(c, cudaGetLastError());
@@ -483,9 +504,9 @@ int asscpp_destroy(AsscppCtx* c) {
   for (void* p : c->allocs) cudaFree(p);
   for (auto& s : c->sets) cudaFree(s.buf);
   cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
-  cudaFree(c->d_trig); cudaFree(c->d_acc);
-  cudaFree(c->d_idx); cudaFree(c->d_cloud); cudaFree(c->d_gather);
-  for (auto& ev : c->kernel_events) { cudaEventDestroy(ev.first); cudaEventDestroy(ev.second); }
+  cudaFree(c->d_trig); cudaFree(c->d_acc); cudaFree(c->d_gains);
+  cudaFree(c->d_idx); cudaFree(c->d_cloud); cudaFree(c->d_gather); cudaFree(c->d_cnt);
+  for (auto& ev : c->kernel_events) { cudaEventDestroy(ev.e0); cudaEventDestroy(ev.e1); }
   if (c->ev_begin) cudaEventDestroy(c->ev_begin);
   if (c->ev_end) cudaEventDestroy(c->ev_end);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -588,16 +609,43 @@ int asscpp_get_counts(AsscppCtx* c, uint32_t* survivors, uint32_t* visible, uint
   return ASSCPP_OK;
 }
 
+// the packed 8 bytes per view only; the 64-byte records stay on the device
+static int fetch_gains(AsscppCtx* c, const uint2* d_src, int64_t count) {
+  c->h_gains.resize((size_t)std::max<int64_t>(count, 1));
+  int32_t counters[4] = {0, 0, 0, 0};
+  if (count > 0)
+    CU(c, cudaMemcpyAsync(c->h_gains.data(), d_src, (size_t)count * sizeof(uint2), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(counters, c->d_counters, sizeof(counters), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (counters[2]) { c->err = "internal scratch bound violated for a view"; return ASSCPP_ERANGE; }
+  return ASSCPP_OK;
+}
+
 int asscpp_get_gain(AsscppCtx* c, uint32_t* gain_pts, uint32_t* gain_vox, int64_t nviews) {
   if (!c || nviews < 0) return ASSCPP_EINVAL;
   cudaSetDevice(c->device);
-  int rc = fetch_results(c, nviews);
+  if (c->last_nviews < 0) { c->err = "no evaluation has been issued"; return ASSCPP_ESTATE; }
+  if (nviews > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
+  int rc = fetch_gains(c, c->d_gains, nviews);
   if (rc) return rc;
   for (int64_t v = 0; v < nviews; ++v) {
-    if (gain_pts) gain_pts[v] = c->h_results[v].gain_pts;
-    if (gain_vox) gain_vox[v] = c->h_results[v].gain_vox;
+    if (gain_pts) gain_pts[v] = c->h_gains[(size_t)v].x;
+    if (gain_vox) gain_vox[v] = c->h_gains[(size_t)v].y;
   }
   return ASSCPP_OK;
+}
+
+int asscpp_eval_ex(AsscppCtx* c, const double* poses, int64_t nviews, const AsscppEvalOpts* o) {
+  if (!c || !o || (!poses && nviews > 0) || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  int rc = ensure_views(c, nviews);
+  if (rc) return rc;
+  const int group = o->group_size > 0 ? o->group_size : 1;
+  if (o->poses_on_device)
+    return run_eval(c, poses, nviews, o->covered_set, o->accum_set, o->accum_min_visible, o->flags, nullptr, group);
+  if (nviews > 0)
+    CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  return run_eval(c, c->d_poses, nviews, o->covered_set, o->accum_set, o->accum_min_visible, o->flags, poses, group);
 }
 
 // ---- covered sets ---------------------------------------------------------------------------------
@@ -814,14 +862,18 @@ int asscpp_timer_end(AsscppCtx* c, float* ms) {
   CU(c, cudaEventRecord(c->ev_end, c->stream));
   CU(c, cudaEventSynchronize(c->ev_end));
   CU(c, cudaEventElapsedTime(ms, c->ev_begin, c->ev_end));
-  float total = 0;
+  float total[3] = {0, 0, 0};
+  int64_t calls[3] = {0, 0, 0};
   for (size_t i = 0; i < c->kernel_events_used; ++i) {
     float t = 0;
-    CU(c, cudaEventElapsedTime(&t, c->kernel_events[i].first, c->kernel_events[i].second));
-    total += t;
+    CU(c, cudaEventElapsedTime(&t, c->kernel_events[i].e0, c->kernel_events[i].e1));
+    total[c->kernel_events[i].kind] += t;
+    calls[c->kernel_events[i].kind] += 1;
   }
-  c->last_kernel_ms = total;
-  c->last_kernel_launches = (int64_t)c->kernel_events_used;
+  c->last_kernel_ms = total[0];
+  c->last_kernel_launches = calls[0];
+  c->last_coll_ms[0] = total[1]; c->last_coll_ms[1] = total[2];
+  c->last_coll_calls[0] = calls[1]; c->last_coll_calls[1] = calls[2];
   c->timing = false;
   c->kernel_events_used = 0;
   return ASSCPP_OK;
@@ -999,20 +1051,80 @@ static int ensure_gather(AsscppCtx* c, size_t bytes) {
   return ASSCPP_OK;
 }
 
+// ncclAllGather needs the same count on every rank: exchange the counts first (8 bytes per rank) and refuse a
+// mismatch instead of hanging or corrupting the gather buffer.  Costs one small collective and a stream sync, so it
+// is done by the host-output variants only (they synchronise anyway).
+static int check_equal_counts(AsscppCtx* c, int64_t nviews_local) {
+  if (!c->d_cnt) {
+    int rc = dev_alloc(c, &c->d_cnt, 1 + c->nranks, false);
+    if (rc) return rc;
+  }
+  std::vector<int64_t> h((size_t)c->nranks + 1, 0);
+  h[0] = nviews_local;
+  CU(c, cudaMemcpyAsync(c->d_cnt, h.data(), sizeof(int64_t), cudaMemcpyHostToDevice, c->stream));
+  int r = g_nccl.AllGather(c->d_cnt, c->d_cnt + 1, sizeof(int64_t), kNcclUint8, c->comm, c->stream);
+  if (r != 0) { c->err = "ncclAllGather failed"; return ASSCPP_ENCCL; }
+  CU(c, cudaMemcpyAsync(h.data() + 1, c->d_cnt + 1, (size_t)c->nranks * sizeof(int64_t), cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  for (int k = 0; k < c->nranks; ++k)
+    if (h[(size_t)k + 1] != nviews_local) {
+      c->err = "allgather needs the same view count on every rank (pad the shards): rank " + std::to_string(k) +
+               " has " + std::to_string(h[(size_t)k + 1]) + ", this rank " + std::to_string(nviews_local);
+      return ASSCPP_EINVAL;
+    }
+  return ASSCPP_OK;
+}
+
 int asscpp_allgather_results(AsscppCtx* c, int64_t nviews_local, AsscppViewResult* out) {
   if (!c || nviews_local < 0) return ASSCPP_EINVAL;
   if (!c->comm) { c->err = "communicator not initialised"; return ASSCPP_ESTATE; }
   if (nviews_local > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
   cudaSetDevice(c->device);
+  if (out) {
+    int rc = check_equal_counts(c, nviews_local);
+    if (rc) return rc;
+  }
   size_t bytes = (size_t)nviews_local * sizeof(AsscppViewResult);
   int rc = ensure_gather(c, bytes * c->nranks);
   if (rc) return rc;
   if (bytes) {
+    AsscppCtx::TimedSpan* sp = span_begin(c, 1);
     int r = g_nccl.AllGather(c->d_results, c->d_gather, bytes, kNcclUint8, c->comm, c->stream);
+    span_end(c, sp);
     if (r != 0) { c->err = "ncclAllGather failed"; return ASSCPP_ENCCL; }
     if (out) CU(c, cudaMemcpyAsync(out, c->d_gather, bytes * c->nranks, cudaMemcpyDeviceToHost, c->stream));
   }
   if (out) CU(c, cudaStreamSynchronize(c->stream));  // out == NULL: gathered scores stay on the device, async
+  return ASSCPP_OK;
+}
+
+int asscpp_allgather_gain(AsscppCtx* c, int64_t nviews_local, uint32_t* gain_pts, uint32_t* gain_vox) {
+  if (!c || nviews_local < 0) return ASSCPP_EINVAL;
+  if (!c->comm) { c->err = "communicator not initialised"; return ASSCPP_ESTATE; }
+  if (nviews_local > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
+  cudaSetDevice(c->device);
+  const bool to_host = gain_pts || gain_vox;
+  if (to_host) {
+    int rc = check_equal_counts(c, nviews_local);
+    if (rc) return rc;
+  }
+  const size_t bytes = (size_t)nviews_local * sizeof(uint2);
+  int rc = ensure_gather(c, std::max<size_t>(bytes * c->nranks, 16));
+  if (rc) return rc;
+  if (bytes) {
+    AsscppCtx::TimedSpan* sp = span_begin(c, 1);
+    int r = g_nccl.AllGather(c->d_gains, c->d_gather, bytes, kNcclUint8, c->comm, c->stream);
+    span_end(c, sp);
+    if (r != 0) { c->err = "ncclAllGather failed"; return ASSCPP_ENCCL; }
+  }
+  if (!to_host) return ASSCPP_OK;  // gathered scores stay on the device (rank-major uint2 array), async
+  const int64_t total = nviews_local * c->nranks;
+  rc = fetch_gains(c, (const uint2*)c->d_gather, total);
+  if (rc) return rc;
+  for (int64_t v = 0; v < total; ++v) {
+    if (gain_pts) gain_pts[v] = c->h_gains[(size_t)v].x;
+    if (gain_vox) gain_vox[v] = c->h_gains[(size_t)v].y;
+  }
   return ASSCPP_OK;
 }
 
@@ -1024,11 +1136,23 @@ int asscpp_allreduce_or(AsscppCtx* c, int set) {
   int rc = ensure_gather(c, bytes * c->nranks);
   if (rc) return rc;
   // NCCL has no bitwise-OR reduction: gather every rank's bitset, then OR them locally
+  AsscppCtx::TimedSpan* sp = span_begin(c, 2);
   int r = g_nccl.AllGather(c->sets[set].buf, c->d_gather, bytes, kNcclUint8, c->comm, c->stream);
   if (r != 0) { c->err = "ncclAllGather failed"; return ASSCPP_ENCCL; }
   launch_or_reduce(c->sets[set].buf, (const uint32_t*)c->d_gather, set_words(c), c->nranks, c->stream);
+  span_end(c, sp);
   c->launches += 1;
   CU(c, cudaGetLastError());
+  return ASSCPP_OK;
+}
+
+int asscpp_collective_ms(AsscppCtx* c, float* allgather_ms, int64_t* allgather_calls, float* allreduce_or_ms,
+                         int64_t* allreduce_or_calls) {
+  if (!c) return ASSCPP_EINVAL;
+  if (allgather_ms) *allgather_ms = c->last_coll_ms[0];
+  if (allgather_calls) *allgather_calls = c->last_coll_calls[0];
+  if (allreduce_or_ms) *allreduce_or_ms = c->last_coll_ms[1];
+  if (allreduce_or_calls) *allreduce_or_calls = c->last_coll_calls[1];
   return ASSCPP_OK;
 }
 
@@ -1042,6 +1166,8 @@ int asscpp_comm_destroy(AsscppCtx* c) {
   c->comm = nullptr;
   c->nranks = 1;
   c->rank = 0;
+  cudaFree(c->d_cnt);
+  c->d_cnt = nullptr;
   return ASSCPP_OK;
 }
 

@@ -74,6 +74,8 @@ struct EvalArgs {
   int64_t nviews;
   int32_t* work_counter;     // device scalar, zeroed before launch
   AsscppViewResult* results;
+  uint2* gains;              // [nviews] {gain_pts, gain_vox}: the 8 bytes per view a search loop reads back
+  int32_t* error_count;      // views whose scratch bound was violated (kVsError), zeroed before launch
   CoveredDev covered;        // score against (pts == nullptr: empty set)
   CoveredDev accum;          // OR visible sets into (pts == nullptr: none)
   int64_t accum_min_visible;

@@ -1405,6 +1405,8 @@ __device__ __forceinline__ void write_result(const EvalArgs& A, const ViewShared
   r.cells = sh.survivors ? (uint64_t)sh.g.cells : 0;
   r.steps = sh.steps; r.vis_hash = sh.vis_hash; r.surv_hash = sh.surv_hash;
   A.results[v] = r;
+  A.gains[v] = make_uint2(sh.gain_p, sh.gain_v);
+  if (sh.status & kVsError) atomicAdd(A.error_count, 1);
   if (A.acc) {
     AccRaw a;
     a.d_hi = sh.acc[0]; a.d_lo = sh.acc[1]; a.z_hi = sh.acc[2]; a.z_lo = sh.acc[3];

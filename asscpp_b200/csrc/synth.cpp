@@ -186,6 +186,18 @@ int asscpp_robot2sensor(const double robot_pose[7], const double offset[3], cons
   return ASSCPP_OK;
 }
 
+int asscpp_robot2sensor_batch(const double* robot_poses, int64_t n, const double offset[3], const double rpy[3],
+                              double* sensor_poses) {
+  if (n < 0 || ((!robot_poses || !sensor_poses) && n > 0) || !offset || !rpy) return ASSCPP_EINVAL;
+  // same operation order per pose as the one-pose entry point (the products are not re-associated), so the
+  // two agree bit for bit
+  for (int64_t k = 0; k < n; ++k) {
+    int rc = asscpp_robot2sensor(robot_poses + 7 * k, offset, rpy, sensor_poses + 7 * k);
+    if (rc) return rc;
+  }
+  return ASSCPP_OK;
+}
+
 int asscpp_synth_structure_v1(uint64_t structure_seed, uint64_t point_seed, int64_t n, float* xyz_out) {
   if (n < 0 || (!xyz_out && n > 0)) return ASSCPP_EINVAL;
   std::vector<Shape> shapes = make_shapes(structure_seed);

@@ -136,7 +136,26 @@ int asscpp_eval_groups(AsscppCtx* ctx, const double* poses, int64_t nviews, int 
                        uint32_t flags);
 int asscpp_get_results(AsscppCtx* ctx, AsscppViewResult* out, int64_t nviews); /* synchronises */
 int asscpp_get_counts(AsscppCtx* ctx, uint32_t* survivors, uint32_t* visible, uint32_t* carry, int64_t nviews);
+/* The two scores a search loop reads per view (c = coverage - parent coverage, heuristic.cpp:482-483, in bitset
+ * form).  Moves 8 bytes per view device -> host, not the 64-byte record.  Either output may be NULL. */
 int asscpp_get_gain(AsscppCtx* ctx, uint32_t* gain_pts, uint32_t* gain_vox, int64_t nviews);
+
+/* General form of the evaluation calls above.  One launch does, per view: cull + per-view grid + DDA, gains against
+ * covered_set (-1: the empty set), and -- for views whose visible count exceeds accum_min_visible -- the OR of the
+ * visible set into accum_set (-1: none; must differ from covered_set).  That is isFilteringConditionSatisfied's
+ * "if(pts.size()>5) globalCloud += pts" (heuristic.cpp:342-346) and calculateHeuristic's scoring (:473-483) in one
+ * pass.  group_size as asscpp_eval_groups (0 or 1: every view on its own).  poses_on_device != 0: poses is a device
+ * pointer (nviews x 7 doubles already in HBM); ASSCPP_EVAL_ACCURACY then uses device trigonometry. */
+typedef struct AsscppEvalOpts {
+  int32_t covered_set;
+  int32_t accum_set;
+  int64_t accum_min_visible;
+  int32_t group_size;
+  uint32_t flags;
+  uint32_t poses_on_device;
+  uint32_t reserved;
+} AsscppEvalOpts;
+int asscpp_eval_ex(AsscppCtx* ctx, const double* poses, int64_t nviews, const AsscppEvalOpts* opts);
 
 /* accuracy terms of the last evaluation issued with ASSCPP_EVAL_ACCURACY (synchronises) */
 int asscpp_get_accuracy(AsscppCtx* ctx, AsscppViewAccuracy* out, int64_t nviews);
@@ -233,11 +252,22 @@ int asscpp_comm_init(AsscppCtx* ctx, int nranks, int rank, const uint8_t id[128]
  * nranks * nviews_local results in rank order.  out == NULL keeps the gathered scores on the
  * device and returns without synchronising. */
 int asscpp_allgather_results(AsscppCtx* ctx, int64_t nviews_local, AsscppViewResult* out);
+/* The same for the 8 bytes a search loop needs per view: gain_pts / gain_vox (host, nranks * nviews_local entries
+ * each, rank order; either may be NULL).  Both NULL: the gathered scores stay on the device, no synchronisation.
+ * EVERY RANK MUST PASS THE SAME nviews_local (pad uneven shards with repeated poses): the host-output forms of both
+ * allgathers exchange the counts first and return ASSCPP_EINVAL on a mismatch; the device-output forms do not check. */
+int asscpp_allgather_gain(AsscppCtx* ctx, int64_t nviews_local, uint32_t* gain_pts, uint32_t* gain_vox);
 /* covered-bitset OR-allreduce (NCCL has no OR op: allgather + fused OR kernel) */
 int asscpp_allreduce_or(AsscppCtx* ctx, int set);
+/* device time spent in the two collectives between asscpp_timer_begin / asscpp_timer_end (CUDA events around them) */
+int asscpp_collective_ms(AsscppCtx* ctx, float* allgather_ms, int64_t* allgather_calls, float* allreduce_or_ms,
+                         int64_t* allreduce_or_calls);
 int asscpp_comm_destroy(AsscppCtx* ctx);
 
 /* -- synthetic workloads of BASELINE.json configs 2/3/5 (host generators) ------- */
+/* These host-only helpers (generators, pose transforms) are also exported by asscpp_b200/lib/libasscpp_host.so,
+ * which has no CUDA in it: the benchmark's CPU reference arm draws its inputs from there, so it never maps the
+ * product's CUDA library. */
 /* structure_seed places the shapes (default 0xA55C0001); point_seed / view_seed drive the
  * sampling streams (defaults 0xA55C0002 / 0xA55C0003).  Deterministic, host only. */
 int asscpp_synth_structure_v1(uint64_t structure_seed, uint64_t point_seed, int64_t n, float* xyz_out);
@@ -246,6 +276,10 @@ int asscpp_synth_views_v1(uint64_t structure_seed, uint64_t view_seed, int64_t n
 /* sspp/src/sensors.cpp:47-90 robot pose -> sensor pose (batcher input), host, double */
 int asscpp_robot2sensor(const double robot_pose[7], const double offset[3], const double rpy[3],
                         double sensor_pose[7]);
+/* the same for n robot poses at once (robot_poses, sensor_poses: n x 7 doubles): the batcher's input transform for a
+ * whole search space (pathplanner.cpp:122-147 calls it once per waypoint and sensor) */
+int asscpp_robot2sensor_batch(const double* robot_poses, int64_t n, const double offset[3], const double rpy[3],
+                              double* sensor_poses);
 /* tf::Matrix3x3(q).getRPY(roll, pitch, yaw) of a pose, as used by occlusion_culling.cpp:497-500, 558-561 (host) */
 int asscpp_pose_rpy(const double pose[7], double rpy[3]);
 /* OcclusionCulling::pointCloudViewportTransform (occlusion_culling.cpp:538-618), host: n x xyz float32 -> same */

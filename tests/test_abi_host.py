@@ -112,3 +112,38 @@ def test_viewport_transform_and_rpy_equal_oracle(lib_built, oracle_mod, etihad, 
         view = np.array([1 - 2 * (y * y + z * z) / n, 2 * (x * y + w * z) / n, 2 * (x * z - w * y) / n])
         depth = (pts.astype(np.float64) - pose[:3]) @ view
         assert np.abs(a[:, 0] - depth).max() < 2e-5  # float32 stages over coordinates of tens of metres
+
+
+def test_host_only_library_and_batch_transform(lib_built, space_2p5):
+    """libasscpp_host.so carries the host helpers without CUDA; the batch robot->sensor transform equals the
+    one-pose entry point bit for bit (sspp/src/sensors.cpp:47-90)."""
+    import asscpp_b200 as A
+    from asscpp_b200 import _abi
+    assert os.path.exists(_abi.HOST_LIB_PATH)
+    H = C.CDLL(_abi.HOST_LIB_PATH)
+    for name in _abi.HOST_SYMBOLS:
+        assert hasattr(H, name), name
+    deps = os.popen("ldd %s" % _abi.HOST_LIB_PATH).read()
+    assert "cuda" not in deps.lower() and "nccl" not in deps.lower(), deps
+    uav = space_2p5["uav"][:200]
+    off, rpy = (0.0, 0.022, 0.065), (0.0, -0.349, 0.0)
+    batch = A.robot2sensor_batch(uav, off, rpy)
+    single = np.stack([A.robot2sensor(u, off, rpy) for u in uav])
+    assert np.array_equal(batch, single)
+
+
+def test_reference_arm_never_maps_the_product_library(lib_built):
+    """bench.py --impl reference: inputs from libasscpp_host.so, compute from oracle/; the CUDA library stays unmapped."""
+    import json
+    import subprocess
+    import sys
+    env = dict(os.environ, ASSCPP_BENCH_REPORT_MAPS="1")
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--config", "2",
+                          "--points", "20000", "--views-per-step", "64", "--steps", "1", "--warmup", "3",
+                          "--cpu-seconds", "1"], capture_output=True, text=True, timeout=600, env=env)
+    assert out.returncode == 0, out.stderr
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["value"] > 0
+    maps = line["mapped_repo_libraries"]
+    assert any("libasscpp_oracle" in m for m in maps) and any("libasscpp_host" in m for m in maps)
+    assert not any("libasscpp_b200" in m for m in maps), maps

@@ -238,6 +238,41 @@ def test_covered_sets_and_gain(A, oracle_mod, etihad_ctx, etihad_oracle, space_2
         x.free()
 
 
+def test_eval_ex_scores_and_accumulates_in_one_launch(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
+    """asscpp_eval_ex: gains against one set while the visible sets of views seeing more than 5 points are OR-ed into
+    another (heuristic.cpp:342-346 + :473-483 in one pass); asscpp_get_gain moves the same two numbers as the
+    64-byte records hold."""
+    o = etihad_oracle
+    poses = np.concatenate([space_2p5["cam0"][560:660], space_2p5["cam1"][560:660]])
+    cp = np.zeros(o.pts_words(), np.uint64)
+    cv = np.zeros(o.vox_words(), np.uint64)
+    o.accumulate(poses[:60], cp, cv, min_visible=5, nthreads=NTHREADS)
+    cov = etihad_ctx.new_set()
+    cov.load(cp, cv)
+    acc = etihad_ctx.new_set()
+    n = etihad_ctx.eval_ex(poses, covered=cov, accum=acc, accum_min_visible=5, flags=A.EVAL_HASH)
+    gp, gv = etihad_ctx.gains(n)
+    res = etihad_ctx.results(n)
+    st = o.eval_batch(poses, memo=True, nthreads=NTHREADS, covered_pts=cp, covered_vox=cv)
+    assert_results_equal(oracle_mod, res, st, "eval_ex")
+    assert np.array_equal(gp, res["gain_pts"]) and np.array_equal(gv, res["gain_vox"])
+    ap = np.zeros(o.pts_words(), np.uint64)
+    av = np.zeros(o.vox_words(), np.uint64)
+    o.accumulate(poses, ap, av, min_visible=5, nthreads=NTHREADS)
+    gp2, gv2 = acc.export()
+    assert np.array_equal(gp2, ap) and np.array_equal(gv2, av)
+    # the accumulator may not be the set scored against
+    with pytest.raises(A.AsscppError):
+        etihad_ctx.eval_ex(poses[:4], covered=cov, accum=cov)
+    # grouped form through the same entry point
+    n = etihad_ctx.eval_ex(poses, covered=cov, group_size=2)
+    grp = etihad_ctx.results(n)
+    ref = etihad_ctx.eval_groups(poses, 2, covered=cov)
+    assert np.array_equal(grp["gain_vox"], ref["gain_vox"])
+    cov.free()
+    acc.free()
+
+
 def test_coverage_percent_of_arbitrary_cloud(A, etihad_ctx, etihad_oracle, etihad, space_2p5):
     """calcCoveragePercent(cloud) voxelises any cloud, e.g. VoxelGrid centroids (heuristic.cpp:476-482)."""
     xyz = etihad[0]

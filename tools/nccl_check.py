@@ -42,6 +42,28 @@ def main():
         if not np.array_equal(gathered[f], full[f][: per * world]):
             ok = False
             print("rank %d: allgather mismatch in %s" % (rank, f))
+    ctx.timer_begin()
+    ctx.eval_async(poses[lo:hi], None, 0)
+    gp, gv = ctx.allgather_gain(per)
+    ctx.timer_end()
+    (ag_ms, ag_n), _ = ctx.collective_ms()
+    if not (np.array_equal(gp, full["gain_pts"][: per * world]) and np.array_equal(gv, full["gain_vox"][: per * world])):
+        ok = False
+        print("rank %d: gain allgather mismatch" % rank)
+    if ag_n != 1 or not ag_ms > 0:
+        ok = False
+        print("rank %d: collective timing missing (%r, %r)" % (rank, ag_ms, ag_n))
+    # unequal counts are refused, not hung on
+    ctx.eval_async(poses[lo:hi - rank], None, 0)
+    try:
+        ctx.allgather_gain(per - rank)
+        if world > 1:
+            ok = False
+            print("rank %d: unequal allgather counts were accepted" % rank)
+    except A.AsscppError as e:
+        if e.code != -1:
+            ok = False
+            print("rank %d: unexpected error %r" % (rank, e))
     s = ctx.new_set()
     s.or_views(poses[lo:hi], 5)
     if rank == world - 1 and per * world < len(poses):
