@@ -3,5 +3,5 @@
 #include <vector>
 #include "Pose.h"
 namespace geometry_msgs {
-struct PoseArray { std::vector<Pose> poses; };
+struct PoseArray { std_msgs::Header header; std::vector<Pose> poses; };
 }  // namespace geometry_msgs

@@ -9,7 +9,7 @@
 #include "../point_types.h"
 namespace pcl {
 namespace io {
-inline int loadPCDFile(const std::string& path, PointCloud<PointXYZ>& cloud) {
+template <class PointT> inline int loadPCDFile(const std::string& path, PointCloud<PointT>& cloud) {
   std::ifstream f(path.c_str(), std::ios::binary);
   if (!f) return -1;
   std::string line, data;
@@ -38,12 +38,12 @@ inline int loadPCDFile(const std::string& path, PointCloud<PointXYZ>& cloud) {
     std::vector<float> raw(3 * npts);
     f.read(reinterpret_cast<char*>(raw.data()), (std::streamsize)(raw.size() * sizeof(float)));
     if ((size_t)f.gcount() != raw.size() * sizeof(float)) return -3;
-    for (size_t i = 0; i < npts; ++i) cloud.points[i] = PointXYZ(raw[3 * i], raw[3 * i + 1], raw[3 * i + 2]);
+    for (size_t i = 0; i < npts; ++i) { PointT q; q.x = raw[3 * i]; q.y = raw[3 * i + 1]; q.z = raw[3 * i + 2]; cloud.points[i] = q; }
   } else if (data == "ascii") {
     for (size_t i = 0; i < npts; ++i) {
       float x, y, z;
       if (!(f >> x >> y >> z)) return -3;
-      cloud.points[i] = PointXYZ(x, y, z);
+      { PointT q; q.x = x; q.y = y; q.z = z; cloud.points[i] = q; }
     }
   } else {
     return -4;

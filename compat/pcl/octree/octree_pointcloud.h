@@ -1,0 +1,3 @@
+// Stand-in for pcl/octree/octree_pointcloud.h: included by the reference, nothing of it is used on the path.
+#pragma once
+#include <pcl/point_types.h>

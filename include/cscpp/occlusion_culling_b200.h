@@ -52,7 +52,7 @@ class OcclusionCulling {
   explicit OcclusionCulling(pcl::PointCloud<pcl::PointXYZ>::Ptr& cloudPtr, int device = 0) {
     init_members();
     cloud->points = cloudPtr->points;  // occlusion_culling.cpp:94
-    std::memcpy(cloud->sensor_origin_, cloudPtr->sensor_origin_, sizeof(cloud->sensor_origin_));
+    // only ->points is copied (occlusion_culling.cpp:94): cloud->sensor_origin_ stays zero, as in the reference
     finish_init(device);
   }
   ~OcclusionCulling() { asscpp_destroy(ctx_); }

@@ -1,0 +1,270 @@
+// ref_facade.cpp -- C entry points over the REFERENCE's own sources, compiled where they lie under /root/reference
+// by oracle/Makefile into oracle/_ref/libasscpp_ref.so (TEST INFRASTRUCTURE; never loaded by the product).
+//
+// What is the reference's own code here: OcclusionCulling, pcl::FrustumCullingTT, pcl::VoxelGridOcclusionEstimationT,
+// SSPP::CoveragePathPlanningHeuristic, SSPP::PathPlanner / Astar / LList / SearchSpace / Node, Sensors -- unmodified
+// .cpp files (cscpp/src, sspp/src).  What is NOT: their third-party dependencies (PCL, Eigen, tf, ROS, CGAL, octomap),
+// which are absent from this image; they are replaced by the stand-in headers under compat/, restated from the
+// published behaviour of those libraries (see the header comments there).  So this library pins the repo's oracle to
+// the reference's control flow, loop order, quirks and expression structure; the float32 reduction orders inside
+// Eigen's dot / norm and PCL's VoxelGrid binning remain stand-in choices (switchable, see compat/Eigen/Core).
+//
+// This file only adapts types: it calls the reference's public methods and turns point clouds back into index lists.
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include <cscpp/coverage_path_planning_heuristic.h>
+#include <cscpp/occlusion_culling.h>
+#include <sspp/pathplanner.h>
+#include <sspp/sensors.h>
+
+namespace {
+
+ros::NodeHandle g_nh;
+
+geometry_msgs::Pose to_pose(const double* p) {
+  geometry_msgs::Pose q;
+  q.position.x = p[0]; q.position.y = p[1]; q.position.z = p[2];
+  q.orientation.x = p[3]; q.orientation.y = p[4]; q.orientation.z = p[5]; q.orientation.w = p[6];
+  return q;
+}
+
+// `sub` is a subsequence of `all` in the same order (the reference copies points in ascending index order,
+// frustum_culling.cpp:150-166, occlusion_culling.cpp:317-363): recover the indices by a merge walk on the bit
+// patterns.  Points with identical coordinates share their voxel and their plane tests, so they are kept or dropped
+// together and the greedy match is exact.
+int64_t match_indices(const std::vector<pcl::PointXYZ>& all, const std::vector<pcl::PointXYZ>& sub, int32_t* out,
+                      int64_t cap) {
+  size_t i = 0;
+  int64_t k = 0;
+  for (size_t j = 0; j < sub.size(); ++j) {
+    while (i < all.size() && std::memcmp(all[i].data, sub[j].data, 12) != 0) ++i;
+    if (i == all.size()) return -1;
+    if (k < cap && out) out[k] = (int32_t)i;
+    ++k;
+    ++i;
+  }
+  return k;
+}
+
+uint64_t mix64(uint64_t x) {
+  x += 0x9E3779B97F4A7C15ull;
+  x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+  x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+  return x ^ (x >> 31);
+}
+
+}  // namespace
+
+extern "C" {
+
+// OcclusionCulling(ros::NodeHandle&, std::string) -- occlusion_culling.cpp:26-79 (full path of the PCD file)
+void* ref_oc_create_pcd(const char* pcd_path) { return new OcclusionCulling(g_nh, std::string(pcd_path)); }
+
+// OcclusionCulling(ros::NodeHandle&, PointCloud::Ptr&) -- occlusion_culling.cpp:81-135; leaf > 0 overrides the
+// public member voxelRes afterwards (the per-view grid of extractVisibleSurface reads it, :305)
+void* ref_oc_create_points(const float* xyz, int64_t n, float leaf) {
+  pcl::PointCloud<pcl::PointXYZ>::Ptr c(new pcl::PointCloud<pcl::PointXYZ>);
+  c->points.resize((size_t)n);
+  for (int64_t i = 0; i < n; ++i) c->points[(size_t)i] = pcl::PointXYZ(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+  OcclusionCulling* oc = new OcclusionCulling(g_nh, c);
+  if (leaf > 0) oc->voxelRes = leaf;
+  return oc;
+}
+void ref_oc_destroy(void* h) { delete static_cast<OcclusionCulling*>(h); }
+int64_t ref_oc_num_points(void* h) { return (int64_t)static_cast<OcclusionCulling*>(h)->cloud->points.size(); }
+float ref_oc_original_voxels(void* h) { return static_cast<OcclusionCulling*>(h)->OriginalVoxelsSize; }
+void ref_oc_set_origin(void* h, const float o[3]) {  // cloud->sensor_origin_ (PCD VIEWPOINT), read at :338-341
+  static_cast<OcclusionCulling*>(h)->cloud->sensor_origin_ = Eigen::Vector4f(o[0], o[1], o[2], 0.0f);
+}
+
+// extractVisibleSurface (occlusion_culling.cpp:265-373).  vis_idx / surv_idx: ascending original indices of the
+// returned cloud / of FrustumCloud (either may be NULL); counts[0] = survivors, counts[1] = visible.
+int ref_oc_extract(void* h, const double pose[7], int32_t* surv_idx, int32_t* vis_idx, int64_t cap, int64_t counts[2]) {
+  OcclusionCulling* oc = static_cast<OcclusionCulling*>(h);
+  pcl::PointCloud<pcl::PointXYZ> vis = oc->extractVisibleSurface(to_pose(pose));
+  oc->occlusionFreeCloud->points.clear();  // grows for ever in the reference (:363); nothing reads it here
+  counts[0] = match_indices(oc->cloudCopy->points, oc->FrustumCloud->points, surv_idx, cap);
+  counts[1] = match_indices(oc->cloudCopy->points, vis.points, vis_idx, cap);
+  return (counts[0] < 0 || counts[1] < 0) ? -1 : 0;
+}
+
+// calcCoveragePercent (occlusion_culling.cpp:375-444) of the model points with the given indices
+float ref_oc_coverage_percent_idx(void* h, const int32_t* idx, int64_t n) {
+  OcclusionCulling* oc = static_cast<OcclusionCulling*>(h);
+  pcl::PointCloud<pcl::PointXYZ>::Ptr c(new pcl::PointCloud<pcl::PointXYZ>);
+  for (int64_t i = 0; i < n; ++i) c->points.push_back(oc->cloudCopy->points[(size_t)idx[i]]);
+  return oc->calcCoveragePercent(c);
+}
+
+// calcAvgAccuracy, both overloads (occlusion_culling.cpp:445-475), of the model points with the given indices
+void ref_oc_avg_accuracy_idx(void* h, const double pose[7], const int32_t* idx, int64_t n, double out[2]) {
+  OcclusionCulling* oc = static_cast<OcclusionCulling*>(h);
+  pcl::PointCloud<pcl::PointXYZ> c;
+  for (int64_t i = 0; i < n; ++i) c.points.push_back(oc->cloudCopy->points[(size_t)idx[i]]);
+  out[0] = oc->calcAvgAccuracy(c, to_pose(pose));
+  out[1] = oc->calcAvgAccuracy(c);
+}
+
+// pointCloudViewportTransform (occlusion_culling.cpp:538-618)
+void ref_oc_viewport_transform(void* h, const double pose[7], const float* xyz, int64_t n, float* out) {
+  OcclusionCulling* oc = static_cast<OcclusionCulling*>(h);
+  pcl::PointCloud<pcl::PointXYZ> c;
+  for (int64_t i = 0; i < n; ++i) c.points.push_back(pcl::PointXYZ(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+  pcl::PointCloud<pcl::PointXYZ> t = oc->pointCloudViewportTransform(c, to_pose(pose));
+  for (int64_t i = 0; i < n; ++i) { out[3 * i] = t.points[(size_t)i].x; out[3 * i + 1] = t.points[(size_t)i].y; out[3 * i + 2] = t.points[(size_t)i].z; }
+}
+
+// Many viewpoints, one OcclusionCulling instance per host thread (the class is not re-entrant: member state at
+// occlusion_culling.cpp:290,297,363,371).  stats: nviews x {survivors, visible, hash of the visible index set}.
+int ref_oc_eval_batch(void** handles, int nthreads, const double* poses, int64_t nviews, int64_t* stats) {
+  std::vector<std::thread> th;
+  std::vector<int> rc((size_t)nthreads, 0);
+  for (int t = 0; t < nthreads; ++t)
+    th.push_back(std::thread([&, t]() {
+      OcclusionCulling* oc = static_cast<OcclusionCulling*>(handles[t]);
+      std::vector<int32_t> idx(oc->cloudCopy->points.size());
+      for (int64_t v = t; v < nviews; v += nthreads) {
+        int64_t counts[2];
+        if (ref_oc_extract(oc, poses + 7 * v, nullptr, idx.data(), (int64_t)idx.size(), counts)) { rc[(size_t)t] = -1; return; }
+        uint64_t hsh = 0;
+        for (int64_t k = 0; k < counts[1]; ++k) hsh += mix64((uint64_t)(uint32_t)idx[(size_t)k]);
+        stats[3 * v] = counts[0]; stats[3 * v + 1] = counts[1]; stats[3 * v + 2] = (int64_t)hsh;
+      }
+    }));
+  for (size_t t = 0; t < th.size(); ++t) th[t].join();
+  for (int t = 0; t < nthreads; ++t) if (rc[(size_t)t]) return -1;
+  return 0;
+}
+
+// Sensors::robot2sensorTransformation (sspp/src/sensors.cpp:47-90)
+void ref_robot2sensor(const double robot[7], const double off[3], const double rpy[3], double out[7]) {
+  Sensors s(58, 45, 0.255, 0.7, 6.0, 640, 480, Eigen::Vector3f((float)off[0], (float)off[1], (float)off[2]),
+            Eigen::Vector3f((float)rpy[0], (float)rpy[1], (float)rpy[2]));
+  geometry_msgs::Pose p = s.robot2sensorTransformation(to_pose(robot));
+  out[0] = p.position.x; out[1] = p.position.y; out[2] = p.position.z;
+  out[3] = p.orientation.x; out[4] = p.orientation.y; out[5] = p.orientation.z; out[6] = p.orientation.w;
+}
+
+// ---- the reference's planner, driven as its demo does (cscpp/src/coverage_heuristic_test.cpp:73-137, 153-181) ------
+struct RefPlanner {
+  SSPP::CoveragePathPlanningHeuristic* heuristic;
+  SSPP::PathPlanner* planner;
+  Robot* robot;
+};
+
+// heuristic_type: the enum of coverage_path_planning_heuristic.h:72
+void* ref_planner_create(const char* obj_path, const char* pcd_path, int heuristic_type, double target, double tolerance,
+                         double conn_radius) {
+  RefPlanner* r = new RefPlanner();
+  geometry_msgs::Point centre;
+  centre.x = -0.3f; centre.y = 0.0f;
+  r->robot = new Robot("Robot", 0.9, 0.5, 0.987, centre);                     // :85-91
+  std::vector<Sensors> sensors;
+  sensors.push_back(Sensors(58, 45, 0.255, 0.7, 6.0, 640, 480, Eigen::Vector3f(0, 0.022f, 0.065f), Eigen::Vector3f(0, -0.349f, 0)));  // :94
+  sensors.push_back(Sensors(58, 45, 0.255, 0.7, 6.0, 640, 480, Eigen::Vector3f(0, 0.022f, -0.065f), Eigen::Vector3f(0, 0.349f, 0)));  // :95
+  r->planner = new SSPP::PathPlanner(g_nh, r->robot, conn_radius, 0, sensors);  // :102 (progress display off)
+  r->planner->setDebugDelay(0.0);
+  r->heuristic = new SSPP::CoveragePathPlanningHeuristic(g_nh, obj_path, pcd_path, false, false, heuristic_type);  // :111
+  r->heuristic->setCoverageTarget(target);
+  r->heuristic->setCoverageTolerance(tolerance);
+  r->planner->setHeuristicFucntion(r->heuristic);
+  return r;
+}
+void ref_planner_destroy(void* h) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  delete r->planner; delete r->heuristic; delete r->robot; delete r;
+}
+
+// PathPlanner::dynamicNodesGenerationAndConnection (sspp/src/pathplanner.cpp:729-850), demo arguments at
+// coverage_heuristic_test.cpp:75-80,137.  max_iterations < 0: run to the end.
+void ref_planner_dynamic_sampling(void* h, const double grid_start[3], const double grid_size[3], double start_res,
+                                  double res_decrement) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  geometry_msgs::Pose gs;
+  gs.position.x = grid_start[0]; gs.position.y = grid_start[1]; gs.position.z = grid_start[2];
+  geometry_msgs::Vector3 sz;
+  sz.x = grid_size[0]; sz.y = grid_size[1]; sz.z = grid_size[2];
+  r->planner->dynamicNodesGenerationAndConnection(gs, sz, start_res, res_decrement);
+}
+
+// One filtered grid (pathplanner.cpp:106-201 as called at :736): candidates -> isFilteringConditionSatisfied
+void ref_planner_regular_grid(void* h, const double grid_start[3], const double grid_size[3], double res) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  geometry_msgs::Pose gs;
+  gs.position.x = grid_start[0]; gs.position.y = grid_start[1]; gs.position.z = grid_start[2];
+  geometry_msgs::Vector3 sz;
+  sz.x = grid_size[0]; sz.y = grid_size[1]; sz.z = grid_size[2];
+  r->planner->generateRegularGrid(gs, sz, (float)res, true, 45, true, true);
+}
+
+// load a search space from the three pose files (pathplanner.cpp:204-269) and connect it (:529-569)
+void ref_planner_load_grid(void* h, const char* robot_file, const char* sensor0_file, const char* sensor1_file) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  r->planner->loadRegularGrid(robot_file, sensor0_file, sensor1_file);
+  r->planner->connectNodes();
+}
+
+// the search space as the demo prints it (coverage_heuristic_test.cpp:153-181): rows {x y z yaw} + the robot and
+// sensor poses; returns the number of nodes (rows may be NULL to ask for the count)
+int64_t ref_planner_search_space(void* h, double* rows_xyzyaw, double* robot_poses, double* sensor_poses, int64_t cap) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  geometry_msgs::PoseArray robot;
+  std::vector<geometry_msgs::PoseArray> sensors;
+  r->planner->getRobotSensorPoses(robot, sensors);
+  const int64_t n = (int64_t)robot.poses.size();
+  for (int64_t j = 0; j < n && j < cap; ++j) {
+    const geometry_msgs::Pose& p = robot.poses[(size_t)j];
+    if (rows_xyzyaw) {
+      tf::Quaternion qt(p.orientation.x, p.orientation.y, p.orientation.z, p.orientation.w);
+      rows_xyzyaw[4 * j] = p.position.x; rows_xyzyaw[4 * j + 1] = p.position.y; rows_xyzyaw[4 * j + 2] = p.position.z;
+      rows_xyzyaw[4 * j + 3] = tf::getYaw(qt);
+    }
+    if (robot_poses) {
+      double* o = robot_poses + 7 * j;
+      o[0] = p.position.x; o[1] = p.position.y; o[2] = p.position.z;
+      o[3] = p.orientation.x; o[4] = p.orientation.y; o[5] = p.orientation.z; o[6] = p.orientation.w;
+    }
+    if (sensor_poses)
+      for (size_t s = 0; s < sensors.size() && s < 2; ++s) {
+        const geometry_msgs::Pose& q = sensors[s].poses[(size_t)j];
+        double* o = sensor_poses + 14 * j + 7 * s;
+        o[0] = q.position.x; o[1] = q.position.y; o[2] = q.position.z;
+        o[3] = q.orientation.x; o[4] = q.orientation.y; o[5] = q.orientation.z; o[6] = q.orientation.w;
+      }
+  }
+  return n;
+}
+int64_t ref_planner_num_connections(void* h) {
+  return (int64_t)static_cast<RefPlanner*>(h)->planner->getConnections().size() / 2;
+}
+
+// setMaxMinSensorAccuracy over the current search space (coverage_heuristic_test.cpp:155-158)
+void ref_planner_set_accuracy_range(void* h) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  geometry_msgs::PoseArray robot;
+  std::vector<geometry_msgs::PoseArray> sensors;
+  r->planner->getRobotSensorPoses(robot, sensors);
+  r->heuristic->setMaxMinSensorAccuracy(sensors);
+}
+
+// PathPlanner::startSearch (coverage_heuristic_test.cpp:188): path rows {x y z qx qy qz qw coverage f distance}
+int64_t ref_planner_search(void* h, const double start_xyz[3], double* rows, int64_t cap) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  Pose start(start_xyz[0], start_xyz[1], start_xyz[2], 0.0);
+  SSPP::Node* path = r->planner->startSearch(start);
+  int64_t n = 0;
+  for (SSPP::Node* p = path; p != NULL; p = p->next, ++n) {
+    if (n >= cap || !rows) continue;
+    double* o = rows + 10 * n;
+    o[0] = p->pose.p.position.x; o[1] = p->pose.p.position.y; o[2] = p->pose.p.position.z;
+    o[3] = p->pose.p.orientation.x; o[4] = p->pose.p.orientation.y; o[5] = p->pose.p.orientation.z; o[6] = p->pose.p.orientation.w;
+    o[7] = p->coverage; o[8] = p->f_value; o[9] = p->distance;
+  }
+  return n;
+}
+
+}  // extern "C"
