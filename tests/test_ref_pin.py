@@ -1,0 +1,127 @@
+"""Pins the oracle to the REFERENCE'S OWN CODE: oracle/_ref/libasscpp_ref.so is cscpp/src/{frustum_culling,
+voxel_grid_occlusion_estimation, occlusion_culling, coverage_path_planning_heuristic}.cpp and sspp/src/*.cpp compiled
+from /root/reference (oracle/Makefile) against the stand-in third-party headers under compat/.  Every comparison here
+is reference object vs oracle restatement on the same inputs, bit for bit.
+
+The library is built where /root/reference is mounted (this container) and shipped prebuilt; where neither the library
+nor the reference exists the tests skip.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+NTHREADS = os.cpu_count() or 1
+REF_PCD = "/root/reference/cscpp/pcd/etihad_nowheels_nointernal_scaled_newdensed.pcd"
+
+
+@pytest.fixture(scope="module")
+def R():
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("oracle/_ref is not built and /root/reference is not mounted")
+    ref.build()
+    return ref
+
+
+@pytest.fixture(scope="module")
+def ref_oc(R, etihad):
+    # from the model points (the PointCloud::Ptr constructor, occlusion_culling.cpp:81-135): works on the GPU box too
+    oc = R.RefOcclusionCulling(xyz=etihad[0], nthreads=NTHREADS)
+    yield oc
+    oc.close()
+
+
+def test_constructor_counts_model_voxels(R, ref_oc, oracle_mod, etihad):
+    """OriginalVoxelsSize (occlusion_culling.cpp:50-65): 2 759 on the bundled model, both constructors."""
+    assert ref_oc.original_voxels == 2759.0
+    assert oracle_mod.Oracle(etihad[0]).n_cov == 2759
+    if os.path.exists(REF_PCD):
+        oc = R.RefOcclusionCulling(pcd_path=REF_PCD)
+        assert oc.n == len(etihad[0]) and oc.original_voxels == 2759.0
+        oc.close()
+
+
+def test_visible_and_survivor_lists_verbatim(ref_oc, oracle_mod, etihad, space_2p5):
+    """extractVisibleSurface (occlusion_culling.cpp:265-373): FrustumCloud and the returned cloud, as index lists."""
+    o = oracle_mod.Oracle(etihad[0])
+    checked = 0
+    for k in list(range(0, 1225, 9)):
+        for cam in ("cam0", "cam1"):
+            s, v = ref_oc.extract(space_2p5[cam][k])
+            r = o.eval_view(space_2p5[cam][k], memo=False)
+            assert np.array_equal(s, r["survivors"]), (k, cam)
+            assert np.array_equal(v, r["visible"]), (k, cam)
+            checked += len(v)
+    assert checked > 50000
+
+
+@pytest.mark.parametrize("which", ["2p5", "1p5"])
+def test_every_fixture_view_counts_and_set_hashes(ref_oc, oracle_mod, etihad, space_2p5, space_1p5, which):
+    """All 2 x 1 225 (cscpp/txt) and 2 x 17 583 (sspp/resources) sensor poses of config 1: survivor count, visible
+    count and the 64-bit hash of the visible index set, reference object vs oracle (literal per-point loop)."""
+    sp = space_2p5 if which == "2p5" else space_1p5
+    poses = np.concatenate([sp["cam0"], sp["cam1"]])
+    st_ref = ref_oc.eval_batch(poses)
+    o = oracle_mod.Oracle(etihad[0])
+    st = o.eval_batch(poses, memo=False, nthreads=NTHREADS)
+    assert np.array_equal(st_ref[:, 0], st[:, oracle_mod.ST_SURVIVORS])
+    assert np.array_equal(st_ref[:, 1], st[:, oracle_mod.ST_VISIBLE])
+    assert np.array_equal(st_ref[:, 2].astype(np.uint64), st[:, oracle_mod.ST_HASH].astype(np.uint64))
+    assert int(st_ref[:, 1].sum()) > 100000
+
+
+def test_coverage_percent_and_accuracy(ref_oc, oracle_mod, etihad, space_2p5):
+    """calcCoveragePercent (:375-444) float32-equal; calcAvgAccuracy both overloads (:445-475) double-equal (same
+    left-to-right sums); pointCloudViewportTransform (:538-618) float32-equal."""
+    o = oracle_mod.Oracle(etihad[0])
+    xyz = etihad[0]
+    for k in (600, 610, 633, 700, 815):
+        pose = space_2p5["cam0"][k]
+        vis = o.eval_view(pose)["visible"]
+        if len(vis) == 0:
+            continue
+        assert np.float32(ref_oc.coverage_percent_idx(vis)) == np.float32(o.coverage_percent_idx(vis))
+        sd, sz, lo, hi = o.accuracy_idx(pose, vis)
+        a_pose, a_z = ref_oc.avg_accuracy_idx(pose, vis)
+        assert a_pose == sd / len(vis) and a_z == sz / len(vis)
+        t_ref = ref_oc.viewport_transform(pose, xyz[vis])
+        t_orc = oracle_mod.viewport_transform(pose, xyz[vis])
+        assert np.array_equal(t_ref, t_orc)
+
+
+def test_robot2sensor(R, oracle_mod, space_2p5):
+    """Sensors::robot2sensorTransformation (sspp/src/sensors.cpp:47-90), the demo's two mounts."""
+    mounts = (((0.0, 0.022, 0.065), (0.0, -0.349, 0.0)), ((0.0, 0.022, -0.065), (0.0, 0.349, 0.0)))
+    for k in range(0, 1225, 37):
+        for off, rpy in mounts:
+            # the reference keeps the mount in float32 (Eigen::Vector3f, sensors.h:60); hand the oracle the same values
+            off32 = np.asarray(off, np.float32).astype(np.float64)
+            rpy32 = np.asarray(rpy, np.float32).astype(np.float64)
+            a = R.robot2sensor(space_2p5["uav"][k], off, rpy)
+            b = oracle_mod.robot2sensor(space_2p5["uav"][k], off32, rpy32)
+            assert np.array_equal(a, b), (k, a, b)
+
+
+def test_synthetic_fine_grid(R, oracle_mod):
+    """leaf 0.05 m on a synthetic structure (the grid of configs 3 and 5): voxelRes is a public member the per-view grid
+    reads (occlusion_culling.cpp:305)."""
+    import ctypes
+    L = ctypes.CDLL(os.path.join(ROOT, "asscpp_b200", "lib", "libasscpp_host.so"))
+    L.asscpp_synth_structure_v1.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int64, ctypes.c_void_p]
+    L.asscpp_synth_views_v1.argtypes = [ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int64, ctypes.c_void_p]
+    xyz = np.empty((300000, 3), np.float32)
+    poses = np.empty((48, 7), np.float64)
+    assert L.asscpp_synth_structure_v1(0xA55C0001, 0xA55C0002, len(xyz), xyz.ctypes.data) == 0
+    assert L.asscpp_synth_views_v1(0xA55C0001, 0xA55C0003, len(poses), poses.ctypes.data) == 0
+    for leaf in (0.05, 0.2):
+        oc = R.RefOcclusionCulling(xyz=xyz, leaf=leaf, nthreads=min(NTHREADS, 8))
+        st_ref = oc.eval_batch(poses)
+        oc.close()
+        st = oracle_mod.Oracle(xyz, oracle_mod.make_params(leaf=leaf)).eval_batch(poses, memo=False, nthreads=NTHREADS)
+        assert np.array_equal(st_ref[:, 0], st[:, oracle_mod.ST_SURVIVORS])
+        assert np.array_equal(st_ref[:, 1], st[:, oracle_mod.ST_VISIBLE])
+        assert np.array_equal(st_ref[:, 2].astype(np.uint64), st[:, oracle_mod.ST_HASH].astype(np.uint64))
+        assert int(st_ref[:, 1].sum()) > 1000
