@@ -125,3 +125,30 @@ def test_synthetic_fine_grid(R, oracle_mod):
         assert np.array_equal(st_ref[:, 1], st[:, oracle_mod.ST_VISIBLE])
         assert np.array_equal(st_ref[:, 2].astype(np.uint64), st[:, oracle_mod.ST_HASH].astype(np.uint64))
         assert int(st_ref[:, 1].sum()) > 1000
+
+
+def test_first_sampling_stage_of_the_shipped_run_is_reproduced(R):
+    """The one output of the reference's own run that ships with it (cscpp/txt/..._dsscpp.txt, written at
+    coverage_heuristic_test.cpp:167-181): its first sampling stage -- generateRegularGrid + mesh filters + "sensors see
+    more than 5 points" (pathplanner.cpp:106-201, heuristic.cpp:317-364) -- is reproduced row for row by the reference's
+    own planner code running on the compiled reference; the only rows the run adds are the earliest ones, which the
+    file lost where it is truncated.  tools/reproduce_dsscpp.py has the derivation of the grid and the full report."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import reproduce_dsscpp as D
+    if not os.path.exists(D.FILE):
+        pytest.skip("/root/reference is not mounted")
+    rows = D.load_file()
+    k = D.first_stage_block(rows)
+    assert len(rows) - k == 302
+    size = [D.UPPER[c] - D.LOWER[c] + 1.0 for c in range(3)]
+    start = [D.LOWER[c] + size[c] / 2 for c in range(3)]
+    p = R.RefPlanner(D.OBJ, D.PCD, heuristic_type=0)
+    p.regular_grid(start, size, 3.0)
+    got, _, _ = p.search_space()
+    p.close()
+    have = set(D.key(r) for r in got)
+    missing = [r for r in rows[k:] if D.key(r) not in have]
+    assert not missing, "rows of the file the run does not accept: %s" % missing[:5]
+    before, after = D.extras_vs_truncation(got, rows)
+    assert after == 0 and before == len(got) - 302
