@@ -18,6 +18,9 @@ r = ctx.eval_batch(poses, flags=A.EVAL_HASH | A.EVAL_ACCURACY)
 s = ctx.new_set()
 s.or_views(poses[:20], 5)
 k = ctx.eval_groups(poses, 2, covered=s)
+acc = ctx.new_set()
+n = ctx.eval_ex(poses, covered=s, accum=acc, accum_min_visible=5)
+gp, gv = ctx.gains(n)
 ids, ctr = s.uncovered()
 lab, cl = s.uncovered_clusters(0.8, 5, 50000)
 b = ctx.eval_batch(poses[:16], flags=A.EVAL_BRUTE | A.EVAL_FORCE_GLOBAL)
