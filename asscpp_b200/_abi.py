@@ -114,6 +114,7 @@ SYMBOLS = [
     "asscpp_uncovered_voxels", "asscpp_uncovered_clusters",
     "asscpp_eval_groups", "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
     "asscpp_mesh_last_error", "asscpp_mesh_filter", "asscpp_mesh_segments_free",
+    "asscpp_covered_or_cloud", "asscpp_covered_invert_voxels",
     "asscpp_eval_ex", "asscpp_allgather_gain", "asscpp_collective_ms", "asscpp_robot2sensor_batch",
 ]
 
@@ -193,6 +194,8 @@ def load():
         "asscpp_mesh_segments_free": (i32, [vp, f64p, f64p, i64, u8p]),
         "asscpp_uncovered_voxels": (i32, [vp, i32, i32p, f32p, i64, i64p]),
         "asscpp_uncovered_clusters": (i32, [vp, i32, C.c_double, C.c_int32, C.c_int32, i32p, vp, i64, i64p]),
+        "asscpp_covered_or_cloud": (i32, [vp, i32, f32p, i64]),
+        "asscpp_covered_invert_voxels": (i32, [vp, i32]),
         "asscpp_eval_ex": (i32, [vp, vp, i64, C.POINTER(EvalOpts)]),
         "asscpp_allgather_gain": (i32, [vp, i64, u32p, u32p]),
         "asscpp_collective_ms": (i32, [vp, f32p, i64p, f32p, i64p]),

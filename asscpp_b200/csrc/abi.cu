@@ -810,6 +810,36 @@ int asscpp_coverage_percent_cloud(AsscppCtx* c, const float* xyz, int64_t n, flo
   return ASSCPP_OK;
 }
 
+int asscpp_covered_or_cloud(AsscppCtx* c, int set, const float* xyz, int64_t n) {
+  if (!c || !valid_set(c, set) || (!xyz && n > 0) || n < 0) return ASSCPP_EINVAL;
+  if (n == 0) return ASSCPP_OK;
+  cudaSetDevice(c->device);
+  if (n > c->cloud_cap) {
+    CU(c, cudaStreamSynchronize(c->stream));
+    cudaFree(c->d_cloud);
+    c->d_cloud = nullptr; c->cloud_cap = 0;
+    int rc = dev_alloc(c, &c->d_cloud, 3 * n, false);
+    if (rc) return rc;
+    c->cloud_cap = n;
+  }
+  CU(c, cudaMemcpyAsync(c->d_cloud, xyz, (size_t)n * 12, cudaMemcpyHostToDevice, c->stream));
+  launch_cloud_cover(c->d_cloud, n, 1.0f / c->params.cov_leaf, c->cov_min_b, c->cov_div, c->d_cov_keys, c->cov_keys_n,
+                     set_dev(c, set).vox, c->stream);
+  c->launches += 1;
+  CU(c, cudaGetLastError());
+  CU(c, cudaStreamSynchronize(c->stream));  // xyz may be pageable and reused by the caller
+  return ASSCPP_OK;
+}
+
+int asscpp_covered_invert_voxels(AsscppCtx* c, int set) {
+  if (!c || !valid_set(c, set)) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  launch_invert_bits(set_dev(c, set).vox, c->m.n_cov, c->stream);
+  c->launches += 1;
+  CU(c, cudaGetLastError());
+  return ASSCPP_OK;
+}
+
 int asscpp_get_visible(AsscppCtx* c, const double pose[7], int32_t* idx_out, int64_t cap, int64_t* n_out) {
   if (!c || !pose || !n_out || cap < 0 || (!idx_out && cap > 0)) return ASSCPP_EINVAL;
   cudaSetDevice(c->device);

@@ -1736,6 +1736,16 @@ __global__ void cloud_cover_kernel(const float* __restrict__ xyz, int64_t n, flo
   }
 }
 
+// flip the first nbits bits (the model's coverage voxels); the padding bits of the last word stay zero
+__global__ void invert_bits_kernel(uint32_t* __restrict__ bits, int64_t nbits) {
+  const int64_t words = (nbits + 31) / 32;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < words; w += (int64_t)gridDim.x * blockDim.x) {
+    uint32_t mask = 0xffffffffu;
+    if (w == words - 1 && (nbits & 31)) mask = (1u << (nbits & 31)) - 1u;
+    bits[w] = (~bits[w]) & mask;
+  }
+}
+
 __global__ void fill_bytes_kernel(uint8_t* p, int64_t n, uint8_t v) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
@@ -1794,6 +1804,9 @@ void launch_cloud_cover(const float* xyz, int64_t n, float inv_cov, const int32_
     cloud_cover_kernel<<<blocks_for(n, 256, 1184), 256, 0, s>>>(xyz, n, inv_cov, make_int3(cmin[0], cmin[1], cmin[2]),
                                                                 make_int3(cdiv[0], cdiv[1], cdiv[2]),
                                                                 (const long long*)keys, nkeys, marks);
+}
+void launch_invert_bits(uint32_t* bits, int64_t nbits, cudaStream_t s) {
+  if (nbits > 0) invert_bits_kernel<<<blocks_for((nbits + 31) / 32, 256, 1184), 256, 0, s>>>(bits, nbits);
 }
 void launch_fill_bytes(uint8_t* p, int64_t n, uint8_t v, cudaStream_t s) {
   if (n > 0) fill_bytes_kernel<<<blocks_for(n, 256, 1184), 256, 0, s>>>(p, n, v);

@@ -29,6 +29,7 @@ void launch_uncovered(const uint32_t* vox_bits, int64_t n_cov, int32_t* wcount, 
 void launch_clusters(const uint32_t* vox_bits, int64_t n_cov, const int64_t* keys, const int32_t cmin[3],
                      const int32_t cdiv[3], const int3* offs, int noffs, int32_t* parent, int32_t* root, int32_t* size,
                      int32_t* box, cudaStream_t s);
+void launch_invert_bits(uint32_t* bits, int64_t nbits, cudaStream_t s);
 void launch_fill_bytes(uint8_t* p, int64_t n, uint8_t v, cudaStream_t s);
 
 }  // namespace asscpp

@@ -179,6 +179,12 @@ int asscpp_covered_or_set(AsscppCtx* ctx, int dst, int src);
  * (heuristic.cpp:344-346: "if(pts.size()>5) globalCloud += pts"; use -1 to take every view) */
 int asscpp_covered_or_views(AsscppCtx* ctx, int set, const double* poses, int64_t nviews, int64_t min_visible);
 int asscpp_covered_or_points(AsscppCtx* ctx, int set, const int32_t* idx, int64_t n); /* original indices */
+/* coverage voxels of an arbitrary cloud (n x xyz float32, host), as calcCoveragePercent / pointCloudDiff voxelise it
+ * (occlusion_culling.cpp:387-428, heuristic.cpp:92-96): OR-ed into the set's voxel bits; point bits are not touched */
+int asscpp_covered_or_cloud(AsscppCtx* ctx, int set, const float* xyz, int64_t n);
+/* complement of the voxel bits over the model's coverage voxels (to cluster the voxels OF a cloud instead of the
+ * voxels a set lacks: clusteringPointCloud is handed the uncovered cloud itself, heuristic.cpp:147) */
+int asscpp_covered_invert_voxels(AsscppCtx* ctx, int set);
 int asscpp_covered_popcount(AsscppCtx* ctx, int set, int64_t* n_points, int64_t* n_voxels);
 /* host bitsets, bit i of 64-bit word i/64: points in ORIGINAL index order; voxels by compact id
  * (ascending k,j,i order of the model's coverage grid) */
