@@ -7,21 +7,27 @@
 //     pcl::PointCloud<pcl::PointXYZ> extractVisibleSurface(geometry_msgs::Pose)   (:82,  .cpp:265-373)
 //     float calcCoveragePercent(pcl::PointCloud<pcl::PointXYZ>::Ptr)              (:84,  .cpp:375-444)
 // plus non-breaking batched entry points used by the viewpoint batcher.  With real ROS/PCL headers on
-// the include path the same source builds against them; otherwise the stand-ins under compat/ are used
-// and the two ros::NodeHandle constructors are not declared.
+// the include path the same source builds against them; otherwise the stand-ins under compat/ are used.
+// All four constructors of the reference are there (occlusion_culling.h:77-80).
 //
 // There is no CPU fallback: construction throws std::runtime_error when no sm_100 GPU is usable.
 #pragma once
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <stdexcept>
 #include <string>
 #include <vector>
 
+#include <ros/ros.h>
+#include <geometry_msgs/Point32.h>
 #include <geometry_msgs/Pose.h>
 #include <geometry_msgs/PoseArray.h>
 #include <pcl/io/pcd_io.h>
 #include <pcl/point_types.h>
+#include <tf/tf.h>
+#include <visualization_msgs/Marker.h>
+#include <visualization_msgs/MarkerArray.h>
 
 #include "../asscpp_gpu.h"
 
@@ -44,6 +50,26 @@ class OcclusionCulling {
   // (occlusion_culling.cpp:363).  Kept on by default for fidelity; the batcher turns it off.
   bool accumulateOcclusionFreeCloud;
 
+  ros::NodeHandle nh;
+  ros::Publisher fov_pub;
+  // occlusion_culling.cpp:26-79: modelName is the full path of the PCD file (coverage_path_planning_heuristic.cpp:32)
+  OcclusionCulling(ros::NodeHandle& n, std::string modelName) : model(modelName), nh(n) {
+    init_members();
+    pcl::io::loadPCDFile<pcl::PointXYZ>(model, *cloud);
+    finish_init(device_from_env());
+  }
+  // occlusion_culling.cpp:81-135
+  OcclusionCulling(ros::NodeHandle& n, pcl::PointCloud<pcl::PointXYZ>::Ptr& cloudPtr) : nh(n) {
+    init_members();
+    cloud->points = cloudPtr->points;  // :94 copies only ->points: cloud->sensor_origin_ stays zero
+    finish_init(device_from_env());
+  }
+  // occlusion_culling.cpp:190-: the reference's default constructor loads a hard-coded scene file of another package
+  // ("scaled_desktop.pcd" under component_test); here it makes an object over an empty cloud
+  OcclusionCulling() {
+    init_members();
+    finish_init(device_from_env());
+  }
   explicit OcclusionCulling(std::string modelName, int device = 0) : model(modelName) {
     init_members();
     pcl::io::loadPCDFile(model, *cloud);  // occlusion_culling.cpp:39 (a missing file yields an empty cloud)
@@ -143,6 +169,37 @@ class OcclusionCulling {
     AccuracyMaxSet = true;
   }
 
+  // occlusion_culling.cpp:521-531
+  void transformPointMatVec(tf::Vector3 translation, tf::Matrix3x3 rotation, geometry_msgs::Point32 in,
+                            geometry_msgs::Point32& out) {
+    double x = rotation[0].x() * in.x + rotation[0].y() * in.y + rotation[0].z() * in.z + translation.x();
+    double y = rotation[1].x() * in.x + rotation[1].y() * in.y + rotation[1].z() * in.z + translation.y();
+    double z = rotation[2].x() * in.x + rotation[2].y() * in.y + rotation[2].z() * in.z + translation.z();
+    out.x = x; out.y = y; out.z = z;
+  }
+  // occlusion_culling.cpp:244-252
+  bool contains(pcl::PointCloud<pcl::PointXYZ> c, pcl::PointXYZ p) {
+    for (size_t i = 0; i < c.points.size(); ++i)
+      if (c.points[i].x == p.x && c.points[i].y == p.y && c.points[i].z == p.z) return true;
+    return false;
+  }
+  // occlusion_culling.cpp:254-263: points of the model cloud that are not in c2
+  pcl::PointCloud<pcl::PointXYZ> pointsDifference(pcl::PointCloud<pcl::PointXYZ> c2) {
+    pcl::PointCloud<pcl::PointXYZ> inter;
+    for (size_t i = 0; i < cloud->points.size(); ++i)
+      if (!contains(c2, cloud->points[i])) inter.push_back(cloud->points[i]);
+    return inter;
+  }
+  // occlusion_culling.cpp:622-718: RViz markers of the frustum.  Unavailable on this box (no graphics stack): the
+  // methods exist so that callers compile and link; they publish nothing.
+  void visualizeFOV(geometry_msgs::Pose) {}
+  visualization_msgs::Marker drawLines(std::vector<geometry_msgs::Point> links, int id_, int[]) {
+    visualization_msgs::Marker m;
+    m.id = id_;
+    m.points = links;
+    return m;
+  }
+
   // ---- additions (non-breaking) -----------------------------------------------------------------
   // ascending original indices of extractVisibleSurface's cloud
   void visibleIndices(const geometry_msgs::Pose& location, std::vector<int32_t>& idx) {
@@ -168,6 +225,10 @@ class OcclusionCulling {
     }
   }
   AsscppCtx* context() { return ctx_; }
+  static int device_from_env() {  // the reference's constructors have no device argument: ASSCPP_DEVICE picks the GPU
+    const char* e = std::getenv("ASSCPP_DEVICE");
+    return e ? std::atoi(e) : 0;
+  }
   static void pack(const geometry_msgs::Pose& q, double p[7]) {
     p[0] = q.position.x; p[1] = q.position.y; p[2] = q.position.z;
     p[3] = q.orientation.x; p[4] = q.orientation.y; p[5] = q.orientation.z; p[6] = q.orientation.w;

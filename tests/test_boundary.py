@@ -1,0 +1,166 @@
+"""The drop-in boundary, verbatim: class SSPP::CoveragePathPlanningHeuristic : public SSPP::Heuristic
+(include/cscpp/coverage_path_planning_heuristic_b200.h) under the reference's OWN callers.
+
+oracle/_ref/ref_sspp_driver is the reference's sspp sources (astar.cpp, pathplanner.cpp, llist.cpp, node.cpp, searchspace.cpp,
+sensors.cpp ... compiled unmodified from /root/reference) linked against this repository's plugin class and C-ABI
+library.  The GPU tests run it and compare with the same planners driving the reference's own CPU heuristic and
+OcclusionCulling (oracle/_ref/libasscpp_ref.so): same accepted samples, same search path, same coverage and f values.
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT
+
+DRIVER = os.path.join(ROOT, "oracle", "_ref", "ref_sspp_driver")
+REF_SSPP = "/root/reference/sspp/include"
+TU = '#include <cscpp/coverage_path_planning_heuristic_b200.h>\n' \
+     'int main() { SSPP::Heuristic* h = 0; (void)h; return sizeof(SSPP::CoveragePathPlanningHeuristic) > 0 ? 0 : 1; }\n'
+
+
+def test_plugin_compiles_against_the_reference_interface(tmp_path):
+    """The class overrides all ten pure virtuals of sspp/include/sspp/heuristic_interface.h:35-56 at the reference's
+    signatures: it is instantiable (sizeof + constructor odr-use) against the reference's own header when that is
+    mounted, and against the compat/sspp stand-in always."""
+    src = tmp_path / "tu.cpp"
+    src.write_text(TU + "SSPP::CoveragePathPlanningHeuristic* make(ros::NodeHandle& nh) { return new "
+                        "SSPP::CoveragePathPlanningHeuristic(nh, \"a.obj\", \"a.pcd\", false, false, SurfaceCoverageH); }\n")
+    inc = ["-I" + os.path.join(ROOT, "compat"), "-I" + os.path.join(ROOT, "include")]
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-fsyntax-only"] + inc + [str(src)])
+    if os.path.isdir(REF_SSPP):
+        ref_inc = ["-I" + REF_SSPP, "-I" + os.path.join(REF_SSPP, "sspp")]
+        subprocess.check_call(["g++", "-std=c++11", "-w", "-fsyntax-only"] + ref_inc + inc + [str(src)])
+
+
+def test_shim_declares_every_reference_constructor_and_method():
+    """cscpp/include/cscpp/occlusion_culling.h:77-94"""
+    text = open(os.path.join(ROOT, "include", "cscpp", "occlusion_culling_b200.h")).read()
+    for sig in ("OcclusionCulling(ros::NodeHandle& n, std::string modelName)",
+                "OcclusionCulling(ros::NodeHandle& n, pcl::PointCloud<pcl::PointXYZ>::Ptr& cloudPtr)", "OcclusionCulling()",
+                "extractVisibleSurface(geometry_msgs::Pose", "calcCoveragePercent(pcl::PointCloud<pcl::PointXYZ>::Ptr",
+                "calcAvgAccuracy(pcl::PointCloud<pcl::PointXYZ> pointCloud)", "transformPointMatVec(", "pointCloudViewportTransform(",
+                "SSMaxMinAccuracy(", "visualizeFOV(", "drawLines(", "contains(", "pointsDifference("):
+        assert sig in text, sig
+
+
+def build_driver():
+    if os.path.isdir(REF_SSPP):
+        subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle"), "-j8", "driver"], stdout=subprocess.DEVNULL)
+    if not os.path.exists(DRIVER):
+        pytest.skip("oracle/_ref/ref_sspp_driver is not built and /root/reference is not mounted")
+    return DRIVER
+
+
+def test_driver_links_reference_planners_against_the_plugin(lib_built):
+    exe = build_driver()
+    out = subprocess.run([exe], capture_output=True, text=True)
+    assert out.returncode == 2 and "usage" in out.stderr
+
+
+# ---- model files written from the committed fixtures (the GPU box has no /root/reference) ---------------------------
+def write_model(tmp, xyz):
+    pcd, obj = str(tmp / "model.pcd"), str(tmp / "model.obj")
+    with open(pcd, "wb") as f:
+        f.write(("# .PCD v0.7\nVERSION 0.7\nFIELDS x y z\nSIZE 4 4 4\nTYPE F F F\nCOUNT 1 1 1\nWIDTH %d\nHEIGHT 1\n"
+                 "VIEWPOINT 0 0 0 0 0.5 0 0\nPOINTS %d\nDATA binary\n" % (len(xyz), len(xyz))).encode())
+        f.write(np.ascontiguousarray(xyz, "<f4").tobytes())
+    g = np.load(os.path.join(GOLDEN, "etihad_mesh.npz"))
+    with open(obj, "w") as f:
+        for v in g["vertices"]:
+            f.write("v %.9g %.9g %.9g\n" % tuple(v))
+        for t in g["triangles"]:
+            f.write("f %d %d %d\n" % tuple(t + 1))
+    return pcd, obj
+
+
+def write_space(tmp, sp):
+    names = []
+    for key in ("uav", "cam0", "cam1"):
+        p = str(tmp / (key + ".txt"))
+        np.savetxt(p, sp[key], fmt="%.17g")
+        names.append(p)
+    return names
+
+
+def parse(out, tag):
+    return np.array([[float(x) for x in ln.split()[1:]] for ln in out.splitlines() if ln.startswith(tag + " ")])
+
+
+@pytest.fixture(scope="module")
+def R():
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("oracle/_ref is not built and /root/reference is not mounted")
+    ref.build()
+    return ref
+
+
+@pytest.mark.gpu
+def test_first_sampling_stage_gpu_plugin_equals_reference_heuristic(tmp_path, lib_built, R, etihad):
+    """PathPlanner::generateRegularGrid (pathplanner.cpp:106-201) calling isFilteringConditionSatisfied once per
+    candidate: the plugin on the GPU accepts exactly the samples the reference's CPU heuristic accepts, in the same
+    order (the stage-1 grid of the shipped _dsscpp.txt run, tools/reproduce_dsscpp.py)."""
+    exe = build_driver()
+    pcd, obj = write_model(tmp_path, etihad[0])
+    g = np.load(os.path.join(GOLDEN, "dsscpp_reference_run.npz"))
+    start, size = g["grid_start"], g["grid_size"]
+    out = subprocess.run([exe, "grid", pcd, obj] + ["%.17g" % v for v in list(start) + list(size)] + ["3.0"],
+                         capture_output=True, text=True, timeout=1800)
+    assert out.returncode == 0, out.stderr[-2000:]
+    rows = parse(out.stdout, "ROW")
+    p = R.RefPlanner(obj, pcd, heuristic_type=0)
+    p.regular_grid(start, size, 3.0)
+    want, _, _ = p.search_space()
+    p.close()
+    assert len(rows) == len(want) == 335
+    assert np.array_equal(rows, want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("htype,batch", [(0, 0), (0, 1), (1, 1), (2, 1), (4, 1)])
+def test_reference_astar_over_gpu_plugin_equals_reference_heuristic(tmp_path, lib_built, R, etihad, space_2p5, htype, batch):
+    """Astar::astarSearch (astar.cpp:220-373), unmodified, scoring children through the plugin -- one child per call
+    (batch 0) or with the one-line batcher hook (batch 1: one launch per expansion) -- against the same search driven
+    by the reference's CPU heuristic: same path, coverage, f value and distance at every node.  Types:
+    SurfaceCoverageH, ...withOrientationH, ...withAccuracyH, VolumetricCoverageH."""
+    exe = build_driver()
+    pcd, obj = write_model(tmp_path, etihad[0])
+    files = write_space(tmp_path, space_2p5)
+    out = subprocess.run([exe, "astar", pcd, obj] + files + [str(htype), "5.0", "1.0", str(batch)], capture_output=True,
+                         text=True, timeout=1800)
+    assert out.returncode == 0, out.stderr[-2000:]
+    path = parse(out.stdout, "NODE")
+    launches = [ln for ln in out.stdout.splitlines() if ln.startswith("LAUNCHES")][0].split()
+    p = R.RefPlanner(obj, pcd, heuristic_type=htype, target=5.0, tolerance=1.0, conn_radius=2.5)
+    p.load_grid(*files)
+    if htype in (2, 4):
+        p.set_accuracy_range()
+    want = p.search()
+    ncon = p.num_connections()
+    p.close()
+    assert int(out.stdout.split("PATH")[1].split()[1]) == ncon
+    assert len(path) == len(want) and len(path) >= 2
+    assert np.array_equal(path[:, :7], want[:, :7])                       # same waypoints in the same order
+    assert np.array_equal(path[:, 7].astype(np.float32), want[:, 7].astype(np.float32)) or np.array_equal(path[:, 7], want[:, 7])
+    assert np.allclose(path[:, 8], want[:, 8], rtol=1e-12, atol=0) and np.array_equal(path[:, 9], want[:, 9])
+    if batch:
+        assert int(launches[1]) < int(launches[3])  # fewer launches than nodes scored: the batcher is on
+
+
+@pytest.mark.gpu
+def test_adaptive_sampling_loop_gpu_plugin_equals_reference_run(tmp_path, lib_built, etihad):
+    """PathPlanner::dynamicNodesGenerationAndConnection (pathplanner.cpp:729-850), unmodified, over the plugin: the
+    whole adaptive loop (two stages, clustering of the uncovered part, cluster boxes, connections) ends with the search
+    space the reference's own CPU heuristic produced (tests/golden/dsscpp_reference_run.npz, made by
+    tools/reproduce_dsscpp.py on the compiled reference)."""
+    exe = build_driver()
+    pcd, obj = write_model(tmp_path, etihad[0])
+    g = np.load(os.path.join(GOLDEN, "dsscpp_reference_run.npz"))
+    out = subprocess.run([exe, "dynamic", pcd, obj] + ["%.17g" % v for v in list(g["grid_start"]) + list(g["grid_size"])]
+                         + ["3.0", "1.5"], capture_output=True, text=True, timeout=3000)
+    assert out.returncode == 0, out.stderr[-2000:]
+    rows = parse(out.stdout, "ROW")
+    assert len(rows) == len(g["rows"])
+    assert np.array_equal(rows, g["rows"])
