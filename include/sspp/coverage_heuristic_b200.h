@@ -47,6 +47,8 @@ class ViewpointBatcher {
         OcclusionCulling::pack(children[i]->senPoses[s], &p[p.size() - 7]);
         owner.push_back(std::make_pair(children[i]->id, (int)s));
       }
+    cache_.clear();  // results of an earlier expansion were scored against another set (and handle ids are recycled)
+    parent_set_ = -2;
     if (owner.empty() || per == 0) return;
     oc_->check(asscpp_eval_groups(oc_->context(), p.data(), (int64_t)owner.size(), (int)per, parent_set, 0));
     std::vector<AsscppViewResult> res(owner.size());
@@ -89,9 +91,23 @@ enum { SurfaceCoverageH = 0, SurfaceCoveragewithOrientationH = 1, SurfaceCoverag
 
 class CoverageHeuristicB200 {
  public:
+  // accumulate = false (default) is what the reference's A* computes: Astar copies the node it pops (astar.cpp:262) and
+  // Node::Node(Node*) gives the copy an empty cloud_filtered (node.cpp:43-68), so every child is scored against the
+  // EMPTY set and node->coverage is that of its own views, while c still subtracts the parent's number (quirk Q10).
+  // accumulate = true is the evidently intended behaviour: the parent's covered set is carried along the path.
+  // The verbatim drop-in (class SSPP::CoveragePathPlanningHeuristic, include/cscpp/coverage_path_planning_heuristic_b200.h)
+  // reads node->parent->cloud_filtered like the reference and so behaves either way depending on the caller.
   CoverageHeuristicB200(OcclusionCulling* oc, double coverageTarget, double coverageTolerance,
-                        int heuristicType = SurfaceCoverageH)
-      : oc_(oc), batcher_(oc), target_(coverageTarget), tol_(coverageTolerance), type_(heuristicType) {}
+                        int heuristicType = SurfaceCoverageH, bool accumulate = false)
+      : oc_(oc), batcher_(oc), target_(coverageTarget), tol_(coverageTolerance), type_(heuristicType),
+        accumulate_(accumulate) {}
+  bool accumulate() const { return accumulate_; }
+  // the set the children of `parent` are scored against (pass it to batcher().prefetch)
+  int scoringSet(const NodeB200* parent) const { return accumulate_ && parent ? parent->covered_set : -1; }
+  // free the device set of a node that is discarded (closed-list clean-up)
+  void release(NodeB200* node) {
+    if (node && node->covered_set >= 0) { asscpp_covered_free(oc_->context(), node->covered_set); node->covered_set = -1; }
+  }
 
   // setMaxMinSensorAccuracy (coverage_path_planning_heuristic.cpp:399-403): needed before SurfaceCoveragewithAccuracyH
   void setMaxMinSensorAccuracy(std::vector<geometry_msgs::PoseArray> sensorsViewsSS) {
@@ -111,8 +127,8 @@ class CoverageHeuristicB200 {
     // no launch here, and the child's covered set is only made if the node is expanded later (ensureSet)
     unsigned long long cachedGain = 0;
     const bool cached = node->parent && type_ != SurfaceCoveragewithAccuracyH && type_ != VolumetricCoverageH &&
-                        node->covered_set < 0 &&
-                        node->parent->covered_set >= 0 && batcher_.groupGain(node, node->parent->covered_set, &cachedGain);
+                        node->covered_set < 0 && (!accumulate_ || node->parent->covered_set >= 0) &&
+                        batcher_.groupGain(node, scoringSet(node->parent), &cachedGain);
     if (!cached) ensureSet(node);
     double a = 1.0;
     if ((type_ == SurfaceCoveragewithAccuracyH || type_ == VolumetricCoverageH) && node->parent) {
@@ -132,7 +148,7 @@ class CoverageHeuristicB200 {
     float pct = 0;
     if (cached) {
       int64_t npts = 0, nvox = 0;
-      oc_->check(asscpp_covered_popcount(c, node->parent->covered_set, &npts, &nvox));
+      if (accumulate_) oc_->check(asscpp_covered_popcount(c, node->parent->covered_set, &npts, &nvox));
       AsscppModelInfo info;
       asscpp_model_info(c, &info);
       pct = (float)(nvox + (int64_t)cachedGain) / (float)info.n_cov_voxels * 100.0f;  // occlusion_culling.cpp:431-432
@@ -150,7 +166,7 @@ class CoverageHeuristicB200 {
       oc_->check(asscpp_covered_popcount(c, node->covered_set, &npts, &nvox));
       node->coverage = ((double)nvox / (double)info.n_cov_voxels) * 100;  // :629
       if (node->parent) {
-        oc_->check(asscpp_covered_popcount(c, node->parent->covered_set, &npts, &pvox));
+        if (accumulate_) oc_->check(asscpp_covered_popcount(c, node->parent->covered_set, &npts, &pvox));
         const double dx = node->pose.position.x - node->parent->pose.position.x,
                      dy = node->pose.position.y - node->parent->pose.position.y,
                      dz = node->pose.position.z - node->parent->pose.position.z;
@@ -215,7 +231,7 @@ class CoverageHeuristicB200 {
   void ensureSet(NodeB200* node) {
     if (node->covered_set >= 0) return;
     AsscppCtx* c = oc_->context();
-    if (node->parent) {
+    if (node->parent && accumulate_) {
       ensureSet(node->parent);
       oc_->check(asscpp_covered_clone(c, node->parent->covered_set, &node->covered_set));  // :473 parent's cloud
     } else {
@@ -358,6 +374,7 @@ class CoverageHeuristicB200 {
   ViewpointBatcher batcher_;
   double target_, tol_;
   int type_;
+  bool accumulate_;
   AsscppMesh* mesh_ = nullptr;
 };
 

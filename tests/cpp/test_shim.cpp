@@ -56,7 +56,7 @@ int main(int argc, char** argv) {
     nodes[i].senPoses.push_back(poses[2 * i]);
     nodes[i].senPoses.push_back(poses[2 * i + 1]);
   }
-  SSPP::CoverageHeuristicB200 heur(&oc, 100.0, 1.0);
+  SSPP::CoverageHeuristicB200 heur(&oc, 100.0, 1.0, SSPP::SurfaceCoverageH, true);
   std::vector<SSPP::NodeB200> path;
   path.reserve(16);
   SSPP::NodeB200 root = nodes[0];
@@ -82,6 +82,22 @@ int main(int argc, char** argv) {
     path.back().distance = 0;
   }
   std::printf("walk launches %d\n", heur.batcher().launches());
+  {
+    // 2b. the DEFAULT mode (accumulate = false, quirk Q10): one expansion from waypoint 0, children scored against the
+    // empty set through the batcher; coverage = the child's own, c = coverage - parent.coverage
+    SSPP::CoverageHeuristicB200 hq(&oc, 100.0, 1.0);
+    SSPP::NodeB200 r0 = nodes[0];
+    hq.calculateHeuristic(&r0);
+    std::vector<SSPP::NodeB200> kids(nodes.begin() + 1, nodes.end());
+    std::vector<SSPP::NodeB200*> ptrs;
+    for (size_t i = 0; i < kids.size(); ++i) { kids[i].parent = &r0; ptrs.push_back(&kids[i]); }
+    hq.batcher().prefetch(ptrs.data(), (int)ptrs.size(), hq.scoringSet(&r0));
+    for (size_t i = 0; i < kids.size(); ++i) {
+      hq.calculateHeuristic(&kids[i]);
+      std::printf("q10 %d coverage %.17g f %.17g\n", kids[i].id, kids[i].coverage, kids[i].f_value);
+    }
+    std::printf("q10 launches %d root %.17g\n", hq.batcher().launches(), r0.coverage);
+  }
   // 3. ASSCPP acceptance rule + uncovered percentage
   int global_set = -1;
   oc.check(asscpp_covered_new(oc.context(), &global_set));
@@ -114,7 +130,7 @@ int main(int argc, char** argv) {
   std::printf("ssmaxmin max %.17g min %.17g set %d\n", oc.maxAccuracyError, oc.minAccuracyError, (int)oc.AccuracyMaxSet);
   // 5. SurfaceCoveragewithAccuracyH: one expansion from waypoint 0 (heuristic.cpp:490-513)
   {
-    SSPP::CoverageHeuristicB200 hacc(&oc, 100.0, 1.0, SSPP::SurfaceCoveragewithAccuracyH);
+    SSPP::CoverageHeuristicB200 hacc(&oc, 100.0, 1.0, SSPP::SurfaceCoveragewithAccuracyH, true);
     hacc.setMaxMinSensorAccuracy(std::vector<geometry_msgs::PoseArray>(1, pa));
     SSPP::NodeB200 r0 = nodes[0];
     hacc.calculateHeuristic(&r0);
@@ -128,7 +144,7 @@ int main(int argc, char** argv) {
   }
   // 7. VolumetricCoverageH: one expansion from waypoint 0 (heuristic.cpp:581-641)
   {
-    SSPP::CoverageHeuristicB200 hv(&oc, 100.0, 1.0, SSPP::VolumetricCoverageH);
+    SSPP::CoverageHeuristicB200 hv(&oc, 100.0, 1.0, SSPP::VolumetricCoverageH, true);
     hv.setMaxMinSensorAccuracy(std::vector<geometry_msgs::PoseArray>(1, pa));
     SSPP::NodeB200 r0 = nodes[0];
     hv.calculateHeuristic(&r0);

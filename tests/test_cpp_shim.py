@@ -90,6 +90,18 @@ def test_shim_matches_oracle(tmp_path, lib_built, oracle_mod, etihad, space_2p5)
         assert float(c_s) == pytest.approx(cbest, abs=1e-6) and float(f_s) == pytest.approx(fbest, rel=1e-12, abs=1e-9)
         covered, cov, fval, cur = ubest, cbest, fbest, ibest
     assert int(re.search(r"walk launches (\d+)", out).group(1)) == 4  # one scoring launch per expansion
+    # 2b. default mode = what the reference's A* computes (quirk Q10): each child against the EMPTY set
+    q10 = re.findall(r"q10 (\d+) coverage (\S+) f (\S+)", out)
+    assert len(q10) == len(rows) - 1
+    root_cov = pct(set(vox[0].tolist()))
+    for i_s, c_s, f_s in q10:
+        i = int(i_s)
+        c = pct(set(vox[i].tolist()))
+        d = float(np.linalg.norm(pos[i] - pos[0]))
+        gain = c - root_cov
+        assert float(c_s) == pytest.approx(c, abs=0)
+        assert float(f_s) == pytest.approx((1 / d) * gain if d != 0 else gain, rel=1e-12, abs=1e-12)
+    assert int(re.search(r"q10 launches (\d+)", out).group(1)) == 1
     # 3. acceptance rule (:339-357) and uncovered percentage (:143)
     st = o.eval_batch(poses, memo=True)
     vis = st[:, O.ST_VISIBLE].reshape(-1, 2)
