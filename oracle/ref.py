@@ -56,6 +56,11 @@ def lib(path=LIB_PATH):
     L.ref_oc_avg_accuracy_idx.argtypes = [vp, f64p, i32p, i64, f64p]; L.ref_oc_avg_accuracy_idx.restype = None
     L.ref_oc_viewport_transform.argtypes = [vp, f64p, f32p, i64, f32p]; L.ref_oc_viewport_transform.restype = None
     L.ref_oc_eval_batch.argtypes = [C.POINTER(vp), C.c_int, f64p, i64, i64p]; L.ref_oc_eval_batch.restype = C.c_int
+    u64p = C.POINTER(C.c_uint64)
+    L.ref_oc_create_many.argtypes = [f32p, i64, C.c_float, C.c_int, C.POINTER(vp)]; L.ref_oc_create_many.restype = None
+    L.ref_oc_eval_batch_gain.argtypes = [C.POINTER(vp), C.c_int, f64p, i64, u64p, u64p, i32p, i64, i64p]
+    L.ref_oc_eval_batch_gain.restype = C.c_int
+    L.ref_oc_accumulate.argtypes = [vp, f64p, u64p, u64p, i32p]; L.ref_oc_accumulate.restype = C.c_int
     L.ref_robot2sensor.argtypes = [f64p, f64p, f64p, f64p]; L.ref_robot2sensor.restype = None
     L.ref_planner_create.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_double, C.c_double, C.c_double]
     L.ref_planner_create.restype = vp
@@ -81,7 +86,13 @@ class RefOcclusionCulling:
     def __init__(self, xyz=None, pcd_path=None, leaf=0.0, nthreads=1, origin=None, lib_path=LIB_PATH):
         self.L = lib(lib_path)
         self.handles = []
-        for _ in range(max(1, nthreads)):
+        if pcd_path is None and nthreads > 1:
+            a = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+            arr = (C.c_void_p * nthreads)()
+            self.L.ref_oc_create_many(_p(a, C.c_float), len(a), float(leaf), nthreads, arr)
+            self.handles = [arr[i] for i in range(nthreads)]
+            nthreads = 0
+        for _ in range(nthreads if self.handles else max(1, nthreads)):
             if pcd_path is not None:
                 h = self.L.ref_oc_create_pcd(pcd_path.encode())
             else:
@@ -126,6 +137,23 @@ class RefOcclusionCulling:
         if rc:
             raise RuntimeError("ref_oc_eval_batch failed")
         return st
+
+    def eval_batch_gain(self, poses, cov_pts, cov_vox, pt_cov, n_cov):
+        """stats [n, 5]: survivors, visible, hash, gain_pts, gain_vox against the covered bitsets (uint64 words)."""
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        st = np.zeros((len(poses), 5), np.int64)
+        arr = (C.c_void_p * len(self.handles))(*self.handles)
+        rc = self.L.ref_oc_eval_batch_gain(arr, len(self.handles), _p(poses, C.c_double), len(poses), _p(cov_pts, C.c_uint64),
+                                           _p(cov_vox, C.c_uint64), _p(pt_cov, C.c_int32), int(n_cov), _p(st, C.c_int64))
+        if rc:
+            raise RuntimeError("ref_oc_eval_batch_gain failed")
+        return st
+
+    def accumulate(self, pose, cov_pts, cov_vox, pt_cov):
+        pose = np.ascontiguousarray(pose, np.float64)
+        if self.L.ref_oc_accumulate(self.handles[0], _p(pose, C.c_double), _p(cov_pts, C.c_uint64), _p(cov_vox, C.c_uint64),
+                                    _p(pt_cov, C.c_int32)):
+            raise RuntimeError("ref_oc_accumulate failed")
 
     def coverage_percent_idx(self, idx):
         idx = np.ascontiguousarray(idx, np.int32)

@@ -10,6 +10,7 @@
 // Eigen's dot / norm and PCL's VoxelGrid binning remain stand-in choices (switchable, see compat/Eigen/Core).
 //
 // This file only adapts types: it calls the reference's public methods and turns point clouds back into index lists.
+#include <algorithm>
 #include <cstdint>
 #include <cstring>
 #include <string>
@@ -40,6 +41,18 @@ int64_t match_indices(const std::vector<pcl::PointXYZ>& all, const std::vector<p
                       int64_t cap) {
   size_t i = 0;
   int64_t k = 0;
+  uint32_t t1 = 0, t2 = 0;
+  if (all.size() > 2) { std::memcpy(&t1, &all[1].data[3], 4); std::memcpy(&t2, &all[2].data[3], 4); }
+  if (t1 == 1 && t2 == 2) {  // index-tagged cloud (ref_oc_create_points)
+    for (size_t j = 0; j < sub.size(); ++j) {
+      uint32_t t;
+      std::memcpy(&t, &sub[j].data[3], 4);
+      if (t >= all.size() || std::memcmp(all[t].data, sub[j].data, 12) != 0) return -1;
+      if (k < cap && out) out[k] = (int32_t)t;
+      ++k;
+    }
+    return k;
+  }
   for (size_t j = 0; j < sub.size(); ++j) {
     while (i < all.size() && std::memcmp(all[i].data, sub[j].data, 12) != 0) ++i;
     if (i == all.size()) return -1;
@@ -69,7 +82,13 @@ void* ref_oc_create_pcd(const char* pcd_path) { return new OcclusionCulling(g_nh
 void* ref_oc_create_points(const float* xyz, int64_t n, float leaf) {
   pcl::PointCloud<pcl::PointXYZ>::Ptr c(new pcl::PointCloud<pcl::PointXYZ>);
   c->points.resize((size_t)n);
-  for (int64_t i = 0; i < n; ++i) c->points[(size_t)i] = pcl::PointXYZ(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+  for (int64_t i = 0; i < n; ++i) {
+    c->points[(size_t)i] = pcl::PointXYZ(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+    // the padding float of PointXYZ carries the point's index (bit pattern): the reference copies whole points and
+    // computes with x, y, z only, so every cloud it returns can be read back as an index list without a search
+    const uint32_t tag = (uint32_t)i;
+    std::memcpy(&c->points[(size_t)i].data[3], &tag, 4);
+  }
   OcclusionCulling* oc = new OcclusionCulling(g_nh, c);
   if (leaf > 0) oc->voxelRes = leaf;
   return oc;
@@ -137,6 +156,66 @@ int ref_oc_eval_batch(void** handles, int nthreads, const double* poses, int64_t
     }));
   for (size_t t = 0; t < th.size(); ++t) th[t].join();
   for (int t = 0; t < nthreads; ++t) if (rc[(size_t)t]) return -1;
+  return 0;
+}
+
+// One instance per host thread, constructed concurrently (each constructor voxelises the whole model,
+// occlusion_culling.cpp:101-131).  handles: count pointers out.
+void ref_oc_create_many(const float* xyz, int64_t n, float leaf, int count, void** handles) {
+  std::vector<std::thread> th;
+  for (int t = 0; t < count; ++t) th.push_back(std::thread([&, t]() { handles[t] = ref_oc_create_points(xyz, n, leaf); }));
+  for (size_t t = 0; t < th.size(); ++t) th[t].join();
+}
+
+// ref_oc_eval_batch + the gain of every view against a running covered set in bitset form (points by original index,
+// coverage voxels by compact id; pt_cov = coverage-voxel id of every model point): the popcount form of
+// heuristic.cpp:473-483, cheaper than the reference's own re-voxelisation of the accumulated cloud per candidate.
+// stats: nviews x {survivors, visible, hash, gain_pts, gain_vox}.
+int ref_oc_eval_batch_gain(void** handles, int nthreads, const double* poses, int64_t nviews, const uint64_t* cov_pts,
+                           const uint64_t* cov_vox, const int32_t* pt_cov, int64_t n_cov, int64_t* stats) {
+  std::vector<std::thread> th;
+  std::vector<int> rc((size_t)nthreads, 0);
+  for (int t = 0; t < nthreads; ++t)
+    th.push_back(std::thread([&, t]() {
+      OcclusionCulling* oc = static_cast<OcclusionCulling*>(handles[t]);
+      std::vector<int32_t> idx(oc->cloudCopy->points.size());
+      std::vector<uint64_t> seen((size_t)(n_cov + 63) / 64);
+      for (int64_t v = t; v < nviews; v += nthreads) {
+        int64_t counts[2];
+        if (ref_oc_extract(oc, poses + 7 * v, nullptr, idx.data(), (int64_t)idx.size(), counts)) { rc[(size_t)t] = -1; return; }
+        uint64_t hsh = 0;
+        int64_t gp = 0, gv = 0;
+        std::fill(seen.begin(), seen.end(), 0);
+        for (int64_t k = 0; k < counts[1]; ++k) {
+          const uint32_t i = (uint32_t)idx[(size_t)k];
+          hsh += mix64((uint64_t)i);
+          if (!cov_pts || !((cov_pts[i >> 6] >> (i & 63)) & 1)) ++gp;
+          const uint32_t c = (uint32_t)pt_cov[i];
+          if (!((seen[c >> 6] >> (c & 63)) & 1)) {
+            seen[c >> 6] |= 1ull << (c & 63);
+            if (!cov_vox || !((cov_vox[c >> 6] >> (c & 63)) & 1)) ++gv;
+          }
+        }
+        int64_t* o = stats + 5 * v;
+        o[0] = counts[0]; o[1] = counts[1]; o[2] = (int64_t)hsh; o[3] = gp; o[4] = gv;
+      }
+    }));
+  for (size_t t = 0; t < th.size(); ++t) th[t].join();
+  for (int t = 0; t < nthreads; ++t) if (rc[(size_t)t]) return -1;
+  return 0;
+}
+
+// accept a viewpoint: OR its visible set into the covered bitsets (heuristic.cpp:344-346 / :473-480 in bitset form)
+int ref_oc_accumulate(void* h, const double pose[7], uint64_t* cov_pts, uint64_t* cov_vox, const int32_t* pt_cov) {
+  OcclusionCulling* oc = static_cast<OcclusionCulling*>(h);
+  std::vector<int32_t> idx(oc->cloudCopy->points.size());
+  int64_t counts[2];
+  if (ref_oc_extract(oc, pose, nullptr, idx.data(), (int64_t)idx.size(), counts)) return -1;
+  for (int64_t k = 0; k < counts[1]; ++k) {
+    const uint32_t i = (uint32_t)idx[(size_t)k], c = (uint32_t)pt_cov[i];
+    cov_pts[i >> 6] |= 1ull << (i & 63);
+    cov_vox[c >> 6] |= 1ull << (c & 63);
+  }
   return 0;
 }
 
