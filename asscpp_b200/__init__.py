@@ -421,3 +421,74 @@ class CoverageContext:
 
     def comm_destroy(self):
         self._ck(self.L.asscpp_comm_destroy(self.h))
+
+
+class MultiContext:
+    """One process, several GPUs (asscpp_multi_*): a context per device, batches sharded over them, covered sets
+    mirrored and kept equal by the NCCL OR-allreduce."""
+
+    def __init__(self, xyz, params=None, devices=(0,)):
+        self.L = _abi.load()
+        self.params = params or default_params()
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        dev = np.ascontiguousarray(devices, np.int32)
+        self.h = C.c_void_p()
+        rc = self.L.asscpp_multi_create(_ptr(dev, C.c_int32), len(dev), _ptr(xyz, C.c_float), xyz.shape[0],
+                                        C.byref(self.params), C.byref(self.h))
+        if rc:
+            self.h = C.c_void_p()
+            raise AsscppError(rc, (self.L.asscpp_last_error(None) or b"").decode())
+        self.ndev = self.L.asscpp_multi_num_devices(self.h)
+
+    def _ck(self, rc):
+        if rc:
+            raise AsscppError(rc, (self.L.asscpp_multi_last_error(self.h) or b"").decode())
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h.value:
+            self.L.asscpp_multi_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def new_set(self):
+        out = C.c_int()
+        self._ck(self.L.asscpp_multi_covered_new(self.h, C.byref(out)))
+        return out.value
+
+    def free_set(self, s):
+        self._ck(self.L.asscpp_multi_covered_free(self.h, s))
+
+    def popcount(self, s):
+        a, b = C.c_int64(), C.c_int64()
+        self._ck(self.L.asscpp_multi_covered_popcount(self.h, s, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def coverage_percent(self, s):
+        out = C.c_float()
+        self._ck(self.L.asscpp_multi_coverage_percent(self.h, s, C.byref(out)))
+        return out.value
+
+    def or_views(self, s, poses, min_visible=-1):
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        self._ck(self.L.asscpp_multi_covered_or_views(self.h, s, _ptr(poses, C.c_double), len(poses), min_visible))
+
+    def eval(self, poses, covered=-1, accum=-1, accum_min_visible=5, group_size=1, flags=0):
+        """(results, gain_pts, gain_vox) for all poses, evaluated on all devices."""
+        poses = np.ascontiguousarray(poses, np.float64).reshape(-1, 7)
+        o = EvalOpts(int(covered), int(accum), int(accum_min_visible), int(group_size), int(flags), 0, 0)
+        res = np.zeros(len(poses), RESULT_DTYPE)
+        gp, gv = np.zeros(len(poses), np.uint32), np.zeros(len(poses), np.uint32)
+        self._ck(self.L.asscpp_multi_eval(self.h, _ptr(poses, C.c_double), len(poses), C.byref(o),
+                                          res.ctypes.data_as(C.c_void_p), _ptr(gp, C.c_uint32), _ptr(gv, C.c_uint32)))
+        return res, gp, gv
+
+    def export_set(self, s, device_index=0):
+        """(point bits, voxel bits) of the set as device `device_index` holds it."""
+        ctx = self.L.asscpp_multi_context(self.h, device_index)
+        info = ModelInfo()
+        self.L.asscpp_model_info(C.c_void_p(ctx), C.byref(info))
+        pts = np.zeros((info.n_points + 63) // 64, np.uint64)
+        vox = np.zeros((info.n_cov_voxels + 63) // 64, np.uint64)
+        rc = self.L.asscpp_covered_export(C.c_void_p(ctx), s, _ptr(pts, C.c_uint64), _ptr(vox, C.c_uint64))
+        if rc:
+            raise AsscppError(rc, "covered_export")
+        return pts, vox

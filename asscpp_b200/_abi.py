@@ -114,7 +114,11 @@ SYMBOLS = [
     "asscpp_uncovered_voxels", "asscpp_uncovered_clusters",
     "asscpp_eval_groups", "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
     "asscpp_mesh_last_error", "asscpp_mesh_filter", "asscpp_mesh_segments_free",
-    "asscpp_covered_or_cloud", "asscpp_covered_invert_voxels",
+    "asscpp_covered_or_cloud", "asscpp_covered_invert_voxels", "asscpp_comm_init_all",
+    "asscpp_multi_create", "asscpp_multi_destroy", "asscpp_multi_num_devices", "asscpp_multi_context",
+    "asscpp_multi_last_error", "asscpp_multi_covered_new", "asscpp_multi_covered_free", "asscpp_multi_covered_clear",
+    "asscpp_multi_covered_popcount", "asscpp_multi_coverage_percent", "asscpp_multi_allreduce_or", "asscpp_multi_eval",
+    "asscpp_multi_covered_or_views",
     "asscpp_eval_ex", "asscpp_allgather_gain", "asscpp_collective_ms", "asscpp_robot2sensor_batch",
 ]
 
@@ -194,6 +198,20 @@ def load():
         "asscpp_mesh_segments_free": (i32, [vp, f64p, f64p, i64, u8p]),
         "asscpp_uncovered_voxels": (i32, [vp, i32, i32p, f32p, i64, i64p]),
         "asscpp_uncovered_clusters": (i32, [vp, i32, C.c_double, C.c_int32, C.c_int32, i32p, vp, i64, i64p]),
+        "asscpp_comm_init_all": (i32, [C.POINTER(vp), i32]),
+        "asscpp_multi_create": (i32, [i32p, i32, f32p, i64, C.POINTER(Params), C.POINTER(vp)]),
+        "asscpp_multi_destroy": (i32, [vp]),
+        "asscpp_multi_num_devices": (i32, [vp]),
+        "asscpp_multi_context": (vp, [vp, i32]),
+        "asscpp_multi_last_error": (C.c_char_p, [vp]),
+        "asscpp_multi_covered_new": (i32, [vp, C.POINTER(i32)]),
+        "asscpp_multi_covered_free": (i32, [vp, i32]),
+        "asscpp_multi_covered_clear": (i32, [vp, i32]),
+        "asscpp_multi_covered_popcount": (i32, [vp, i32, i64p, i64p]),
+        "asscpp_multi_coverage_percent": (i32, [vp, i32, f32p]),
+        "asscpp_multi_allreduce_or": (i32, [vp, i32]),
+        "asscpp_multi_eval": (i32, [vp, f64p, i64, C.POINTER(EvalOpts), vp, u32p, u32p]),
+        "asscpp_multi_covered_or_views": (i32, [vp, i32, f64p, i64, i64]),
         "asscpp_covered_or_cloud": (i32, [vp, i32, f32p, i64]),
         "asscpp_covered_invert_voxels": (i32, [vp, i32]),
         "asscpp_eval_ex": (i32, [vp, vp, i64, C.POINTER(EvalOpts)]),

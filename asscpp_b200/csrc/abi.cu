@@ -28,6 +28,7 @@ struct NcclApi {
   void* handle = nullptr;
   int (*GetUniqueId)(NcclUniqueId*) = nullptr;
   int (*CommInitRank)(NcclComm*, int, NcclUniqueId, int) = nullptr;
+  int (*CommInitAll)(NcclComm*, int, const int*) = nullptr;
   int (*AllGather)(const void*, void*, size_t, int, NcclComm, cudaStream_t) = nullptr;
   int (*CommDestroy)(NcclComm) = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
@@ -45,6 +46,7 @@ struct NcclApi {
     CommInitRank = (int (*)(NcclComm*, int, NcclUniqueId, int))dlsym(handle, "ncclCommInitRank");
     AllGather = (int (*)(const void*, void*, size_t, int, NcclComm, cudaStream_t))dlsym(handle, "ncclAllGather");
     CommDestroy = (int (*)(NcclComm))dlsym(handle, "ncclCommDestroy");
+    CommInitAll = (int (*)(NcclComm*, int, const int*))dlsym(handle, "ncclCommInitAll");
     GetErrorString = (const char* (*)(int))dlsym(handle, "ncclGetErrorString");
     if (!GetUniqueId || !CommInitRank || !AllGather || !CommDestroy) { *err = "libnccl lacks required symbols"; return false; }
     return true;
@@ -1065,6 +1067,26 @@ int asscpp_comm_init(AsscppCtx* c, int nranks, int rank, const uint8_t id[128]) 
   }
   c->nranks = nranks;
   c->rank = rank;
+  return ASSCPP_OK;
+}
+
+// one process, several GPUs (asscpp_comm_init(ctxs[], n)): ncclCommInitAll over the contexts' devices
+int asscpp_comm_init_all(AsscppCtx** ctxs, int n) {
+  if (!ctxs || n < 1) return ASSCPP_EINVAL;
+  for (int i = 0; i < n; ++i)
+    if (!ctxs[i] || ctxs[i]->comm) return ASSCPP_EINVAL;
+  if (n == 1) { ctxs[0]->nranks = 1; ctxs[0]->rank = 0; return ASSCPP_OK; }
+  if (!g_nccl.load(&ctxs[0]->err)) return ASSCPP_ENCCL;
+  if (!g_nccl.CommInitAll) { ctxs[0]->err = "libnccl lacks ncclCommInitAll"; return ASSCPP_ENCCL; }
+  std::vector<NcclComm> comms((size_t)n, nullptr);
+  std::vector<int> devs((size_t)n);
+  for (int i = 0; i < n; ++i) devs[(size_t)i] = ctxs[i]->device;
+  int r = g_nccl.CommInitAll(comms.data(), n, devs.data());
+  if (r != 0) {
+    ctxs[0]->err = std::string("ncclCommInitAll: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(r) : "error");
+    return ASSCPP_ENCCL;
+  }
+  for (int i = 0; i < n; ++i) { ctxs[i]->comm = comms[(size_t)i]; ctxs[i]->nranks = n; ctxs[i]->rank = i; }
   return ASSCPP_OK;
 }
 

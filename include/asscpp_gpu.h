@@ -269,6 +269,33 @@ int asscpp_allreduce_or(AsscppCtx* ctx, int set);
 int asscpp_collective_ms(AsscppCtx* ctx, float* allgather_ms, int64_t* allgather_calls, float* allreduce_or_ms,
                          int64_t* allreduce_or_calls);
 int asscpp_comm_destroy(AsscppCtx* ctx);
+/* one process, several GPUs: a communicator over n contexts of THIS process, one per device (ncclCommInitAll);
+ * context i becomes rank i.  The collectives above are then called once per context, from one host thread each. */
+int asscpp_comm_init_all(AsscppCtx** ctxs, int n);
+
+/* -- single-process multi-GPU evaluator -------------------------------------------------------------------------
+ * The reference is one process (coverage_heuristic_test.cpp:42): a program that links the C++ shim cannot start a
+ * rank per GPU.  AsscppMulti holds one context per listed device (model replicated), one host worker thread per
+ * device, and shards each batch over them in contiguous blocks of whole groups; covered sets are mirrored (the same
+ * handle on every device) and kept equal by the NCCL OR-allreduce. */
+typedef struct AsscppMulti AsscppMulti;
+int asscpp_multi_create(const int* devices, int ndev, const float* xyz, int64_t n, const AsscppParams* params,
+                        AsscppMulti** out);
+int asscpp_multi_destroy(AsscppMulti* m);
+int asscpp_multi_num_devices(const AsscppMulti* m);
+AsscppCtx* asscpp_multi_context(AsscppMulti* m, int i);
+const char* asscpp_multi_last_error(const AsscppMulti* m);
+int asscpp_multi_covered_new(AsscppMulti* m, int* set_out);
+int asscpp_multi_covered_free(AsscppMulti* m, int set);
+int asscpp_multi_covered_clear(AsscppMulti* m, int set);
+int asscpp_multi_covered_popcount(AsscppMulti* m, int set, int64_t* n_points, int64_t* n_voxels);
+int asscpp_multi_coverage_percent(AsscppMulti* m, int set, float* pct);
+int asscpp_multi_allreduce_or(AsscppMulti* m, int set);
+/* asscpp_eval_ex over all devices (host poses only).  results / gain_pts / gain_vox (any may be NULL): nviews entries
+ * in the order of poses.  opts->accum_set >= 0: the accumulator is OR-allreduced afterwards. */
+int asscpp_multi_eval(AsscppMulti* m, const double* poses, int64_t nviews, const AsscppEvalOpts* opts,
+                      AsscppViewResult* results, uint32_t* gain_pts, uint32_t* gain_vox);
+int asscpp_multi_covered_or_views(AsscppMulti* m, int set, const double* poses, int64_t nviews, int64_t min_visible);
 
 /* -- synthetic workloads of BASELINE.json configs 2/3/5 (host generators) ------- */
 /* These host-only helpers (generators, pose transforms) are also exported by asscpp_b200/lib/libasscpp_host.so,

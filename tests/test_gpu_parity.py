@@ -524,3 +524,43 @@ def test_uncovered_regions(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
             assert np.array_equal(clusters["grid_start"][c], start) and np.array_equal(clusters["grid_size"][c], size)
             assert clusters["first_id"][c] == ids[mine == c].min()
     s.free()
+
+
+@pytest.mark.gpu
+def test_single_process_multi_gpu_evaluator(A, oracle_mod, etihad, space_2p5):
+    """asscpp_multi_*: one process, every visible GPU (1 on the test box, 2-8 under gpurun --gpus N): a batch sharded
+    over the devices gives the results of one context, and the mirrored covered set equals the oracle's union on
+    every device."""
+    import torch
+    ndev = torch.cuda.device_count()
+    o = oracle_mod.Oracle(etihad[0])
+    poses = np.concatenate([space_2p5["cam0"][500:701], space_2p5["cam1"][500:701]])  # 402 views: uneven shards
+    m = A.MultiContext(etihad[0], A.default_params(), devices=list(range(ndev)))
+    cov, acc = m.new_set(), m.new_set()
+    m.or_views(cov, poses[:60], 5)
+    cp = np.zeros(o.pts_words(), np.uint64)
+    cv = np.zeros(o.vox_words(), np.uint64)
+    o.accumulate(poses[:60], cp, cv, min_visible=5, nthreads=NTHREADS)
+    for d in range(ndev):
+        gp, gv = m.export_set(cov, d)
+        assert np.array_equal(gp, cp) and np.array_equal(gv, cv), d
+    res, gpts, gvox = m.eval(poses, covered=cov, accum=acc, accum_min_visible=5, flags=A.EVAL_HASH)
+    st = o.eval_batch(poses, memo=True, nthreads=NTHREADS, covered_pts=cp, covered_vox=cv)
+    assert_results_equal(oracle_mod, res, st, "multi eval")
+    assert np.array_equal(gpts, res["gain_pts"]) and np.array_equal(gvox, res["gain_vox"])
+    ap = np.zeros(o.pts_words(), np.uint64)
+    av = np.zeros(o.vox_words(), np.uint64)
+    o.accumulate(poses, ap, av, min_visible=5, nthreads=NTHREADS)
+    for d in range(ndev):
+        gp, gv = m.export_set(acc, d)
+        assert np.array_equal(gp, ap) and np.array_equal(gv, av), d
+    # grouped (the sensors of a candidate stay on one device)
+    res2, _, _ = m.eval(poses, covered=cov, group_size=2)
+    one = A.CoverageContext(etihad[0], A.default_params())
+    s1 = one.new_set()
+    s1.load(cp, cv)
+    ref = one.eval_groups(poses, 2, covered=s1)
+    assert np.array_equal(res2["gain_vox"], ref["gain_vox"])
+    assert np.float32(m.coverage_percent(cov)) == np.float32(o.coverage_percent_vox(cv))
+    one.close()
+    m.close()
