@@ -215,14 +215,15 @@ class CoveredSet:
         self.ctx._ck(self.ctx.L.asscpp_covered_import(self.ctx.h, self.handle, _ptr(pts, C.c_uint64),
                                                       _ptr(vox, C.c_uint64)))
 
-    def uncovered(self):
-        """pointCloudDiff (heuristic.cpp:88-145): (ids, centres) of the model's coverage voxels not in the set."""
+    def uncovered(self, pcl_aliasing=False):
+        """pointCloudDiff (heuristic.cpp:88-145): (ids, centres) of the model's coverage voxels not in the set;
+        pcl_aliasing=True reproduces the reference's unchecked linear-index lookup (quirk Q11)."""
         n_cov = self.ctx.n_cov_voxels
         ids = np.zeros(max(n_cov, 1), np.int32)
         ctr = np.zeros((max(n_cov, 1), 3), np.float32)
         n = C.c_int64()
-        self.ctx._ck(self.ctx.L.asscpp_uncovered_voxels(self.ctx.h, self.handle, _ptr(ids, C.c_int32),
-                                                        _ptr(ctr, C.c_float), n_cov, C.byref(n)))
+        self.ctx._ck(self.ctx.L.asscpp_uncovered_voxels_ex(self.ctx.h, self.handle, 1 if pcl_aliasing else 0,
+                                                           _ptr(ids, C.c_int32), _ptr(ctr, C.c_float), n_cov, C.byref(n)))
         return ids[:n.value].copy(), ctr[:n.value].copy()
 
     def uncovered_clusters(self, tolerance=0.8, min_size=5, max_size=50000):

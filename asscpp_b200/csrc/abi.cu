@@ -949,12 +949,25 @@ static int ensure_region_buffers(AsscppCtx* c) {
 }
 
 int asscpp_uncovered_voxels(AsscppCtx* c, int set, int32_t* ids, float* centres, int64_t cap, int64_t* n_out) {
-  if (!c || !valid_set(c, set) || cap < 0 || !n_out) return ASSCPP_EINVAL;
+  return asscpp_uncovered_voxels_ex(c, set, 0, ids, centres, cap, n_out);
+}
+
+int asscpp_uncovered_voxels_ex(AsscppCtx* c, int set, uint32_t flags, int32_t* ids, float* centres, int64_t cap,
+                               int64_t* n_out) {
+  if (!c || !valid_set(c, set) || cap < 0 || !n_out || set == c->tmp_set) return ASSCPP_EINVAL;
   cudaSetDevice(c->device);
   int rc = ensure_region_buffers(c);
   if (rc) return rc;
   const int64_t n = c->m.n_cov;
-  launch_uncovered(set_dev(c, set).vox, n, c->d_region, c->d_region_total, c->d_cov_keys, c->cov_min_b, c->cov_div,
+  const uint32_t* bits = set_dev(c, set).vox;
+  if ((flags & ASSCPP_DIFF_PCL_ALIASING) && n > 0) {
+    // quirk Q11: cells the reference's unchecked linear index takes for covered join the set (in the scratch set)
+    uint32_t* out = set_dev(c, c->tmp_set).vox;
+    launch_covered_alias(bits, out, n, c->d_cov_keys, c->cov_div, (int32_t*)c->d_region_offs, c->stream);
+    c->launches += 2;
+    bits = out;
+  }
+  launch_uncovered(bits, n, c->d_region, c->d_region_total, c->d_cov_keys, c->cov_min_b, c->cov_div,
                    c->params.cov_leaf, c->d_region_ids, c->d_region_ctr, n, c->stream);
   c->launches += 3;
   CU(c, cudaGetLastError());

@@ -26,6 +26,8 @@ void launch_cloud_cover(const float* xyz, int64_t n, float inv_cov, const int32_
 void launch_uncovered(const uint32_t* vox_bits, int64_t n_cov, int32_t* wcount, int64_t* d_total, const int64_t* keys,
                       const int32_t cmin[3], const int32_t cdiv[3], float leaf, int32_t* ids, float* centres,
                       int64_t cap, cudaStream_t s);
+void launch_covered_alias(const uint32_t* vox_bits, uint32_t* out_bits, int64_t n_cov, const int64_t* keys,
+                          const int32_t cdiv[3], int32_t* box6, cudaStream_t s);
 void launch_clusters(const uint32_t* vox_bits, int64_t n_cov, const int64_t* keys, const int32_t cmin[3],
                      const int32_t cdiv[3], const int3* offs, int noffs, int32_t* parent, int32_t* root, int32_t* size,
                      int32_t* box, cudaStream_t s);

@@ -7,6 +7,8 @@
 // reference's scan order); a covered set is one bit per compact id.
 #include <cuda_runtime.h>
 
+#include <climits>
+
 #include "common.h"
 #include "kernels.h"
 
@@ -92,6 +94,53 @@ __global__ void uncovered_emit_kernel(const uint32_t* __restrict__ bits, int64_t
       }
       ++at;
     }
+  }
+}
+
+// ---- quirk Q11: pointCloudDiff's unchecked linear index ----------------------------------------------------------
+// heuristic.cpp:120-123 looks every model cell up in the COVERED cloud's voxel grid with <PCL getCentroidIndexAt>, which
+// linearises (ijk - min_b) . (1, div0, div0 div1) with the covered grid's own box and checks only 0 <= idx < size.  A
+// model cell outside that box can land on the index of another, covered cell and is then NOT reported as uncovered.
+// box[0..2] = min, box[3..5] = max of the covered cells (lattice coordinates relative to the model grid).
+__global__ void covered_box_kernel(const uint32_t* __restrict__ bits, int64_t n_cov, const long long* __restrict__ keys,
+                                   int3 cdiv, int32_t* __restrict__ box) {
+  int mn[3] = {INT_MAX, INT_MAX, INT_MAX}, mx[3] = {INT_MIN, INT_MIN, INT_MIN};
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_cov; i += (int64_t)gridDim.x * blockDim.x) {
+    if (vox_uncovered(bits, i)) continue;
+    const long long key = keys[i];
+    const int r[3] = {(int)(key % cdiv.x), (int)((key / cdiv.x) % cdiv.y), (int)(key / ((long long)cdiv.x * cdiv.y))};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { mn[k] = min(mn[k], r[k]); mx[k] = max(mx[k], r[k]); }
+  }
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int lo = __reduce_min_sync(0xffffffffu, mn[k]), hi = __reduce_max_sync(0xffffffffu, mx[k]);
+    if ((threadIdx.x & 31) == 0 && lo <= hi) { atomicMin(&box[k], lo); atomicMax(&box[3 + k], hi); }
+  }
+}
+
+// out = bits, plus every uncovered model cell whose linear index in the covered grid is that of a covered cell
+__global__ void covered_alias_kernel(const uint32_t* __restrict__ bits, uint32_t* __restrict__ out, int64_t n_cov,
+                                     const long long* __restrict__ keys, int3 cdiv, const int32_t* __restrict__ box) {
+  const int mn0 = box[0], mn1 = box[1], mn2 = box[2];
+  if (mn0 > box[3]) return;  // empty covered set: an empty leaf layout answers -1 to every lookup
+  const int d0 = box[3] - mn0 + 1, d1 = box[4] - mn1 + 1, d2 = box[5] - mn2 + 1;
+  const int size = d0 * d1 * d2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_cov; i += (int64_t)gridDim.x * blockDim.x) {
+    if (!vox_uncovered(bits, i)) continue;
+    const long long key = keys[i];
+    const int r0 = (int)(key % cdiv.x) - mn0, r1 = (int)((key / cdiv.x) % cdiv.y) - mn1,
+              r2 = (int)(key / ((long long)cdiv.x * cdiv.y)) - mn2;
+    const int lin = r0 + r1 * d0 + r2 * d0 * d1;  // <PCL> (ijk - min_b_).dot(divb_mul_), int arithmetic
+    if (lin < 0 || lin >= size) continue;
+    const int a2 = lin / (d0 * d1), rem = lin - a2 * d0 * d1, a1 = rem / d0, a0 = rem - a1 * d0;
+    const long long akey = (a0 + mn0) + (long long)cdiv.x * ((a1 + mn1) + (long long)cdiv.y * (a2 + mn2));
+    int64_t lo = 0, hi = n_cov;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (keys[mid] < akey) lo = mid + 1; else hi = mid;
+    }
+    if (lo < n_cov && keys[lo] == akey && !vox_uncovered(bits, lo)) atomicOr(&out[i >> 5], 1u << (i & 31));
   }
 }
 
@@ -182,6 +231,17 @@ void launch_uncovered(const uint32_t* vox_bits, int64_t n_cov, int32_t* wcount, 
   uncovered_emit_kernel<<<grid_for(words), 256, 0, s>>>(vox_bits, n_cov, wcount, (const long long*)keys,
                                                         make_int3(cmin[0], cmin[1], cmin[2]),
                                                         make_int3(cdiv[0], cdiv[1], cdiv[2]), leaf, ids, centres, cap);
+}
+
+void launch_covered_alias(const uint32_t* vox_bits, uint32_t* out_bits, int64_t n_cov, const int64_t* keys,
+                          const int32_t cdiv[3], int32_t* box6, cudaStream_t s) {
+  if (n_cov <= 0) return;
+  static const int32_t init[6] = {INT_MAX, INT_MAX, INT_MAX, INT_MIN, INT_MIN, INT_MIN};
+  cudaMemcpyAsync(box6, init, sizeof(init), cudaMemcpyHostToDevice, s);
+  const int3 dv = make_int3(cdiv[0], cdiv[1], cdiv[2]);
+  cudaMemcpyAsync(out_bits, vox_bits, (size_t)((n_cov + 31) / 32) * 4, cudaMemcpyDeviceToDevice, s);
+  covered_box_kernel<<<grid_for(n_cov), 256, 0, s>>>(vox_bits, n_cov, (const long long*)keys, dv, box6);
+  covered_alias_kernel<<<grid_for(n_cov), 256, 0, s>>>(vox_bits, out_bits, n_cov, (const long long*)keys, dv, box6);
 }
 
 void launch_clusters(const uint32_t* vox_bits, int64_t n_cov, const int64_t* keys, const int32_t cmin[3],

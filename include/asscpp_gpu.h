@@ -200,6 +200,13 @@ int asscpp_coverage_percent_cloud(AsscppCtx* ctx, const float* xyz, int64_t n, f
  * scan order (= ascending compact id), with their cell centres (getCentroidCoordinate).  ids / centres_xyz may be
  * NULL; at most cap entries are written; *n_out receives the full count (uncovered % = 100 * n / n_cov_voxels). */
 int asscpp_uncovered_voxels(AsscppCtx* ctx, int set, int32_t* ids, float* centres_xyz, int64_t cap, int64_t* n_out);
+/* The same with the reference's quirk (flags & ASSCPP_DIFF_PCL_ALIASING): pointCloudDiff looks every model cell up in
+ * the COVERED cloud's voxel grid through PCL's getCentroidIndexAt (heuristic.cpp:120-123), which linearises the cell
+ * with that grid's own box and only checks 0 <= idx < size; a model cell outside the box whose index is that of a
+ * covered cell is therefore not reported.  With the flag the list is exactly the reference's. */
+enum { ASSCPP_DIFF_PCL_ALIASING = 1u };
+int asscpp_uncovered_voxels_ex(AsscppCtx* ctx, int set, uint32_t flags, int32_t* ids, float* centres_xyz, int64_t cap,
+                               int64_t* n_out);
 
 /* clusteringPointCloud (:147-190, pcl::EuclideanClusterExtraction: tolerance 0.8, sizes 5..50000 in the reference)
  * over those voxel centres + findClusterBB (:218-246) per cluster.  Clusters come largest first (equal sizes: by

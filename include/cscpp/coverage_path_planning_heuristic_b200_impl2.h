@@ -188,7 +188,8 @@ inline double CoveragePathPlanningHeuristic::pointCloudDiff(pcl::PointCloud<pcl:
   asscpp_model_info(ctx(), &info);
   std::vector<float> ctr(3 * (size_t)std::max<int64_t>(info.n_cov_voxels, 1));
   int64_t n = 0;
-  check(asscpp_uncovered_voxels(ctx(), set, NULL, ctr.data(), info.n_cov_voxels, &n));
+  // with the reference's unchecked linear-index lookup into the covered cloud's grid (:120-123, quirk Q11)
+  check(asscpp_uncovered_voxels_ex(ctx(), set, ASSCPP_DIFF_PCL_ALIASING, NULL, ctr.data(), info.n_cov_voxels, &n));
   pointCloudDiffPtr->points.resize((size_t)n);
   for (int64_t i = 0; i < n; ++i) pointCloudDiffPtr->points[(size_t)i] = pcl::PointXYZ(ctr[3 * i], ctr[3 * i + 1], ctr[3 * i + 2]);
   return ((double)n / (double)info.n_cov_voxels) * 100;  // :143

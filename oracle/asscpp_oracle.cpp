@@ -9,6 +9,8 @@
 #include "asscpp_oracle.h"
 
 #include <algorithm>
+#include <map>
+#include <array>
 #include <atomic>
 #include <cmath>
 #include <cstdlib>
@@ -768,16 +770,38 @@ void orc_accuracy_idx(const OrcCtx* c, const double pose[7], const int32_t* idx,
   *err_sum_depth = sd; *err_sum_z = sz; *depth_min = lo; *depth_max = hi;
 }
 
-int64_t orc_uncovered(const OrcCtx* oc, const uint64_t* covered_vox, int32_t* ids, float* centres) {
+int64_t orc_uncovered_ex(const OrcCtx* oc, const uint64_t* covered_vox, int pcl_aliasing, int32_t* ids, float* centres) {
   // pointCloudDiff (coverage_path_planning_heuristic.cpp:88-145): scan the model's coverage grid in k, j, i order
   // (= ascending compact id) and keep the occupied cells whose centre falls in no covered voxel.  Both grids share
-  // the lattice floor(x * inv_leaf), so "centre not in a covered voxel" is "bit not set".  Centre =
-  // getCentroidCoordinate (voxel_grid_occlusion_estimation.h:143-157) on the model grid.
+  // the lattice floor(x * inv_leaf), so "centre not in a covered voxel" is "bit not set" -- except for quirk Q11
+  // (pcl_aliasing): the lookup into the covered cloud's grid is <PCL getCentroidIndexAt> (:122), which linearises
+  // (ijk - min_b) . (1, div0, div0 div1) with THAT grid's box and checks only 0 <= idx < size, so a model cell
+  // outside the box can read the entry of another, covered cell and is then not reported.
+  // Centre = getCentroidCoordinate (voxel_grid_occlusion_estimation.h:143-157) on the model grid.
   const Ctx& c = oc->c;
   const f32 leaf = c.p.cov_leaf;
+  auto covered = [&](int64_t u) { return covered_vox && ((covered_vox[u >> 6] >> (u & 63)) & 1ull); };
+  int mn[3] = {INT32_MAX, INT32_MAX, INT32_MAX}, mx[3] = {INT32_MIN, INT32_MIN, INT32_MIN};
+  std::map<std::array<int32_t, 3>, int64_t> index;
+  if (pcl_aliasing)
+    for (int64_t u = 0; u < c.n_cov; ++u) {
+      index[{c.cov_ijk[3 * u], c.cov_ijk[3 * u + 1], c.cov_ijk[3 * u + 2]}] = u;
+      if (!covered(u)) continue;
+      for (int k = 0; k < 3; ++k) { mn[k] = std::min(mn[k], c.cov_ijk[3 * u + k]); mx[k] = std::max(mx[k], c.cov_ijk[3 * u + k]); }
+    }
+  const bool any = pcl_aliasing && mn[0] <= mx[0];
+  const int d0 = any ? mx[0] - mn[0] + 1 : 0, d1 = any ? mx[1] - mn[1] + 1 : 0, d2 = any ? mx[2] - mn[2] + 1 : 0;
   int64_t n = 0;
   for (int64_t u = 0; u < c.n_cov; ++u) {
-    if (covered_vox && ((covered_vox[u >> 6] >> (u & 63)) & 1ull)) continue;
+    if (covered(u)) continue;
+    if (any) {
+      const int lin = (c.cov_ijk[3 * u] - mn[0]) + (c.cov_ijk[3 * u + 1] - mn[1]) * d0 + (c.cov_ijk[3 * u + 2] - mn[2]) * d0 * d1;
+      if (lin >= 0 && lin < d0 * d1 * d2) {
+        const int a2 = lin / (d0 * d1), rem = lin - a2 * d0 * d1, a1 = rem / d0, a0 = rem - a1 * d0;
+        auto it = index.find({a0 + mn[0], a1 + mn[1], a2 + mn[2]});
+        if (it != index.end() && covered(it->second)) continue;  // leaf_layout_[lin] != -1
+      }
+    }
     if (ids) ids[n] = (int32_t)u;
     if (centres)
       for (int k = 0; k < 3; ++k) {
@@ -787,6 +811,10 @@ int64_t orc_uncovered(const OrcCtx* oc, const uint64_t* covered_vox, int32_t* id
     ++n;
   }
   return n;
+}
+
+int64_t orc_uncovered(const OrcCtx* oc, const uint64_t* covered_vox, int32_t* ids, float* centres) {
+  return orc_uncovered_ex(oc, covered_vox, 0, ids, centres);
 }
 
 int32_t orc_euclidean_clusters(const float* xyz, int64_t n, double tol, int32_t min_size, int32_t max_size,

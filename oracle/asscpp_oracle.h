@@ -114,6 +114,8 @@ void orc_accuracy_idx(const OrcCtx* c, const double pose[7], const int32_t* idx,
 /* pointCloudDiff (coverage_path_planning_heuristic.cpp:88-145) in bitset form: uncovered coverage voxels in the
  * reference's k, j, i scan order (= ascending compact id) with their cell centres; returns their number */
 int64_t orc_uncovered(const OrcCtx* c, const uint64_t* covered_vox, int32_t* ids, float* centres);
+/* pcl_aliasing != 0: with the reference's unchecked linear-index lookup (quirk Q11, heuristic.cpp:120-123) */
+int64_t orc_uncovered_ex(const OrcCtx* c, const uint64_t* covered_vox, int pcl_aliasing, int32_t* ids, float* centres);
 /* clusteringPointCloud (:147-190), <PCL EuclideanClusterExtraction>: labels[i] = cluster rank (largest first) or -1;
  * ties (optional) counts point pairs at squared distance exactly float(tol*tol) */
 int32_t orc_euclidean_clusters(const float* xyz, int64_t n, double tol, int32_t min_size, int32_t max_size,

@@ -95,6 +95,8 @@ def lib():
         L.orc_accuracy_idx.restype = None
         L.orc_uncovered.argtypes = [vp, u64p, i32p, f32p]
         L.orc_uncovered.restype = i64
+        L.orc_uncovered_ex.argtypes = [vp, u64p, C.c_int, i32p, f32p]
+        L.orc_uncovered_ex.restype = i64
         L.orc_euclidean_clusters.argtypes = [f32p, i64, C.c_double, C.c_int32, C.c_int32, i32p, i64p]
         L.orc_euclidean_clusters.restype = C.c_int32
         L.orc_cluster_bb.argtypes = [f32p, i64, C.c_float, f64p, f64p]
@@ -200,11 +202,11 @@ class Oracle:
         idx = np.ascontiguousarray(idx, dtype=np.int32)
         return float(self.L.orc_coverage_percent_idx(self.h, _p(idx, C.c_int32), idx.shape[0]))
 
-    def uncovered(self, covered_vox=None):
+    def uncovered(self, covered_vox=None, pcl_aliasing=False):
         """pointCloudDiff (heuristic.cpp:88-145): (ids, centres) of the uncovered coverage voxels."""
         ids = np.zeros(max(self.n_cov, 1), np.int32)
         ctr = np.zeros((max(self.n_cov, 1), 3), np.float32)
-        n = lib().orc_uncovered(self.h, _p(covered_vox, C.c_uint64), _p(ids, C.c_int32), _p(ctr, C.c_float))
+        n = lib().orc_uncovered_ex(self.h, _p(covered_vox, C.c_uint64), int(pcl_aliasing), _p(ids, C.c_int32), _p(ctr, C.c_float))
         return ids[:n].copy(), ctr[:n].copy()
 
     def accuracy_idx(self, pose, idx):

@@ -70,6 +70,8 @@ def lib(path=LIB_PATH):
     L.ref_planner_load_grid.argtypes = [vp, C.c_char_p, C.c_char_p, C.c_char_p]; L.ref_planner_load_grid.restype = None
     L.ref_planner_search_space.argtypes = [vp, f64p, f64p, f64p, i64]; L.ref_planner_search_space.restype = i64
     L.ref_planner_num_connections.argtypes = [vp]; L.ref_planner_num_connections.restype = i64
+    L.ref_planner_point_cloud_diff.argtypes = [vp, f32p, i64, f32p, i64, i64p]; L.ref_planner_point_cloud_diff.restype = C.c_double
+    L.ref_planner_clusters.argtypes = [vp, f32p, i64, i32p, f64p, i64]; L.ref_planner_clusters.restype = i64
     L.ref_planner_set_accuracy_range.argtypes = [vp]; L.ref_planner_set_accuracy_range.restype = None
     L.ref_planner_search.argtypes = [vp, f64p, f64p, i64]; L.ref_planner_search.restype = i64
     _libs[path] = L
@@ -216,6 +218,22 @@ class RefPlanner:
         sens = np.zeros((n, 2, 7), np.float64)
         self.L.ref_planner_search_space(self.h, _p(rows, C.c_double), _p(robot, C.c_double), _p(sens, C.c_double), n)
         return rows, robot, sens
+
+    def point_cloud_diff(self, xyz):
+        """pointCloudDiff of a covered cloud: (uncovered %, cell centres of the uncovered model voxels)."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.zeros((200000, 3), np.float32)
+        n = C.c_int64()
+        pct = self.L.ref_planner_point_cloud_diff(self.h, _p(xyz, C.c_float), len(xyz), _p(out, C.c_float), len(out), C.byref(n))
+        return pct, out[:n.value].copy()
+
+    def clusters(self, xyz):
+        """clusteringPointCloud + findClusterBB: (labels per point, boxes [k, 6])."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        labels = np.zeros(len(xyz), np.int32)
+        boxes = np.zeros((4096, 6), np.float64)
+        k = self.L.ref_planner_clusters(self.h, _p(xyz, C.c_float), len(xyz), _p(labels, C.c_int32), _p(boxes, C.c_double), len(boxes))
+        return labels, boxes[:k].copy()
 
     def num_connections(self):
         return self.L.ref_planner_num_connections(self.h)

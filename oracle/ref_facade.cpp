@@ -321,6 +321,43 @@ int64_t ref_planner_num_connections(void* h) {
   return (int64_t)static_cast<RefPlanner*>(h)->planner->getConnections().size() / 2;
 }
 
+// CoveragePathPlanningHeuristic::pointCloudDiff (heuristic.cpp:88-145) of an arbitrary covered cloud
+double ref_planner_point_cloud_diff(void* h, const float* xyz, int64_t n, float* centres, int64_t cap, int64_t* n_out) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  pcl::PointCloud<pcl::PointXYZ>::Ptr c(new pcl::PointCloud<pcl::PointXYZ>), d(new pcl::PointCloud<pcl::PointXYZ>);
+  for (int64_t i = 0; i < n; ++i) c->points.push_back(pcl::PointXYZ(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+  const double pct = r->heuristic->pointCloudDiff(c, d);
+  *n_out = (int64_t)d->points.size();
+  for (int64_t i = 0; i < *n_out && i < cap; ++i) {
+    centres[3 * i] = d->points[(size_t)i].x; centres[3 * i + 1] = d->points[(size_t)i].y; centres[3 * i + 2] = d->points[(size_t)i].z;
+  }
+  return pct;
+}
+
+// clusteringPointCloud (heuristic.cpp:147-190) + findClusterBB (:218-246): labels per input point (-1: in no cluster),
+// boxes: per cluster {start x y z, size x y z}
+int64_t ref_planner_clusters(void* h, const float* xyz, int64_t n, int32_t* labels, double* boxes, int64_t cap) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  pcl::PointCloud<pcl::PointXYZ>::Ptr c(new pcl::PointCloud<pcl::PointXYZ>);
+  for (int64_t i = 0; i < n; ++i) c->points.push_back(pcl::PointXYZ(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+  std::vector<pcl::PointCloud<pcl::PointXYZ> > cl;
+  r->heuristic->clusteringPointCloud(cl, c);
+  for (int64_t i = 0; i < n; ++i) labels[i] = -1;
+  for (size_t k = 0; k < cl.size(); ++k) {
+    for (size_t j = 0; j < cl[k].points.size(); ++j)
+      for (int64_t i = 0; i < n; ++i)
+        if (std::memcmp(c->points[(size_t)i].data, cl[k].points[j].data, 12) == 0) { labels[i] = (int32_t)k; break; }
+    if ((int64_t)k < cap) {
+      geometry_msgs::Vector3 sz;
+      geometry_msgs::Pose st;
+      r->heuristic->findClusterBB(cl[k], sz, st);
+      double* o = boxes + 6 * k;
+      o[0] = st.position.x; o[1] = st.position.y; o[2] = st.position.z; o[3] = sz.x; o[4] = sz.y; o[5] = sz.z;
+    }
+  }
+  return (int64_t)cl.size();
+}
+
 // setMaxMinSensorAccuracy over the current search space (coverage_heuristic_test.cpp:155-158)
 void ref_planner_set_accuracy_range(void* h) {
   RefPlanner* r = static_cast<RefPlanner*>(h);

@@ -119,8 +119,9 @@ def test_first_sampling_stage_gpu_plugin_equals_reference_heuristic(tmp_path, li
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("htype,batch", [(0, 0), (0, 1), (1, 1), (2, 1), (4, 1)])
-def test_reference_astar_over_gpu_plugin_equals_reference_heuristic(tmp_path, lib_built, R, etihad, space_2p5, htype, batch):
+@pytest.mark.parametrize("htype,batch,target", [(0, 0, 5.0), (0, 1, 5.0), (1, 1, 5.0), (2, 1, 5.0), (4, 1, 3.0)])
+def test_reference_astar_over_gpu_plugin_equals_reference_heuristic(tmp_path, lib_built, R, etihad, space_2p5, htype, batch,
+                                                                    target):
     """Astar::astarSearch (astar.cpp:220-373), unmodified, scoring children through the plugin -- one child per call
     (batch 0) or with the one-line batcher hook (batch 1: one launch per expansion) -- against the same search driven
     by the reference's CPU heuristic: same path, coverage, f value and distance at every node.  Types:
@@ -128,12 +129,12 @@ def test_reference_astar_over_gpu_plugin_equals_reference_heuristic(tmp_path, li
     exe = build_driver()
     pcd, obj = write_model(tmp_path, etihad[0])
     files = write_space(tmp_path, space_2p5)
-    out = subprocess.run([exe, "astar", pcd, obj] + files + [str(htype), "5.0", "1.0", str(batch)], capture_output=True,
+    out = subprocess.run([exe, "astar", pcd, obj] + files + [str(htype), str(target), "1.0", str(batch)], capture_output=True,
                          text=True, timeout=1800)
     assert out.returncode == 0, out.stderr[-2000:]
     path = parse(out.stdout, "NODE")
     launches = [ln for ln in out.stdout.splitlines() if ln.startswith("LAUNCHES")][0].split()
-    p = R.RefPlanner(obj, pcd, heuristic_type=htype, target=5.0, tolerance=1.0, conn_radius=2.5)
+    p = R.RefPlanner(obj, pcd, heuristic_type=htype, target=target, tolerance=1.0, conn_radius=2.5)
     p.load_grid(*files)
     if htype in (2, 4):
         p.set_accuracy_range()

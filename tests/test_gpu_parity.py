@@ -527,6 +527,29 @@ def test_uncovered_regions(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
 
 
 @pytest.mark.gpu
+def test_uncovered_with_reference_index_aliasing(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
+    """asscpp_uncovered_voxels_ex(ASSCPP_DIFF_PCL_ALIASING): pointCloudDiff's unchecked linear-index lookup (quirk Q11,
+    heuristic.cpp:120-123) on the device equals the oracle's restatement (which equals the reference's own
+    pointCloudDiff, tests/test_ref_pin.py)."""
+    o = etihad_oracle
+    for lo, hi in ((560, 600), (600, 700), (300, 900)):
+        poses = np.concatenate([space_2p5["cam0"][lo:hi], space_2p5["cam1"][lo:hi]])
+        cp = np.zeros(o.pts_words(), np.uint64)
+        cv = np.zeros(o.vox_words(), np.uint64)
+        o.accumulate(poses, cp, cv, min_visible=5, nthreads=NTHREADS)
+        s = etihad_ctx.new_set()
+        s.load(cp, cv)
+        for alias in (False, True):
+            ids, ctr = s.uncovered(pcl_aliasing=alias)
+            ids_o, ctr_o = o.uncovered(cv, pcl_aliasing=alias)
+            assert np.array_equal(ids, ids_o) and np.array_equal(ctr, ctr_o), (lo, hi, alias)
+        s.free()
+    e = etihad_ctx.new_set()  # empty set: nothing to alias into
+    assert len(e.uncovered(pcl_aliasing=True)[0]) == o.n_cov
+    e.free()
+
+
+@pytest.mark.gpu
 def test_single_process_multi_gpu_evaluator(A, oracle_mod, etihad, space_2p5):
     """asscpp_multi_*: one process, every visible GPU (1 on the test box, 2-8 under gpurun --gpus N): a batch sharded
     over the devices gives the results of one context, and the mirrored covered set equals the oracle's union on

@@ -152,3 +152,36 @@ def test_first_sampling_stage_of_the_shipped_run_is_reproduced(R):
     assert not missing, "rows of the file the run does not accept: %s" % missing[:5]
     before, after = D.extras_vs_truncation(got, rows)
     assert after == 0 and before == len(got) - 302
+
+
+def test_uncovered_regions_of_the_adaptive_loop(R, oracle_mod, etihad):
+    """pointCloudDiff (heuristic.cpp:88-145) incl. its unchecked linear-index lookup (quirk Q11),
+    clusteringPointCloud (:147-190) and findClusterBB (:218-246): the reference's heuristic object vs the oracle, on the
+    covered cloud the first sampling stage of the shipped run leaves behind."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import reproduce_dsscpp as D
+    if not os.path.exists(D.OBJ):
+        pytest.skip("/root/reference is not mounted")
+    xyz = etihad[0]
+    g = np.load(os.path.join(ROOT, "tests", "golden", "dsscpp_reference_run.npz"))
+    o = oracle_mod.Oracle(xyz)
+    stage1 = g["sensors"][-335:].reshape(-1, 7)
+    cp = np.zeros(o.pts_words(), np.uint64)
+    cv = np.zeros(o.vox_words(), np.uint64)
+    o.accumulate(stage1, cp, cv, min_visible=5, nthreads=NTHREADS)
+    idx = np.nonzero(np.unpackbits(cp.view(np.uint8), bitorder="little")[:len(xyz)])[0]
+    p = R.RefPlanner(D.OBJ, D.PCD, 0)
+    pct, ctr = p.point_cloud_diff(xyz[idx])
+    ids_a, ctr_a = o.uncovered(cv, pcl_aliasing=True)
+    ids_p, ctr_p = o.uncovered(cv)
+    assert np.array_equal(ctr, ctr_a)                      # same cells, same order, same float32 centres
+    assert pct == len(ctr_a) / o.n_cov * 100
+    assert len(ctr_p) > len(ctr_a)                         # the quirk hides cells: plain set difference finds more
+    labels, boxes = p.clusters(ctr)
+    lab_o, k_o, _ = oracle_mod.euclidean_clusters(ctr, 0.8, 5, 50000)
+    assert len(boxes) == k_o and np.array_equal(labels, lab_o)
+    for c in range(k_o):
+        start, size = oracle_mod.cluster_bb(ctr[lab_o == c], 0.5)
+        assert boxes[c].tolist() == start.tolist() + size.tolist()
+    p.close()
