@@ -3,7 +3,6 @@
 set -u
 O=gpurun_out/r02b
 mkdir -p $O
-( time python -m pytest tests/test_boundary.py tests/test_cpp_shim.py tests/test_ref_pin.py -m gpu -q -x ) > $O/pytest_boundary.txt 2>&1
-echo "rc=$?" >> $O/pytest_boundary.txt
 ( time python -m pytest tests/test_boundary.py tests/test_cpp_shim.py -m gpu -q ) > $O/pytest_boundary_all.txt 2>&1
-tail -30 $O/pytest_boundary_all.txt
+( time python -m pytest tests/test_gpu_parity.py -m gpu -q -k "aliasing or multi_gpu or eval_ex or uncovered" ) > $O/pytest_new.txt 2>&1
+tail -5 $O/pytest_boundary_all.txt $O/pytest_new.txt
