@@ -482,6 +482,32 @@ class MultiContext:
                                           res.ctypes.data_as(C.c_void_p), _ptr(gp, C.c_uint32), _ptr(gv, C.c_uint32)))
         return res, gp, gv
 
+    def adaptive_sampling(self, mesh, grid_start, grid_size, start_res=4.5, res_decrement=1.5, mounts=None,
+                          global_set=None, cap=200000):
+        """asscpp_adaptive_sampling (the batched C++ host loop of pathplanner.cpp:729-850):
+        (robot poses [n, 7] newest first, sensor poses [n, sensors, 7], stages)."""
+        from ._abi import STAGE_DTYPE, SamplingOpts
+        mounts = mounts or (((0.0, 0.022, 0.065), (0.0, -0.349, 0.0)), ((0.0, 0.022, -0.065), (0.0, 0.349, 0.0)))
+        o = SamplingOpts()
+        o.grid_start[:] = list(grid_start)
+        o.grid_size[:] = list(grid_size)
+        o.start_res, o.res_decrement, o.orientation_res_deg = start_res, res_decrement, 45.0
+        o.min_dist, o.max_dist, o.stop_uncovered_pct = 1.0, 4.0, 0.01
+        o.n_sensors = len(mounts)
+        for i, (off, rpy) in enumerate(mounts):
+            # the reference keeps the mounts in float32 (Eigen::Vector3f, sspp/include/sspp/sensors.h:60)
+            o.sensor_offset[i][:] = [float(np.float32(v)) for v in off]
+            o.sensor_rpy[i][:] = [float(np.float32(v)) for v in rpy]
+        gs = self.new_set() if global_set is None else global_set
+        robot = np.zeros((cap, 7), np.float64)
+        sens = np.zeros((cap, len(mounts), 7), np.float64)
+        stages = np.zeros(16, STAGE_DTYPE)
+        n, nst = C.c_int64(), C.c_int()
+        self._ck(self.L.asscpp_adaptive_sampling(self.h, mesh.h, C.byref(o), gs, _ptr(robot, C.c_double),
+                                                 _ptr(sens, C.c_double), cap, C.byref(n),
+                                                 stages.ctypes.data_as(C.c_void_p), len(stages), C.byref(nst)))
+        return robot[:n.value].copy(), sens[:n.value].copy(), stages[:nst.value].copy(), gs
+
     def export_set(self, s, device_index=0):
         """(point bits, voxel bits) of the set as device `device_index` holds it."""
         ctx = self.L.asscpp_multi_context(self.h, device_index)

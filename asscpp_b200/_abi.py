@@ -41,6 +41,20 @@ class ModelInfo(C.Structure):
     ]
 
 
+class SamplingOpts(C.Structure):
+    _fields_ = [
+        ("grid_start", C.c_double * 3), ("grid_size", C.c_double * 3), ("start_res", C.c_double),
+        ("res_decrement", C.c_double), ("orientation_res_deg", C.c_double), ("min_dist", C.c_double),
+        ("max_dist", C.c_double), ("stop_uncovered_pct", C.c_double), ("n_sensors", C.c_int32), ("reserved", C.c_int32),
+        ("sensor_offset", (C.c_double * 3) * 4), ("sensor_rpy", (C.c_double * 3) * 4),
+    ]
+
+
+STAGE_DTYPE = np.dtype([("res", np.float64), ("uncovered_pct_before", np.float64), ("uncovered_pct_after", np.float64),
+                        ("grids", np.int64), ("candidates", np.int64), ("passed_mesh", np.int64), ("accepted", np.int64),
+                        ("clusters", np.int64)])
+
+
 class EvalOpts(C.Structure):
     _fields_ = [
         ("covered_set", C.c_int32),
@@ -118,7 +132,7 @@ SYMBOLS = [
     "asscpp_multi_create", "asscpp_multi_destroy", "asscpp_multi_num_devices", "asscpp_multi_context",
     "asscpp_multi_last_error", "asscpp_multi_covered_new", "asscpp_multi_covered_free", "asscpp_multi_covered_clear",
     "asscpp_multi_covered_popcount", "asscpp_multi_coverage_percent", "asscpp_multi_allreduce_or", "asscpp_multi_eval",
-    "asscpp_multi_covered_or_views",
+    "asscpp_multi_covered_or_views", "asscpp_grid_candidates", "asscpp_adaptive_sampling",
     "asscpp_eval_ex", "asscpp_allgather_gain", "asscpp_collective_ms", "asscpp_robot2sensor_batch",
 ]
 
@@ -213,6 +227,9 @@ def load():
         "asscpp_multi_allreduce_or": (i32, [vp, i32]),
         "asscpp_multi_eval": (i32, [vp, f64p, i64, C.POINTER(EvalOpts), vp, u32p, u32p]),
         "asscpp_multi_covered_or_views": (i32, [vp, i32, f64p, i64, i64]),
+        "asscpp_grid_candidates": (i64, [f64p, f64p, C.c_double, C.c_double, f64p, i64]),
+        "asscpp_adaptive_sampling": (i32, [vp, vp, C.POINTER(SamplingOpts), i32, f64p, f64p, i64, i64p, vp, i32,
+                                           C.POINTER(i32)]),
         "asscpp_covered_or_cloud": (i32, [vp, i32, f32p, i64]),
         "asscpp_covered_invert_voxels": (i32, [vp, i32]),
         "asscpp_eval_ex": (i32, [vp, vp, i64, C.POINTER(EvalOpts)]),

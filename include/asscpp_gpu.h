@@ -304,6 +304,34 @@ int asscpp_multi_eval(AsscppMulti* m, const double* poses, int64_t nviews, const
                       AsscppViewResult* results, uint32_t* gain_pts, uint32_t* gain_vox);
 int asscpp_multi_covered_or_views(AsscppMulti* m, int set, const double* poses, int64_t nviews, int64_t min_visible);
 
+/* -- the adaptive sampling loop, host side in C++ (sspp/src/pathplanner.cpp:106-201, 729-850) ---------------------- */
+/* PathPlanner::generateRegularGrid's candidate lattice: robot poses {x y z qx qy qz qw} in its loop order (z, x, y,
+ * then 360 / orientation_res_deg yaws from 0).  Returns the count (robot_poses may be NULL / cap 0 to ask for it). */
+int64_t asscpp_grid_candidates(const double grid_start[3], const double grid_size[3], double res,
+                               double orientation_res_deg, double* robot_poses, int64_t cap);
+typedef struct AsscppSamplingOpts {
+  double grid_start[3], grid_size[3];   /* first stage (coverage_heuristic_test.cpp:75-80)                           */
+  double start_res, res_decrement;      /* 4.5, 1.5 in the demo (:137)                                                */
+  double orientation_res_deg;           /* 45 (pathplanner.cpp:736)                                                   */
+  double min_dist, max_dist;            /* stand-off window of the mesh filter: 1, 4 (pathplanner.cpp:160)            */
+  double stop_uncovered_pct;            /* 0.01 (pathplanner.cpp:776)                                                 */
+  int32_t n_sensors, reserved;          /* <= 4                                                                       */
+  double sensor_offset[4][3];           /* mounts (coverage_heuristic_test.cpp:94-95), as float32 values              */
+  double sensor_rpy[4][3];
+} AsscppSamplingOpts;
+typedef struct AsscppSamplingStage {
+  double res, uncovered_pct_before, uncovered_pct_after;
+  int64_t grids, candidates, passed_mesh, accepted, clusters;
+} AsscppSamplingStage;
+/* PathPlanner::dynamicNodesGenerationAndConnection without the node connection: per stage ONE mesh launch and ONE
+ * evaluation launch over all GPUs of m for every candidate of every cluster grid, the accepted sensors' clouds OR-ed
+ * into global_set (a set of m), then pointCloudDiff / clusteringPointCloud / findClusterBB on the device.
+ * robot_poses (cap x 7) / sensor_poses (cap x n_sensors x 7) receive the accepted waypoints in the search space's
+ * order (newest first, duplicates dropped as SearchSpace::insertNode does); either may be NULL. */
+int asscpp_adaptive_sampling(AsscppMulti* m, AsscppMesh* mesh, const AsscppSamplingOpts* opts, int global_set,
+                             double* robot_poses, double* sensor_poses, int64_t cap, int64_t* n_out,
+                             AsscppSamplingStage* stages, int stage_cap, int* n_stages);
+
 /* -- synthetic workloads of BASELINE.json configs 2/3/5 (host generators) ------- */
 /* These host-only helpers (generators, pose transforms) are also exported by asscpp_b200/lib/libasscpp_host.so,
  * which has no CUDA in it: the benchmark's CPU reference arm draws its inputs from there, so it never maps the

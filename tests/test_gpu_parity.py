@@ -587,3 +587,28 @@ def test_single_process_multi_gpu_evaluator(A, oracle_mod, etihad, space_2p5):
     assert np.float32(m.coverage_percent(cov)) == np.float32(o.coverage_percent_vox(cv))
     one.close()
     m.close()
+
+
+@pytest.mark.gpu
+def test_adaptive_sampling_host_loop(A, etihad):
+    """asscpp_adaptive_sampling: the C++ host loop of PathPlanner::dynamicNodesGenerationAndConnection
+    (sspp/src/pathplanner.cpp:729-850), batched -- one mesh launch and one evaluation launch per stage over every
+    visible GPU -- produces, row for row and in the search space's order, the waypoints the reference's OWN loop
+    produced with the reference's own CPU heuristic (tests/golden/dsscpp_reference_run.npz, tools/reproduce_dsscpp.py)."""
+    import torch
+    g = np.load(os.path.join(GOLDEN, "dsscpp_reference_run.npz"))
+    mg = np.load(os.path.join(GOLDEN, "etihad_mesh.npz"))
+    m = A.MultiContext(etihad[0], A.default_params(), devices=list(range(torch.cuda.device_count())))
+    mesh = A.Mesh(mg["vertices"], mg["triangles"])
+    robot, sens, stages, gs = m.adaptive_sampling(mesh, g["grid_start"], g["grid_size"], start_res=3.0, res_decrement=1.5)
+    assert len(stages) == 2 and stages["candidates"][0] == 2112 and stages["accepted"][0] == 335
+    assert len(robot) == len(g["robot"]) == 2885
+    assert np.array_equal(robot, g["robot"])
+    assert np.array_equal(sens, g["sensors"])
+    cand = np.zeros((4000, 7))
+    n = A._abi.load().asscpp_grid_candidates(A._ptr(np.ascontiguousarray(g["grid_start"]), A.C.c_double),
+                                             A._ptr(np.ascontiguousarray(g["grid_size"]), A.C.c_double), 3.0, 45.0,
+                                             A._ptr(cand, A.C.c_double), len(cand))
+    assert n == 2112
+    mesh.close()
+    m.close()
