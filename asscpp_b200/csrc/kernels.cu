@@ -33,6 +33,17 @@ __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b)
 __device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }
 __device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b); }
 
+// Model points are read once per view and never reused by the CTA; the per-CTA scratch (voxel lists, ray queues) is
+// rewritten every view and should stay in L2.  ASSCPP_STREAM_POINTS marks the point reads evict-first (ld.global.cs)
+// so that they do not push dirty scratch lines out to DRAM.
+__device__ __forceinline__ float4 ld_pt(const float4* p) {
+#ifdef ASSCPP_STREAM_POINTS
+  return __ldcs(p);
+#else
+  return *p;
+#endif
+}
+
 __device__ __forceinline__ uint64_t mix64(uint64_t x) {
   x += 0x9E3779B97F4A7C15ull;
   x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
@@ -464,7 +475,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           for (uint32_t qb = q0; qb < q1; qb += 4) {
             float4 p[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) p[k] = m.pts[min(qb + k, q1 - 1)];
+            for (int k = 0; k < 4; ++k) p[k] = ld_pt(&m.pts[min(qb + k, q1 - 1)]);
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
               if (qb + k >= q1 || !point_in_frustum(sh.planes, p[k].x, p[k].y, p[k].z)) continue;
@@ -600,7 +611,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         uint32_t pos = base0 + 32 * k + lane;
-        pt[k] = pos < pe ? m.pts[pos] : make_float4(0.f, 0.f, 0.f, __uint_as_float(0xffffffffu));
+        pt[k] = pos < pe ? ld_pt(&m.pts[pos]) : make_float4(0.f, 0.f, 0.f, __uint_as_float(0xffffffffu));
       }
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -809,7 +820,7 @@ __device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const View
     }
   } else {
     for (uint32_t pos = pb; pos < pe; ++pos) {
-      float4 p = m.pts[pos];
+      float4 p = ld_pt(&m.pts[pos]);
       if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
       any = true;
       if (mode == 0) {
@@ -1524,7 +1535,7 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
         const uint32_t u = uf & kVoxMask;
         const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
         for (uint32_t pos = pb; pos < pe; ++pos) {
-          const float4 p = m.pts[pos];
+          const float4 p = ld_pt(&m.pts[pos]);
           if (!(uf & kVoxInside) && !point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
           acc_point(tr, A.acc_scale_d, A.acc_scale_z, p.x, p.y, p.z, acc);
         }

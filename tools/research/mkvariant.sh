@@ -9,5 +9,5 @@ mkdir -p ../lib/variants build
 nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -fmad=false -Xcompiler -fPIC,-ffp-contract=off \
   -I. -I../../include "$@" -c "$src" -o build/kernels_$name.o
 nvcc -gencode arch=compute_100a,code=sm_100a -shared -o ../lib/variants/lib_$name.so build/kernels_$name.o \
-  build/regions.o build/mesh.o build/abi.o build/preprocess.o build/synth.o -lpthread -ldl
+  build/regions.o build/mesh.o build/abi.o build/multi.o build/preprocess.o build/synth.o build/hostloop.o -lpthread -ldl
 echo built asscpp_b200/lib/variants/lib_$name.so
