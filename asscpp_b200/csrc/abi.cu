@@ -84,6 +84,9 @@ struct AsscppCtx {
   uint2* d_chunk_list = nullptr;
   uint32_t *d_vox_list = nullptr, *d_vis_list = nullptr, *d_grid_scratch = nullptr, *d_cov_scratch = nullptr;
   int64_t vis_cap = 0;
+  uint32_t* d_view_cov = nullptr;      // split-group mode: per-view coverage bitsets
+  int64_t view_cov_cap = 0;
+  int64_t split_group_max_views = 4096;
   uint4* d_ray_buf = nullptr;
   int64_t ray_cap = 0;
   int walk_thresh = 16;
@@ -299,12 +302,30 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.grid_scratch = c->d_grid_scratch; a.grid_cap_words = c->grid_cap_words;
   a.cov_scratch = c->d_cov_scratch; a.cov_words = c->cov_words;
   a.group = group; a.cov_direct = (c->m.cov_same && group == 1) ? 1 : 0;
+  a.view_cov = nullptr; a.split_group = 0;
+  // Small grouped batches (the A* use: the sensors of a few dozen children): a group per CTA leaves most SMs idle and
+  // runs the group's views one after the other.  Split-group mode makes every VIEW a work unit; each writes the
+  // coverage-voxel bitset of its visible cloud and group_gain_kernel turns those into the union gains.
+  const int64_t split_max = c->split_group_max_views;
+  if (group > 1 && nviews <= split_max && accum_set < 0) {
+    const int64_t need = nviews * c->cov_words;
+    if (need > c->view_cov_cap) {
+      CU(c, cudaStreamSynchronize(c->stream));
+      cudaFree(c->d_view_cov);
+      c->d_view_cov = nullptr; c->view_cov_cap = 0;
+      int rc = dev_alloc(c, &c->d_view_cov, need, false);
+      if (rc) return rc;
+      c->view_cov_cap = need;
+    }
+    CU(c, cudaMemsetAsync(c->d_view_cov, 0, (size_t)need * 4, c->stream));
+    a.view_cov = c->d_view_cov; a.split_group = group; a.group = 1; a.cov_direct = 0;
+  }
   a.vstate = c->d_vstate;
   a.ordered_list = c->d_ordered_list;
   a.ordered_count = c->d_counters + 1;
   a.smem_grid_words = c->smem_grid_words;
   a.phase_cycles = c->d_phase;
-  int ctas = (int)std::min<int64_t>(c->ctas, (nviews + group - 1) / group);
+  int ctas = (int)std::min<int64_t>(c->ctas, (nviews + a.group - 1) / a.group);
   AsscppCtx::TimedSpan* evp = span_begin(c, 0);
   a.smem_grid_words = c->eval_grid_words;
   launch_eval(a, ctas, c->cta_threads, c->eval_smem_bytes_, c->stream);
@@ -312,6 +333,7 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   span_end(c, evp);
   launch_ordered(a, c->ordered_ctas, c->smem_bytes, c->stream);
   c->launches += 3;
+  if (a.view_cov) { launch_group_gain(a, a.split_group, c->stream); c->launches += 1; }
   CU(c, cudaGetLastError());
   return ASSCPP_OK;
 }
@@ -482,6 +504,7 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = dev_alloc(c, &c->d_ray_buf, 3 * c->ray_cap * 32 * c->ctas))) return fail(rc);
   if (const char* e = getenv("ASSCPP_HALO_ITERS")) c->halo_iters = std::max(0, std::min(64, atoi(e)));
   if (const char* e = getenv("ASSCPP_SETUP_ITERS")) c->setup_iters = std::max(1, std::min(64, atoi(e)));
+  if (const char* e = getenv("ASSCPP_SPLIT_GROUP_MAX")) c->split_group_max_views = std::max(0, atoi(e));
   if (const char* wt = getenv("ASSCPP_WALK_THRESH")) c->walk_thresh = std::max(1, std::min(32, atoi(wt)));
   if ((rc = dev_alloc(c, &c->d_grid_scratch, c->grid_cap_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_cov_scratch, c->cov_words * c->ctas))) return fail(rc);
@@ -507,7 +530,7 @@ int asscpp_destroy(AsscppCtx* c) {
   for (auto& s : c->sets) cudaFree(s.buf);
   cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
   cudaFree(c->d_trig); cudaFree(c->d_acc); cudaFree(c->d_gains);
-  cudaFree(c->d_idx); cudaFree(c->d_cloud); cudaFree(c->d_gather); cudaFree(c->d_cnt);
+  cudaFree(c->d_idx); cudaFree(c->d_cloud); cudaFree(c->d_gather); cudaFree(c->d_cnt); cudaFree(c->d_view_cov);
   for (auto& ev : c->kernel_events) { cudaEventDestroy(ev.e0); cudaEventDestroy(ev.e1); }
   if (c->ev_begin) cudaEventDestroy(c->ev_begin);
   if (c->ev_end) cudaEventDestroy(c->ev_end);

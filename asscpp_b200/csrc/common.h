@@ -101,6 +101,10 @@ struct EvalArgs {
   int setup_iters;           // DDA iterations done in the converged ray setup before a ray is queued
   int group;                 // views per candidate (sensors of one node): cov_scratch is kept across a group
   int cov_direct;            // coverage lattice == occlusion lattice and group == 1: no marks needed
+  uint32_t* view_cov;        // split-group mode (small grouped batches): [nviews][cov_words] coverage-voxel bitset of
+                             // every view's visible cloud; every view is its own work unit and group_gain_kernel
+                             // turns the bitsets into the per-view union gains afterwards.  nullptr: off
+  int split_group;           // views per group in split-group mode (A.group is 1 then)
   uint8_t* vstate;           // [ordered ctas][n_vox] per-voxel state for the ordered (Q5) path
   int32_t* ordered_list;     // views that saw a Q5 carry
   int32_t* ordered_count;

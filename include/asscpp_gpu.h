@@ -130,8 +130,11 @@ int asscpp_eval_batch(AsscppCtx* ctx, const double* poses, int64_t nviews, int c
  * gain_vox of a view counts only coverage voxels that are neither in covered_set nor seen by an earlier view
  * of its group, so the sum over a group is the gain of the union of the sensors' visible clouds
  * (calculateHeuristic's visibleCloud, heuristic.cpp:439-445, scored as :473-483).  gain_pts stays per view.
- * A group containing a view with ASSCPP_VS_ORDERED set (quirk Q5 replay) is not union-exact: score it with
- * asscpp_covered_clone + asscpp_covered_or_views instead. */
+ * Batches of up to 4096 views run in split-group mode: every VIEW is a work unit of its own (a group per CTA would
+ * leave most SMs idle for the few dozen children of an A* expansion), each writes the coverage-voxel bitset of its
+ * visible cloud, and a second small kernel derives the per-view gains; the numbers are the same.  In a larger batch a
+ * group containing a view with ASSCPP_VS_ORDERED set (quirk Q5 replay) is not union-exact: score that group with
+ * asscpp_covered_clone + asscpp_covered_or_views instead (split-group mode is exact there too). */
 int asscpp_eval_groups(AsscppCtx* ctx, const double* poses, int64_t nviews, int group_size, int covered_set,
                        uint32_t flags);
 int asscpp_get_results(AsscppCtx* ctx, AsscppViewResult* out, int64_t nviews); /* synchronises */

@@ -154,11 +154,15 @@ def test_astar_gpu_equals_oracle(oracle_mod, etihad, space_2p5, accumulate):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("model", ["etihad", "synthetic_fine"])
-def test_eval_groups_union_gain(oracle_mod, etihad, space_2p5, model):
+@pytest.mark.parametrize("split", [True, False])
+def test_eval_groups_union_gain(oracle_mod, etihad, space_2p5, model, split, monkeypatch):
     """asscpp_eval_groups: the gain_vox sum of a group = |voxels(union of the group's visible clouds) \\ covered|;
-    every other field equals asscpp_eval_batch's."""
+    every other field equals asscpp_eval_batch's.  Both schedules: a group per CTA (large batches) and split-group
+    mode (batches of up to 4096 views: every view its own work unit, group_gain_kernel afterwards); per view the two
+    give the same numbers."""
     import asscpp_b200 as A
     O = oracle_mod
+    monkeypatch.setenv("ASSCPP_SPLIT_GROUP_MAX", "4096" if split else "0")
     if model == "etihad":
         xyz = etihad[0]
         prm, oprm = A.default_params(), None
@@ -192,6 +196,14 @@ def test_eval_groups_union_gain(oracle_mod, etihad, space_2p5, model):
             assert got[gi] == int((~in_cov[u]).sum()), (group, gi)
         if group == 1:
             assert np.array_equal(res["gain_vox"], plain["gain_vox"])
+        if split:
+            monkeypatch.setenv("ASSCPP_SPLIT_GROUP_MAX", "0")
+            other = A.CoverageContext(xyz, prm)
+            monkeypatch.setenv("ASSCPP_SPLIT_GROUP_MAX", "4096")
+            oc = other.new_set()
+            oc.load(*covered.export())
+            assert np.array_equal(other.eval_groups(poses[:n], group, covered=oc)["gain_vox"], res["gain_vox"]), group
+            other.close()
     assert got.sum() > 0
     # ragged tail (the last group is short), a group larger than the batch, empty batch, bad group size
     r7 = ctx.eval_groups(poses[:7], 3, covered=covered)

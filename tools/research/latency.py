@@ -1,3 +1,6 @@
+"""Small-batch latency of the grouped evaluation (the A* use: the sensors of the children of one expansion).
+Per batch size: wall time per call through host buffers, device time on the context's stream (CUDA events around the
+whole call) and the time of eval_views_kernel itself."""
 import os, sys, time
 import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -7,6 +10,7 @@ g = np.load(os.path.join(ROOT, "tests", "golden", "etihad_model.npz"))
 sp = np.load(os.path.join(ROOT, "tests", "golden", "etihad_searchspace_2p5m.npz"))
 ctx = A.CoverageContext(g["xyz"], A.default_params())
 s = ctx.new_set(); s.or_views(sp["cam0"][600:620], 5)
+print("split-group mode up to %s views" % os.environ.get("ASSCPP_SPLIT_GROUP_MAX", "4096 (default)"))
 for n in (2, 40, 400, 2450):
     poses = np.stack([sp["cam0"][:n // 2], sp["cam1"][:n // 2]], 1).reshape(-1, 7)
     for _ in range(20): ctx.eval_groups(poses, 2, covered=s)
@@ -14,4 +18,12 @@ for n in (2, 40, 400, 2450):
     reps = 300
     for _ in range(reps): ctx.eval_groups(poses, 2, covered=s)
     dt = (time.perf_counter() - t) / reps
-    print("views %5d: %.1f us per call, %.0f VE/s" % (n, dt * 1e6, n / dt))
+    dev, kern = [], []
+    for _ in range(50):
+        ctx.timer_begin()
+        ctx.eval_ex(poses, covered=s, group_size=2)
+        dev.append(ctx.timer_end())
+        kern.append(ctx.eval_kernel_ms()[0])
+        ctx.gains(n)
+    print("views %5d: %.1f us per call, %.0f VE/s; stream %.1f us, eval_views_kernel %.1f us" % (
+        n, dt * 1e6, n / dt, 1e3 * float(np.median(dev)), 1e3 * float(np.median(kern))))
