@@ -125,7 +125,7 @@ SYMBOLS = [
     "asscpp_comm_unique_id", "asscpp_comm_init", "asscpp_allgather_results", "asscpp_allreduce_or",
     "asscpp_comm_destroy", "asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor",
     "asscpp_frustum_planes", "asscpp_get_accuracy", "asscpp_pose_rpy", "asscpp_viewport_transform",
-    "asscpp_uncovered_voxels", "asscpp_uncovered_voxels_ex", "asscpp_uncovered_clusters",
+    "asscpp_uncovered_voxels", "asscpp_uncovered_voxels_ex", "asscpp_uncovered_clusters", "asscpp_uncovered_ids_noalloc",
     "asscpp_eval_groups", "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
     "asscpp_mesh_last_error", "asscpp_mesh_filter", "asscpp_mesh_segments_free",
     "asscpp_covered_or_cloud", "asscpp_covered_invert_voxels", "asscpp_comm_init_all",
@@ -212,6 +212,7 @@ def load():
         "asscpp_mesh_segments_free": (i32, [vp, f64p, f64p, i64, u8p]),
         "asscpp_uncovered_voxels": (i32, [vp, i32, i32p, f32p, i64, i64p]),
         "asscpp_uncovered_voxels_ex": (i32, [vp, i32, C.c_uint32, i32p, f32p, i64, i64p]),
+        "asscpp_uncovered_ids_noalloc": (i32, [vp, i64, vp, i64, vp, vp, C.c_char_p, i64]),
         "asscpp_uncovered_clusters": (i32, [vp, i32, C.c_double, C.c_int32, C.c_int32, i32p, vp, i64, i64p]),
         "asscpp_comm_init_all": (i32, [C.POINTER(vp), i32]),
         "asscpp_multi_create": (i32, [i32p, i32, f32p, i64, C.POINTER(Params), C.POINTER(vp)]),

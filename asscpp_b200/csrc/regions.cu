@@ -7,7 +7,11 @@
 // reference's scan order); a covered set is one bit per compact id.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <climits>
+#include <cstdio>
+
+#include "../../include/asscpp_gpu.h"
 
 #include "common.h"
 #include "kernels.h"
@@ -244,6 +248,22 @@ void launch_covered_alias(const uint32_t* vox_bits, uint32_t* out_bits, int64_t 
   covered_alias_kernel<<<grid_for(n_cov), 256, 0, s>>>(vox_bits, out_bits, n_cov, (const long long*)keys, dv, box6);
 }
 
+// ---- allocation-free variant of the uncovered-id extraction (asscpp_uncovered_ids_noalloc) ------------------------
+// No counterpart in the reference; see include/asscpp_gpu.h.  The per-word counts / offsets the count -> scan -> emit
+// kernels need live in this file-scope array instead of a cudaMalloc'ed buffer; every GPU that loads the library holds
+// it until exit (ASSCPP_NOALLOC_MAX_VOXELS / 32 + 1 words).  g_noalloc_scratch is a host-side stand-in for the symbol
+// here: host code only ever uses the device address cudaGetSymbolAddress returns, fetched once per device.
+__device__ __align__(256) static int32_t g_noalloc_scratch[ASSCPP_NOALLOC_MAX_VOXELS / 32 + 1];
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::atomic<int32_t*> g_noalloc_ptr[kNoallocMaxDevices];
+
+void noalloc_error(char* err, int64_t err_len, const char* fmt, long long a, long long b, const char* text) {
+  if (err && err_len > 0) std::snprintf(err, (size_t)err_len, fmt, a, b, text ? text : "");
+}
+}  // namespace
+
 void launch_clusters(const uint32_t* vox_bits, int64_t n_cov, const int64_t* keys, const int32_t cmin[3],
                      const int32_t cdiv[3], const int3* offs, int noffs, int32_t* parent, int32_t* root, int32_t* size,
                      int32_t* box, cudaStream_t s) {
@@ -257,3 +277,52 @@ void launch_clusters(const uint32_t* vox_bits, int64_t n_cov, const int64_t* key
 }
 
 }  // namespace asscpp
+
+// include/asscpp_gpu.h: no cudaMalloc / cudaFree / allocating routine on this path, nothing synchronises; the three
+// launches go on the caller's stream and leave ids + count in the caller's device buffers.
+extern "C" int asscpp_uncovered_ids_noalloc(const uint32_t* d_voxel_bits, int64_t n_voxels, int32_t* d_ids, int64_t cap,
+                                            int64_t* d_count, void* stream, char* err, int64_t err_len) {
+  using namespace asscpp;
+  if (err && err_len > 0) err[0] = 0;
+  if (n_voxels < 0 || cap < 0 || !d_count || (n_voxels > 0 && !d_voxel_bits) || (cap > 0 && !d_ids)) {
+    noalloc_error(err, err_len, "asscpp_uncovered_ids_noalloc: bad argument (n_voxels %lld, cap %lld)%s", n_voxels, cap, "");
+    return ASSCPP_EINVAL;
+  }
+  if (n_voxels > (int64_t)ASSCPP_NOALLOC_MAX_VOXELS) {
+    noalloc_error(err, err_len, "asscpp_uncovered_ids_noalloc: n_voxels %lld exceeds ASSCPP_NOALLOC_MAX_VOXELS %lld%s", n_voxels,
+                  (long long)ASSCPP_NOALLOC_MAX_VOXELS, "");
+    return ASSCPP_ERANGE;
+  }
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kNoallocMaxDevices) {
+    noalloc_error(err, err_len, "asscpp_uncovered_ids_noalloc: cudaGetDevice -> %lld (device %lld) %s", (long long)e, dev,
+                  e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
+    return e != cudaSuccess ? ASSCPP_ECUDA : ASSCPP_ERANGE;
+  }
+  // set-up, once per device, with that device current: the device address of the scratch array
+  int32_t* scratch = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+  if (!scratch) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      noalloc_error(err, err_len, "asscpp_uncovered_ids_noalloc: cudaGetSymbolAddress -> %lld (device %lld) %s", (long long)e, dev,
+                    cudaGetErrorString(e));
+      return ASSCPP_ECUDA;
+    }
+    scratch = (int32_t*)p;
+    g_noalloc_ptr[dev].store(scratch, std::memory_order_release);
+  }
+  // every word of the scratch the emit kernel reads is rewritten by the count + scan kernels of this call and
+  // *d_count is written by the scan kernel (or the memset below): nothing has to start at zero
+  const int32_t zero3[3] = {0, 0, 0}, one3[3] = {1, 1, 1};
+  launch_uncovered(d_voxel_bits, n_voxels, scratch, d_count, nullptr, zero3, one3, 0.0f, d_ids, nullptr, cap,
+                   (cudaStream_t)stream);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    noalloc_error(err, err_len, "asscpp_uncovered_ids_noalloc: launch -> %lld (device %lld) %s", (long long)e, dev,
+                  cudaGetErrorString(e));
+    return ASSCPP_ECUDA;
+  }
+  return ASSCPP_OK;
+}

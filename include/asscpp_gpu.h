@@ -211,6 +211,25 @@ enum { ASSCPP_DIFF_PCL_ALIASING = 1u };
 int asscpp_uncovered_voxels_ex(AsscppCtx* ctx, int set, uint32_t flags, int32_t* ids, float* centres_xyz, int64_t cap,
                                int64_t* n_out);
 
+/* Allocation-free variant of the uncovered-id extraction.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  The count -> scan -> emit kernels of asscpp_uncovered_voxels run with their per-word
+ * offsets in a static device array of ASSCPP_NOALLOC_MAX_VOXELS / 32 + 1 int32 (1 MiB, held by every GPU that loads
+ * the library until exit) instead of a context buffer; the call needs no context, allocates nothing (no cudaMalloc,
+ * cudaFree or allocating library routine) and does not synchronise.
+ *   d_voxel_bits  DEVICE pointer, (n_voxels + 31) / 32 words: bit i set = voxel i covered (the voxel bitset of
+ *                 asscpp_covered_export, as 32-bit words)
+ *   d_ids         DEVICE pointer, cap entries: the ids whose bit is clear, ascending (at most cap are written)
+ *   d_count       DEVICE pointer to one int64: the full count of clear bits
+ *   stream        cudaStream_t of the CURRENT device the three launches go on (NULL = default stream)
+ *   err, err_len  optional host buffer that receives the error text
+ * n_voxels > ASSCPP_NOALLOC_MAX_VOXELS is refused with ASSCPP_ERANGE.  All calls on a device share the one array:
+ * calls that overlap on the GPU (different streams, or threads launching concurrently) race; calls on one stream,
+ * or otherwise ordered, do not.  Nothing in the array has to start at zero: each call rewrites every word it reads. */
+#define ASSCPP_NOALLOC_MAX_VOXELS (1 << 23)
+int asscpp_uncovered_ids_noalloc(const uint32_t* d_voxel_bits, int64_t n_voxels, int32_t* d_ids, int64_t cap,
+                                 int64_t* d_count, void* stream, char* err, int64_t err_len);
+
 /* clusteringPointCloud (:147-190, pcl::EuclideanClusterExtraction: tolerance 0.8, sizes 5..50000 in the reference)
  * over those voxel centres + findClusterBB (:218-246) per cluster.  Clusters come largest first (equal sizes: by
  * smallest member id).  labels: n_cov_voxels entries, cluster index or -1 (covered, or cluster size out of range);
