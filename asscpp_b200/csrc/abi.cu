@@ -87,6 +87,25 @@ struct AsscppCtx {
   uint32_t* d_view_cov = nullptr;      // split-group mode: per-view coverage bitsets
   int64_t view_cov_cap = 0;
   int64_t split_group_max_views = 4096;
+  // small batches (at most kSmallMaxViews views, host poses, no accumulator, no communicator): ONE launch per evaluation
+  // (eval_views_small_kernel); gains and counters are mirrored into mapped host memory, so reading the gains back is a
+  // stream synchronisation and nothing else.  A view that needs the ordered replay (quirk Q5) sends the whole batch
+  // through the general path when its results are asked for (finalize_small).
+  struct SmallHost {
+    uint2 gains[kSmallMaxViews];
+    int32_t counters[4];
+    ViewTrig trig[kSmallMaxViews];
+    AsscppViewResult results[kSmallMaxViews];
+    AccRaw acc[kSmallMaxViews];
+  };
+  SmallHost* h_small = nullptr;  // cudaHostAlloc, mapped
+  SmallHost* d_small = nullptr;  // the same memory as the device sees it
+  uint32_t* d_group_ticket = nullptr;
+  bool small_enabled = true, small_pending = false, small_valid = false, counters_clean = false;
+  std::vector<double> small_poses;
+  int small_covered = -1, small_group = 1;
+  uint32_t small_flags = 0;
+  int64_t small_launches = 0, small_fallbacks = 0;
   uint4* d_ray_buf = nullptr;
   int64_t ray_cap = 0;
   int walk_thresh = 16;
@@ -246,9 +265,15 @@ void span_end(AsscppCtx* c, AsscppCtx::TimedSpan* t) {
   if (t) cudaEventRecord(t->e1, c->stream);
 }
 
+bool takes_small_path(const AsscppCtx* c, int64_t nviews, int accum_set, int group, const double* h_poses) {
+  return c->small_enabled && c->h_small && h_poses && !c->comm && nviews > 0 && nviews <= kSmallMaxViews && accum_set < 0 &&
+         (group == 1 || (group > 1 && group <= kSmallMaxGroup && nviews <= c->split_group_max_views));
+}
+
 // planes -> eval -> ordered, all on the context's stream
 int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_set, int accum_set,
-             int64_t accum_min_visible, uint32_t flags, const double* h_poses = nullptr, int group = 1) {
+             int64_t accum_min_visible, uint32_t flags, const double* h_poses = nullptr, int group = 1,
+             bool allow_small = true) {
   if (nviews < 0 || nviews > 0x7fffffffLL) { c->err = "nviews out of range"; return ASSCPP_EINVAL; }
   if (group < 1) { c->err = "group size must be at least 1"; return ASSCPP_EINVAL; }
   if (covered_set != -1 && !valid_set(c, covered_set)) { c->err = "bad covered set handle"; return ASSCPP_EINVAL; }
@@ -259,8 +284,15 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   }
   c->last_nviews = nviews;
   c->last_had_acc = (flags & ASSCPP_EVAL_ACCURACY) != 0;
+  c->small_pending = false; c->small_valid = false;
   if (nviews == 0) return ASSCPP_OK;
-  if (flags & ASSCPP_EVAL_ACCURACY) {
+  const bool small = allow_small && takes_small_path(c, nviews, accum_set, group, h_poses);
+  if (small) {
+    if (flags & ASSCPP_EVAL_ACCURACY) {
+      CU(c, cudaStreamSynchronize(c->stream));  // the previous small batch may still be reading the mapped constants
+      for (int64_t v = 0; v < nviews; ++v) viewport_trig_host(h_poses + 7 * v, &c->h_small->trig[(size_t)v]);
+    }
+  } else if (flags & ASSCPP_EVAL_ACCURACY) {
     if (h_poses) {
       // yaw / pitch and their sines and cosines with the host's libm, as the reference computes them
       // (occlusion_culling.cpp:556-584)
@@ -274,8 +306,9 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
       c->launches += 1;
     }
   }
-  CU(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(int32_t), c->stream));
-  launch_planes(d_poses, nviews, c->fc, c->d_views, c->stream);
+  if (!small || !c->counters_clean) CU(c, cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(int32_t), c->stream));
+  c->counters_clean = small;  // the small kernel leaves them zeroed
+  if (!small) launch_planes(d_poses, nviews, c->fc, c->d_views, c->stream);
   EvalArgs a;
   a.m = c->m;
   a.views = c->d_views;
@@ -290,8 +323,15 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   if (accum_set >= 0) a.accum = set_dev(c, accum_set);
   a.accum_min_visible = accum_min_visible;
   a.flags = flags;
-  a.trig = c->d_trig;
+  a.trig = small ? c->d_small->trig : c->d_trig;
   a.acc = (flags & ASSCPP_EVAL_ACCURACY) ? c->d_acc : nullptr;
+  a.small = small ? 1 : 0;
+  a.fc = c->fc;
+  a.host_gains = small ? c->d_small->gains : nullptr;
+  a.host_counters = small ? c->d_small->counters : nullptr;
+  a.host_results = small ? c->d_small->results : nullptr;
+  a.host_acc = small ? c->d_small->acc : nullptr;
+  a.group_ticket = c->d_group_ticket;
   a.acc_scale_d = c->acc_scale_d; a.acc_scale_z = c->acc_scale_z;
   a.chunk_list = c->d_chunk_list; a.chunk_cap = c->chunk_cap;
   a.vox_list = c->d_vox_list; a.list_cap = c->list_cap;
@@ -317,7 +357,7 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
       if (rc) return rc;
       c->view_cov_cap = need;
     }
-    CU(c, cudaMemsetAsync(c->d_view_cov, 0, (size_t)need * 4, c->stream));
+    if (!small) CU(c, cudaMemsetAsync(c->d_view_cov, 0, (size_t)need * 4, c->stream));  // small: every CTA clears its view's row
     a.view_cov = c->d_view_cov; a.split_group = group; a.group = 1; a.cov_direct = 0;
   }
   a.vstate = c->d_vstate;
@@ -328,6 +368,17 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   int ctas = (int)std::min<int64_t>(c->ctas, (nviews + a.group - 1) / a.group);
   AsscppCtx::TimedSpan* evp = span_begin(c, 0);
   a.smem_grid_words = c->eval_grid_words;
+  if (small) {
+    launch_eval_small(a, h_poses, ctas, c->cta_threads, c->eval_smem_bytes_, c->stream);
+    span_end(c, evp);
+    c->launches += 1;
+    c->small_launches += 1;
+    CU(c, cudaGetLastError());
+    c->small_poses.assign(h_poses, h_poses + 7 * nviews);
+    c->small_covered = covered_set; c->small_group = group; c->small_flags = flags;
+    c->small_pending = true;
+    return ASSCPP_OK;
+  }
   launch_eval(a, ctas, c->cta_threads, c->eval_smem_bytes_, c->stream);
   a.smem_grid_words = c->smem_grid_words;
   span_end(c, evp);
@@ -338,14 +389,37 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   return ASSCPP_OK;
 }
 
+// Before anything reads the results of the last evaluation: a small batch is complete once the stream has drained and
+// no view asked for the ordered replay; otherwise the batch is evaluated again by the general path.
+int finalize_small(AsscppCtx* c) {
+  if (!c->small_pending) return ASSCPP_OK;
+  CU(c, cudaStreamSynchronize(c->stream));
+  c->small_pending = false;
+  if (c->h_small->counters[0] == 0) { c->small_valid = true; return ASSCPP_OK; }
+  c->small_fallbacks += 1;
+  const int64_t n = (int64_t)(c->small_poses.size() / 7);
+  std::vector<double> poses;
+  poses.swap(c->small_poses);
+  CU(c, cudaMemcpyAsync(c->d_poses, poses.data(), poses.size() * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+  int rc = run_eval(c, c->d_poses, n, c->small_covered, -1, 0, c->small_flags, poses.data(), c->small_group, false);
+  if (rc) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));  // poses (pageable) and the trig constants go out of scope
+  return ASSCPP_OK;
+}
+
 int fetch_results(AsscppCtx* c, int64_t nviews) {
   if (c->last_nviews < 0) { c->err = "no evaluation has been issued"; return ASSCPP_ESTATE; }
   if (nviews > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
+  if (int rc = finalize_small(c)) return rc;
   c->h_results.resize((size_t)std::max<int64_t>(nviews, 1));
-  if (nviews > 0)
-    CU(c, cudaMemcpyAsync(c->h_results.data(), c->d_results, (size_t)nviews * sizeof(AsscppViewResult),
-                          cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaStreamSynchronize(c->stream));
+  if (c->small_valid) {  // mirrored into mapped host memory by the kernel, which has finished
+    if (nviews > 0) memcpy(c->h_results.data(), c->h_small->results, (size_t)nviews * sizeof(AsscppViewResult));
+  } else {
+    if (nviews > 0)
+      CU(c, cudaMemcpyAsync(c->h_results.data(), c->d_results, (size_t)nviews * sizeof(AsscppViewResult),
+                            cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+  }
   for (int64_t v = 0; v < nviews; ++v)
     if (c->h_results[v].status & kVsError) { c->err = "internal scratch bound violated for a view"; return ASSCPP_ERANGE; }
   return ASSCPP_OK;
@@ -510,6 +584,24 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = dev_alloc(c, &c->d_cov_scratch, c->cov_words * c->ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_vstate, std::max<int64_t>(m.n_vox, 1) * c->ordered_ctas))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_counters, 4))) return fail(rc);
+  cudaMemsetAsync(c->d_counters, 0, 4 * sizeof(int32_t), c->stream);
+  c->counters_clean = true;
+  if ((rc = dev_alloc(c, &c->d_group_ticket, kSmallMaxViews))) return fail(rc);
+  cudaMemsetAsync(c->d_group_ticket, 0, kSmallMaxViews * sizeof(uint32_t), c->stream);
+  if (getenv("ASSCPP_NO_SMALL")) c->small_enabled = false;
+  {
+    void* hp = nullptr;
+    void* dp = nullptr;
+    if (cudaHostAlloc(&hp, sizeof(AsscppCtx::SmallHost), cudaHostAllocMapped) == cudaSuccess &&
+        cudaHostGetDevicePointer(&dp, hp, 0) == cudaSuccess) {
+      memset(hp, 0, sizeof(AsscppCtx::SmallHost));
+      c->h_small = (AsscppCtx::SmallHost*)hp;
+      c->d_small = (AsscppCtx::SmallHost*)dp;
+    } else {
+      if (hp) cudaFreeHost(hp);
+      cudaGetLastError();  // no mapped host memory: the general path serves small batches too
+    }
+  }
   if ((rc = dev_alloc(c, &c->d_pop, 2))) return fail(rc);
   if ((rc = dev_alloc(c, &c->d_tmp_bits, c->pts_words))) return fail(rc);
   cudaMemsetAsync(c->d_cov_scratch, 0, (size_t)c->cov_words * c->ctas * 4, c->stream);
@@ -526,6 +618,7 @@ int asscpp_destroy(AsscppCtx* c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(c->comm);
+  if (c->h_small) cudaFreeHost(c->h_small);
   for (void* p : c->allocs) cudaFree(p);
   for (auto& s : c->sets) cudaFree(s.buf);
   cudaFree(c->d_poses); cudaFree(c->d_views); cudaFree(c->d_results); cudaFree(c->d_ordered_list);
@@ -565,7 +658,7 @@ int asscpp_eval_batch(AsscppCtx* c, const double* poses, int64_t nviews, int cov
   cudaSetDevice(c->device);
   int rc = ensure_views(c, nviews);
   if (rc) return rc;
-  if (nviews > 0)
+  if (nviews > 0 && !takes_small_path(c, nviews, -1, 1, poses))
     CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   return run_eval(c, c->d_poses, nviews, covered_set, -1, 0, flags, poses);
 }
@@ -576,7 +669,7 @@ int asscpp_eval_groups(AsscppCtx* c, const double* poses, int64_t nviews, int gr
   cudaSetDevice(c->device);
   int rc = ensure_views(c, nviews);
   if (rc) return rc;
-  if (nviews > 0)
+  if (nviews > 0 && !takes_small_path(c, nviews, -1, group_size, poses))
     CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   return run_eval(c, c->d_poses, nviews, covered_set, -1, 0, flags, poses, group_size);
 }
@@ -595,10 +688,15 @@ int asscpp_get_accuracy(AsscppCtx* c, AsscppViewAccuracy* out, int64_t nviews) {
   cudaSetDevice(c->device);
   if (c->last_nviews < 0 || !c->last_had_acc) { c->err = "the last evaluation was not issued with ASSCPP_EVAL_ACCURACY"; return ASSCPP_ESTATE; }
   if (nviews > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
+  if (int rc = finalize_small(c)) return rc;
   c->h_acc.resize((size_t)std::max<int64_t>(nviews, 1));
-  if (nviews > 0)
-    CU(c, cudaMemcpyAsync(c->h_acc.data(), c->d_acc, (size_t)nviews * sizeof(AccRaw), cudaMemcpyDeviceToHost, c->stream));
-  CU(c, cudaStreamSynchronize(c->stream));
+  if (c->small_valid) {
+    if (nviews > 0) memcpy(c->h_acc.data(), c->h_small->acc, (size_t)nviews * sizeof(AccRaw));
+  } else {
+    if (nviews > 0)
+      CU(c, cudaMemcpyAsync(c->h_acc.data(), c->d_acc, (size_t)nviews * sizeof(AccRaw), cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+  }
   auto decode = [](unsigned long long hi, unsigned long long lo, double scale) {
     unsigned __int128 t = ((unsigned __int128)hi << 32) + lo;  // exact sum of the scaled terms
     return (double)t / scale;                                  // one rounding; the division by 2^S is exact
@@ -651,7 +749,18 @@ int asscpp_get_gain(AsscppCtx* c, uint32_t* gain_pts, uint32_t* gain_vox, int64_
   cudaSetDevice(c->device);
   if (c->last_nviews < 0) { c->err = "no evaluation has been issued"; return ASSCPP_ESTATE; }
   if (nviews > c->last_nviews) { c->err = "more results requested than views evaluated"; return ASSCPP_EINVAL; }
-  int rc = fetch_gains(c, c->d_gains, nviews);
+  int rc = finalize_small(c);
+  if (rc) return rc;
+  if (c->small_valid) {
+    // the kernel wrote the gains and the counters into mapped host memory: nothing to copy
+    if (c->h_small->counters[1]) { c->err = "internal scratch bound violated for a view"; return ASSCPP_ERANGE; }
+    for (int64_t v = 0; v < nviews; ++v) {
+      if (gain_pts) gain_pts[v] = c->h_small->gains[(size_t)v].x;
+      if (gain_vox) gain_vox[v] = c->h_small->gains[(size_t)v].y;
+    }
+    return ASSCPP_OK;
+  }
+  rc = fetch_gains(c, c->d_gains, nviews);
   if (rc) return rc;
   for (int64_t v = 0; v < nviews; ++v) {
     if (gain_pts) gain_pts[v] = c->h_gains[(size_t)v].x;
@@ -668,7 +777,7 @@ int asscpp_eval_ex(AsscppCtx* c, const double* poses, int64_t nviews, const Assc
   const int group = o->group_size > 0 ? o->group_size : 1;
   if (o->poses_on_device)
     return run_eval(c, poses, nviews, o->covered_set, o->accum_set, o->accum_min_visible, o->flags, nullptr, group);
-  if (nviews > 0)
+  if (nviews > 0 && !takes_small_path(c, nviews, o->accum_set, group, poses))
     CU(c, cudaMemcpyAsync(c->d_poses, poses, (size_t)nviews * 7 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
   return run_eval(c, c->d_poses, nviews, o->covered_set, o->accum_set, o->accum_min_visible, o->flags, poses, group);
 }

@@ -68,6 +68,9 @@ struct CoveredDev {
   uint32_t* vox;  // bit per compact coverage id
 };
 
+constexpr int kSmallMaxViews = 512;   // most views eval_views_small_kernel takes (poses are kernel parameters)
+constexpr int kSmallMaxGroup = 8;     // largest group whose union gains it computes in the kernel
+
 struct EvalArgs {
   ModelDev m;
   const ViewDev* views;
@@ -109,6 +112,16 @@ struct EvalArgs {
   int32_t* ordered_list;     // views that saw a Q5 carry
   int32_t* ordered_count;
   uint32_t smem_grid_words;  // capacity of the shared-memory grid
+  // small batches (the A* use), one launch for the whole evaluation: poses arrive as kernel parameters and the planes are
+  // computed by the CTA that takes the view; the last view of a group to finish computes the group's union gains; gains
+  // and counters are mirrored into mapped host memory; the last CTA resets the device counters for the next launch
+  int small;                 // 1: eval_views_small_kernel
+  FrustumConst fc;
+  uint2* host_gains;         // [nviews] mapped host mirror of gains
+  AsscppViewResult* host_results;  // [nviews] ... of results
+  AccRaw* host_acc;          // [nviews] ... of acc (ASSCPP_EVAL_ACCURACY)
+  int32_t* host_counters;    // mapped: {views that need the ordered replay, views with a scratch error}
+  uint32_t* group_ticket;    // [groups] views of the group that have finished (wraps to 0 by itself)
   unsigned long long* phase_cycles;  // optional profiling counters (nullptr: off)
 };
 

@@ -19,6 +19,7 @@
 #include <cuda_runtime.h>
 
 #include <cmath>
+#include <cstring>
 
 #include "common.h"
 #include "kernels.h"
@@ -98,11 +99,7 @@ __device__ __forceinline__ bool box_inside(const float* pl, float lx, float ly, 
 // planes_kernel: one thread per pose.  Double part = <tf Matrix3x3::setRotation>; float part =
 // frustum_culling.cpp:97-141 with the operation order of SURVEY.md A.2.
 // ------------------------------------------------------------------------------------------------
-__global__ void planes_kernel(const double* __restrict__ poses, int64_t nviews, FrustumConst fc,
-                              ViewDev* __restrict__ views) {
-  int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (v >= nviews) return;
-  const double* ps = poses + 7 * v;
+__device__ __forceinline__ void compute_view(const double* __restrict__ ps, const FrustumConst& fc, ViewDev& out) {
   double x = ps[3], y = ps[4], z = ps[5], w = ps[6];
   double d = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn(x, x), __dmul_rn(y, y)), __dmul_rn(z, z)), __dmul_rn(w, w));
   double s = __ddiv_rn(2.0, d);
@@ -134,7 +131,6 @@ __global__ void planes_kernel(const double* __restrict__ poses, int64_t nviews, 
   auto ndot = [](const float* a, const float* b) {
     return -fadd(fmul(a[0], b[0]), fadd(fmul(a[1], b[1]), fmul(a[2], b[2])));
   };
-  ViewDev out;
   float *pl_l = out.planes, *pl_r = out.planes + 4, *pl_t = out.planes + 8, *pl_b = out.planes + 12,
         *pl_f = out.planes + 16, *pl_n = out.planes + 20;
   float e1[3], e2[3], a[3], b[3], cc[3], dd[3];
@@ -152,6 +148,15 @@ __global__ void planes_kernel(const double* __restrict__ poses, int64_t nviews, 
   pl_r[3] = ndot(T, pl_r); pl_l[3] = ndot(T, pl_l); pl_t[3] = ndot(T, pl_t); pl_b[3] = ndot(T, pl_b);
   out.origin[0] = T[0]; out.origin[1] = T[1]; out.origin[2] = T[2];
   out.pad = 0.0f;
+}
+
+
+__global__ void planes_kernel(const double* __restrict__ poses, int64_t nviews, FrustumConst fc,
+                              ViewDev* __restrict__ views) {
+  int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= nviews) return;
+  ViewDev out;
+  compute_view(poses + 7 * v, fc, out);
   views[v] = out;
 }
 
@@ -192,6 +197,10 @@ __device__ __forceinline__ uint32_t grid_load(const GridMem& gm, unsigned w) {
 }
 
 constexpr unsigned kDescShared = 1024;
+// A voxel with at least this many points is not walked by one lane (a chain of dependent loads, one point after the
+// other): it is set aside and the points are tested 32 at a time by a whole warp (coarse lattices hold hundreds of
+// points per voxel; with few voxels per view that chain was most of a small batch's latency).
+constexpr uint32_t kCoopMinPoints = 8;
 
 struct ViewShared {
   float planes[24];
@@ -203,11 +212,12 @@ struct ViewShared {
   int view;
   int use_smem;
   unsigned long long cand_state;  // cull: descriptors handed out (high word) | candidate voxels so far (low word)
-  unsigned chunk_count, chunk_next, super_count, list_count, vis_count, ray_next, ray_count;
+  unsigned big_count, chunk_next, super_count, list_count, vis_count, ray_next, big_next;  // big_*: voxels handled one warp per voxel
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
   unsigned long long acc[4];  // accuracy: fixed-point sums (depth hi / lo, z hi / lo)
   int acc_min, acc_max;       // accuracy: ordered-int keys of the depth extrema
+  ViewTrig trig;              // accuracy: the view's transform constants, fetched while the cull runs
   int seg_last[1024];  // ordered path; cull: list of surviving super-chunks
   uint2 chunk_desc[kDescShared];  // cull: candidate chunk descriptors (the rest spill to the global chunk list)
 };
@@ -467,12 +477,14 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         const unsigned i = i0 + lane;
         unsigned cnt = 0;
         uint32_t u = 0;
+        bool big = false;
         if (i < ncut) {
           u = __ldcg(cut + i);
           const int4 vx = m.vox[u];
           const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
+          big = q1 - q0 >= kCoopMinPoints;
           // the points of a voxel four at a time: the loads, not the plane tests, are what this loop waits for
-          for (uint32_t qb = q0; qb < q1; qb += 4) {
+          for (uint32_t qb = q0; qb < q1 && !big; qb += 4) {
             float4 p[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) p[k] = ld_pt(&m.pts[min(qb + k, q1 - 1)]);
@@ -490,6 +502,14 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           }
         }
         emit_voxels(cnt != 0, u);
+        // voxels with many points: set aside for the whole CTA (one warp per voxel, below), from the top of the list
+        const unsigned bb = __ballot_sync(0xffffffffu, big);
+        if (bb) {
+          unsigned base = 0;
+          if (lane == 0) base = atomicAdd(&sh.big_count, (unsigned)__popc(bb));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (big) __stcg(vox_list + (A.list_cap - 1 - (int64_t)(base + __popc(bb & ((1u << lane) - 1)))), u);
+        }
       }
       ncut = 0;
       __syncwarp();
@@ -588,6 +608,36 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     const long long d1 = prof2 ? clock64() : 0;
     if (prof2) atomicAdd(&A.phase_cycles[10], (unsigned long long)ncut);
     flush_cut();
+    // the cut voxels with many points, one warp per voxel, 64 points in flight per warp
+    __syncthreads();
+    const unsigned nbig = sh.big_count;
+    for (unsigned i = warp; i < nbig; i += nwarps) {
+      const uint32_t u = __ldcg(vox_list + (A.list_cap - 1 - (int64_t)i));
+      const int4 vx = m.vox[u];
+      const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
+      unsigned c = 0;
+      for (uint32_t qb = q0; qb < q1; qb += 64) {
+        const uint32_t qa = qb + lane, qc = qa + 32;
+        const bool oa = qa < q1, oc = qc < q1;
+        float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pc = pa;
+        if (oa) pa = ld_pt(&m.pts[qa]);
+        if (oc) pc = ld_pt(&m.pts[qc]);
+        const bool ia = oa && point_in_frustum(sh.planes, pa.x, pa.y, pa.z);
+        const bool ic = oc && point_in_frustum(sh.planes, pc.x, pc.y, pc.z);
+        if (want_hash) {
+          if (ia) shash += mix64((uint64_t)(uint32_t)m.orig[qa]);
+          if (ic) shash += mix64((uint64_t)(uint32_t)m.orig[qc]);
+        }
+        c += (unsigned)__popc(__ballot_sync(0xffffffffu, ia)) + (unsigned)__popc(__ballot_sync(0xffffffffu, ic));
+      }
+      if (c && lane == 0) {
+        surv_in += c;
+        bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
+        bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
+        const unsigned at = atomicAdd(&sh.list_count, 1u);
+        if (at < A.list_cap) vox_list[at] = u;
+      }
+    }
     if (prof2) {
       atomicAdd(&A.phase_cycles[8], (unsigned long long)(d1 - d0));
       atomicAdd(&A.phase_cycles[9], (unsigned long long)(clock64() - d1));
@@ -683,6 +733,7 @@ __device__ __forceinline__ bool build_grid(const EvalArgs& A, ViewShared& sh, ui
                            uint32_t* vox_list, GridMem* gm_out) {
   const ModelDev& m = A.m;
   if (threadIdx.x == 0) {
+    sh.big_count = 0;  // the cull's list of many-point voxels is done with; P4b starts its own
     GridView& g = sh.g;
     g.leaf = m.leaf; g.inv = m.inv_leaf; g.half = m.half_leaf; g.thr_sq = m.dist_thr_sq;
     unsigned long long cells = 1, pcells = 1;
@@ -701,10 +752,13 @@ __device__ __forceinline__ bool build_grid(const EvalArgs& A, ViewShared& sh, ui
     g.mul2 = g.div[0] * g.div[1];
     g.cells = (unsigned)cells;
     g.P0 = g.div[0] + 4; g.P1 = g.div[1] + 4; g.P2 = g.div[2] + 4; g.P01 = g.P0 * g.P1;
-    g.mP0 = (unsigned)(0x100000000ull / (unsigned long long)g.P0);
-    g.mP01 = (unsigned)(0x100000000ull / (unsigned long long)g.P01);
-    g.mD0 = g.mul1 > 1 ? (unsigned)(0x100000000ull / (unsigned long long)g.mul1) : 0xffffffffu;
-    g.mD01 = g.mul2 > 1 ? (unsigned)(0x100000000ull / (unsigned long long)g.mul2) : 0xffffffffu;
+    // floor(2^32 / d) for d >= 2 in 32-bit arithmetic (a 64-bit division is several hundred cycles on this
+    // one-thread path): floor((2^32 - 1) / d), plus one when the remainder is d - 1
+    auto inv32 = [](unsigned d) { const unsigned q = 0xffffffffu / d; return q + ((0xffffffffu - q * d) == d - 1u ? 1u : 0u); };
+    g.mP0 = inv32((unsigned)g.P0);
+    g.mP01 = inv32((unsigned)g.P01);
+    g.mD0 = g.mul1 > 1 ? inv32((unsigned)g.mul1) : 0xffffffffu;
+    g.mD01 = g.mul2 > 1 ? inv32((unsigned)g.mul2) : 0xffffffffu;
     unsigned long long words = (pcells + 31) / 32;
     sh.words = (unsigned)words;
     bool fits_smem = words <= A.smem_grid_words && !(A.flags & ASSCPP_EVAL_FORCE_GLOBAL);
@@ -1360,6 +1414,76 @@ __device__ __forceinline__ void acc_commit(ViewShared& sh, AccLocal& a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// One warp, one voxel (every lane passes the same entry): visit_voxel_points with the points taken 32 at a time, four
+// loads in flight per lane.  MODE 0: counts / gains / hash; 1: OR into A.accum; 2: accuracy terms.
+// ------------------------------------------------------------------------------------------------
+template <int MODE>
+__device__ __forceinline__ void visit_voxel_warp(const EvalArgs& A, const ViewShared& sh, uint32_t uf, uint32_t* cov_scratch,
+                                                 unsigned& vis, unsigned& gain_p, unsigned& gain_v,
+                                                 unsigned long long& vhash, const ViewTrig* tr, AccLocal* acc) {
+  const ModelDev& m = A.m;
+  const int lane = threadIdx.x & 31;
+  const uint32_t u = uf & kVoxMask;
+  const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
+  const bool inside = (uf & kVoxInside) != 0;  // every point of the voxel passed the frustum test
+  const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
+  const int32_t vcov = MODE == 2 ? 0 : m.vox_cov[u];
+  bool any = false;
+  constexpr int K = 4;
+  for (uint32_t p0 = pb; p0 < pe; p0 += 32 * K) {
+    float4 p[K];
+    bool in[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const uint32_t pos = p0 + 32 * k + lane;
+      in[k] = pos < pe;
+      p[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (in[k] && (!inside || MODE == 2)) p[k] = ld_pt(&m.pts[pos]);
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      if (p0 + 32 * k >= pe) break;  // warp-uniform
+      const uint32_t pos = p0 + 32 * k + lane;
+      const bool on = in[k] && (inside || point_in_frustum(sh.planes, p[k].x, p[k].y, p[k].z));
+      any |= on;
+      if (MODE == 1) {
+        // the 32 positions straddle at most two words of the point bitset: two atomics per warp step
+        const unsigned mb = __ballot_sync(0xffffffffu, on);
+        const uint32_t base = p0 + 32 * k, sft = base & 31;
+        if (lane == 0 && (mb << sft)) atomicOr(&A.accum.pts[base >> 5], mb << sft);
+        if (lane == 1 && sft && (mb >> (32 - sft))) atomicOr(&A.accum.pts[(base >> 5) + 1], mb >> (32 - sft));
+      }
+      if (!on) continue;
+      if (MODE == 0) {
+        ++vis;
+        if (!A.covered.pts || !bit_test(A.covered.pts, pos)) ++gain_p;
+        if (want_hash) vhash += mix64((uint64_t)(uint32_t)m.orig[pos]);
+      } else if (MODE == 2) {
+        acc_point(*tr, A.acc_scale_d, A.acc_scale_z, p[k].x, p[k].y, p[k].z, *acc);
+      }
+      if (MODE != 2 && vcov < 0) {
+        const uint32_t id = (uint32_t)m.pt_cov[pos], bit = 1u << (id & 31);
+        if (MODE == 0) {
+          const uint32_t old = atomicOr(&cov_scratch[id >> 5], bit);
+          if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
+        } else {
+          atomicOr(&A.accum.vox[id >> 5], bit);
+        }
+      }
+    }
+  }
+  if (MODE != 2 && vcov >= 0 && __any_sync(0xffffffffu, any) && lane == 0) {
+    const uint32_t id = (uint32_t)vcov, bit = 1u << (id & 31);
+    if (MODE == 0) {
+      const uint32_t old = A.cov_direct ? 0u : atomicOr(&cov_scratch[id >> 5], bit);
+      if (!(old & bit) && (!A.covered.vox || !bit_test(A.covered.vox, id))) ++gain_v;
+    } else {
+      atomicOr(&A.accum.vox[id >> 5], bit);
+    }
+  }
+}
+
 // pointCloudViewportTransform constants from device-resident poses (asscpp_eval_batch_device).  The host path
 // computes them with libm instead (abi.cu): CUDA's double asin / atan2 / sin / cos may differ from libm in the
 // last ulp.
@@ -1390,16 +1514,30 @@ __global__ void trig_kernel(const double* __restrict__ poses, int64_t nviews, Vi
   out[v] = t;
 }
 
-__device__ __forceinline__ void reset_view(ViewShared& sh, const ViewDev& vd, int v) {
-  if (threadIdx.x < 24) sh.planes[threadIdx.x] = vd.planes[threadIdx.x];
+__device__ __forceinline__ void reset_view(const EvalArgs& A, ViewShared& sh, const double* pose, int v) {
+  if (pose) {
+    // small batches: the planes of this view, computed here instead of by a planes_kernel launch
+    if (threadIdx.x == 32) {
+      ViewDev vd;
+      compute_view(pose, A.fc, vd);
+#pragma unroll
+      for (int k = 0; k < 24; ++k) sh.planes[k] = vd.planes[k];
+      sh.origin[0] = vd.origin[0]; sh.origin[1] = vd.origin[1]; sh.origin[2] = vd.origin[2];
+    }
+  } else {
+    const ViewDev& vd = A.views[v];
+    if (threadIdx.x < 24) sh.planes[threadIdx.x] = vd.planes[threadIdx.x];
+    if (threadIdx.x < 3) sh.origin[threadIdx.x] = vd.origin[threadIdx.x];
+  }
   if (threadIdx.x < 3) {
-    sh.origin[threadIdx.x] = vd.origin[threadIdx.x];
     sh.bb_min[threadIdx.x] = INT_MAX;
     sh.bb_max[threadIdx.x] = INT_MIN;
   }
+  if (A.acc && threadIdx.x >= 64 && threadIdx.x < 72)
+    reinterpret_cast<double*>(&sh.trig)[threadIdx.x - 64] = reinterpret_cast<const double*>(&A.trig[v])[threadIdx.x - 64];
   if (threadIdx.x == 0) {
     sh.view = v;
-    sh.cand_state = 0; sh.chunk_count = 0; sh.chunk_next = 0; sh.super_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.ray_count = 0;
+    sh.cand_state = 0; sh.big_count = 0; sh.chunk_next = 0; sh.super_count = 0; sh.list_count = 0; sh.vis_count = 0; sh.ray_next = 0; sh.big_next = 0;
     sh.survivors = 0; sh.visible = 0; sh.carry = 0; sh.unique = 0; sh.gain_p = 0; sh.gain_v = 0; sh.status = 0;
     sh.steps = 0; sh.vis_hash = 0; sh.surv_hash = 0;
     sh.acc[0] = sh.acc[1] = sh.acc[2] = sh.acc[3] = 0;
@@ -1417,6 +1555,10 @@ __device__ __forceinline__ void write_result(const EvalArgs& A, const ViewShared
   r.steps = sh.steps; r.vis_hash = sh.vis_hash; r.surv_hash = sh.surv_hash;
   A.results[v] = r;
   A.gains[v] = make_uint2(sh.gain_p, sh.gain_v);
+  if (A.small) {
+    A.host_results[v] = r;
+    if (!A.view_cov) A.host_gains[v] = make_uint2(sh.gain_p, sh.gain_v);
+  }
   if (sh.status & kVsError) atomicAdd(A.error_count, 1);
   if (A.acc) {
     AccRaw a;
@@ -1424,6 +1566,7 @@ __device__ __forceinline__ void write_result(const EvalArgs& A, const ViewShared
     a.min_key = sh.acc_min; a.max_key = sh.acc_max;
     a.visible = sh.visible; a.pad = 0;
     A.acc[v] = a;
+    if (A.small) A.host_acc[v] = a;
   }
 }
 
@@ -1432,7 +1575,55 @@ __device__ __forceinline__ void write_result(const EvalArgs& A, const ViewShared
 // ------------------------------------------------------------------------------------------------
 extern __shared__ __align__(16) unsigned char smem_raw[];
 
-__global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
+// Split-group mode inside the small-batch kernel: called by all threads of the CTA when view v is finished.  The last
+// view of a group to finish (a ticket that wraps to zero by itself) computes the group's union gains from the per-view
+// coverage bitsets: gain_vox of view s = voxels of its visible cloud neither in the covered set nor seen by an earlier
+// view of the group (heuristic.cpp:439-445, 473-483), exactly what group_gain_kernel does for larger batches.
+__device__ __forceinline__ void finish_group_view(const EvalArgs& A, int v, int* s_last, unsigned* s_gain) {
+  const int G = A.split_group;
+  const int grp = v / G, v0 = grp * G;
+  const int gsz = (int)min((int64_t)G, A.nviews - v0);
+  __syncthreads();  // the view's result and bitset are written
+  if (threadIdx.x == 0) {
+    __threadfence();
+    *s_last = atomicInc(A.group_ticket + grp, (unsigned)gsz - 1u) == (unsigned)gsz - 1u;
+  }
+  if (threadIdx.x < kSmallMaxGroup) s_gain[threadIdx.x] = 0;
+  __syncthreads();
+  if (!*s_last) return;
+  __threadfence();
+  unsigned n[kSmallMaxGroup];
+#pragma unroll
+  for (int s = 0; s < kSmallMaxGroup; ++s) n[s] = 0;
+  for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) {
+    uint32_t seen = A.covered.vox ? A.covered.vox[w] : 0u;
+#pragma unroll
+    for (int s = 0; s < kSmallMaxGroup; ++s) {
+      if (s >= gsz) break;
+      const uint32_t mine = __ldcg(A.view_cov + (int64_t)(v0 + s) * A.cov_words + w);
+      n[s] += __popc(mine & ~seen);
+      seen |= mine;
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < kSmallMaxGroup; ++s) {
+    if (s >= gsz) break;
+    const unsigned t = warp_sum(n[s]);
+    if ((threadIdx.x & 31) == 0 && t) atomicAdd(&s_gain[s], t);
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < gsz) {
+    const int vs = v0 + (int)threadIdx.x;
+    const unsigned gp = __ldcg(&A.gains[vs].x), gv = s_gain[threadIdx.x];
+    A.results[vs].gain_vox = gv;
+    A.host_results[vs].gain_vox = gv;
+    A.gains[vs] = make_uint2(gp, gv);
+    A.host_gains[vs] = make_uint2(gp, gv);
+  }
+}
+
+// param_poses: the poses as kernel parameters (eval_views_small_kernel) or nullptr (planes_kernel has filled A.views)
+__device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double* param_poses) {
   ViewShared& sh = *reinterpret_cast<ViewShared*>(smem_raw);
   uint32_t* smem_grid = reinterpret_cast<uint32_t*>(smem_raw + ((sizeof(ViewShared) + 15) & ~size_t(15)));
   const ModelDev& m = A.m;
@@ -1444,7 +1635,8 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
   // views are handed out in groups of A.group consecutive views (the sensors of one candidate); within a group
   // the coverage-voxel marks are kept, so gain_vox of a later view counts only voxels no earlier view of the
   // group has seen: the group's gain_vox sum is the gain of the union (heuristic.cpp:439-445, 473-483)
-  __shared__ int s_view, s_end, s_first, s_dirty;
+  __shared__ int s_view, s_end, s_first, s_dirty, s_group_last;
+  __shared__ unsigned s_group_gain[kSmallMaxGroup];
   if (threadIdx.x == 0) { s_view = -1; s_end = 0; s_dirty = 0; }
   const long long k_start = clock64();
   for (;;) {
@@ -1473,7 +1665,9 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     long long t0 = 0, t1 = 0, t2 = 0, t3 = 0;
     const bool prof = A.phase_cycles != nullptr && threadIdx.x == 0;
     if (prof) t0 = clock64();
-    reset_view(sh, A.views[v], v);
+    if (A.view_cov && A.small)  // the view's coverage bitset starts empty (larger split-group batches: zeroed by the host)
+      for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
+    reset_view(A, sh, param_poses ? param_poses + 7 * (int64_t)v : nullptr, v);
     __syncthreads();
     cull_view(A, sh, chunk_list, vox_list,
               reinterpret_cast<uint32_t*>(A.ray_buf + ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 3 * kRayQueueCap),
@@ -1482,6 +1676,7 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     if (sh.survivors == 0) {  // empty frustum cloud: extractVisibleSurface returns an empty cloud
       if (threadIdx.x == 0) write_result(A, sh, v);
       if (prof) atomicAdd(&A.phase_cycles[0], (unsigned long long)(t1 - t0));
+      if (A.small && A.view_cov) finish_group_view(A, v, &s_group_last, s_group_gain);
       continue;
     }
     GridMem gm;
@@ -1500,24 +1695,47 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     }
     __syncthreads();
     if (prof) t3 = clock64();
-    // P4b: second gate (occlusion_culling.cpp:338-342) per free voxel, then its survivors -> counts, gains, hash
+    // P4b: second gate (occlusion_culling.cpp:338-342) per free voxel, then its survivors -> counts, gains, hash.
+    // One lane per voxel; voxels with many points are set aside (the front of vox_list is free now) and taken one
+    // warp per voxel afterwards.
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     {
       unsigned vis = 0, gain_p = 0, gain_v = 0;
       unsigned long long vhash = 0;
       const unsigned nvis = sh.vis_count;
       const GridView& g = sh.g;
       const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
-      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x) {
-        const uint32_t u = vis_list[e];
-        const int4 vx = m.vox[u & kVoxMask];
-        const float tc[3] = {centre(g, 0, vx.x - g.min_b[0]), centre(g, 1, vx.y - g.min_b[1]),
-                             centre(g, 2, vx.z - g.min_b[2])};
-        if (!second_gate(g, pcd_o, tc)) { vis_list[e] = 0xffffffffu; continue; }
-        visit_voxel_points(A, sh, u, 0, cov_scratch, vis, gain_p, gain_v, vhash);
+      for (unsigned e0 = threadIdx.x & ~31u; e0 < nvis; e0 += blockDim.x) {
+        const unsigned e = e0 + lane;
+        bool big = false;
+        uint32_t u = 0;
+        if (e < nvis) {
+          u = vis_list[e];
+          const int4 vx = m.vox[u & kVoxMask];
+          const float tc[3] = {centre(g, 0, vx.x - g.min_b[0]), centre(g, 1, vx.y - g.min_b[1]),
+                               centre(g, 2, vx.z - g.min_b[2])};
+          if (!second_gate(g, pcd_o, tc)) {
+            vis_list[e] = 0xffffffffu;
+          } else {
+            big = (uint32_t)m.vox[(u & kVoxMask) + 1].w - (uint32_t)vx.w >= kCoopMinPoints;
+            if (!big) visit_voxel_points(A, sh, u, 0, cov_scratch, vis, gain_p, gain_v, vhash);
+          }
+        }
+        const unsigned bb = __ballot_sync(0xffffffffu, big);
+        if (bb) {
+          unsigned base = 0;
+          if (lane == 0) base = atomicAdd(&sh.big_count, (unsigned)__popc(bb));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (big) __stcg(vox_list + base + __popc(bb & ((1u << lane) - 1)), u);
+        }
       }
+      __syncthreads();
+      const unsigned nbig = sh.big_count;
+      for (unsigned i = warp; i < nbig; i += nwarps)
+        visit_voxel_warp<0>(A, sh, __ldcg(vox_list + i), cov_scratch, vis, gain_p, gain_v, vhash, nullptr, nullptr);
       vis = warp_sum(vis); gain_p = warp_sum(gain_p); gain_v = warp_sum(gain_v);
       for (int o = 16; o; o >>= 1) vhash += __shfl_xor_sync(0xffffffffu, vhash, o);
-      if ((threadIdx.x & 31) == 0) {
+      if (lane == 0) {
         if (vis) atomicAdd(&sh.visible, vis);
         if (gain_p) atomicAdd(&sh.gain_p, gain_p);
         if (gain_v) atomicAdd(&sh.gain_v, gain_v);
@@ -1527,7 +1745,7 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
     __syncthreads();
     if (A.acc && sh.visible && !sh.carry) {
       // P4c: accuracy terms of the visible points (occlusion_culling.cpp:445-475, 505-513)
-      const ViewTrig tr = A.trig[v];
+      const ViewTrig tr = sh.trig;
       AccLocal acc;
       const unsigned nvis = sh.vis_count;
       for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x) {
@@ -1535,11 +1753,19 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
         if (uf == 0xffffffffu) continue;
         const uint32_t u = uf & kVoxMask;
         const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
+        if (pe - pb >= kCoopMinPoints) continue;  // in the list of P4b
         for (uint32_t pos = pb; pos < pe; ++pos) {
           const float4 p = ld_pt(&m.pts[pos]);
           if (!(uf & kVoxInside) && !point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
           acc_point(tr, A.acc_scale_d, A.acc_scale_z, p.x, p.y, p.z, acc);
         }
+      }
+      {
+        unsigned d0 = 0, d1 = 0, d2 = 0;
+        unsigned long long d3 = 0;
+        const unsigned nbig = sh.big_count;
+        for (unsigned i = warp; i < nbig; i += nwarps)
+          visit_voxel_warp<2>(A, sh, __ldcg(vox_list + i), cov_scratch, d0, d1, d2, d3, &tr, &acc);
       }
       acc_commit(sh, acc);
       __syncthreads();
@@ -1554,6 +1780,7 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
         sh.status |= ASSCPP_VS_ORDERED;
         write_result(A, sh, v);
       }
+      if (A.small && A.view_cov) finish_group_view(A, v, &s_group_last, s_group_gain);
       continue;
     }
     // P5: OR the visible set into the accumulator (heuristic.cpp:344-346)
@@ -1561,10 +1788,18 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
       unsigned d0 = 0, d1 = 0, d2 = 0;
       unsigned long long d3 = 0;
       const unsigned nvis = sh.vis_count;
-      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x)
-        if (vis_list[e] != 0xffffffffu) visit_voxel_points(A, sh, vis_list[e], 1, cov_scratch, d0, d1, d2, d3);
+      for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x) {
+        const uint32_t uf = vis_list[e];
+        if (uf == 0xffffffffu) continue;
+        if ((uint32_t)m.vox[(uf & kVoxMask) + 1].w - (uint32_t)m.vox[uf & kVoxMask].w >= kCoopMinPoints) continue;
+        visit_voxel_points(A, sh, uf, 1, cov_scratch, d0, d1, d2, d3);
+      }
+      const unsigned nbig = sh.big_count;
+      for (unsigned i = warp; i < nbig; i += nwarps)
+        visit_voxel_warp<1>(A, sh, __ldcg(vox_list + i), cov_scratch, d0, d1, d2, d3, nullptr, nullptr);
     }
     if (threadIdx.x == 0) write_result(A, sh, v);
+    if (A.small && A.view_cov) finish_group_view(A, v, &s_group_last, s_group_gain);
     if (prof) {
       long long t4 = clock64();
       atomicAdd(&A.phase_cycles[0], (unsigned long long)(t1 - t0));  // cull (P1 + P2)
@@ -1577,7 +1812,35 @@ __global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) {
   if (s_dirty && !A.view_cov)  // ordered_views_kernel expects clean marks
     for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) (A.cov_scratch + (int64_t)blockIdx.x * A.cov_words)[w] = 0;
   if (A.phase_cycles != nullptr && threadIdx.x == 0) atomicAdd(&A.phase_cycles[5], (unsigned long long)clock64() - (unsigned long long)k_start);
+  if (A.small) {
+    // the last CTA to leave publishes the counters the host looks at and resets the device counters, so the next
+    // small launch needs no memset: {work counter, ordered views, error views, CTAs done}
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      if (atomicAdd(A.work_counter + 3, 1) == (int)gridDim.x - 1) {
+        A.host_counters[0] = *(volatile int32_t*)A.ordered_count;
+        A.host_counters[1] = *(volatile int32_t*)A.error_count;
+        A.work_counter[0] = 0; A.work_counter[1] = 0; A.work_counter[2] = 0; A.work_counter[3] = 0;
+      }
+    }
+  }
 }
+
+__global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) { eval_views_body(A, nullptr); }
+
+// Small batches: the poses travel with the launch (7 doubles per view) instead of through a host-to-device copy and a
+// planes_kernel launch.
+template <int NVIEWS>
+struct PoseBlock {
+  double p[7 * NVIEWS];
+};
+template <int NVIEWS>
+__global__ void __launch_bounds__(1024, 1) eval_views_small_kernel(const __grid_constant__ EvalArgs A,
+                                                                   const __grid_constant__ PoseBlock<NVIEWS> P) {
+  eval_views_body(A, P.p);
+}
+
 
 // ------------------------------------------------------------------------------------------------
 // ordered_views_kernel: exact replay of occlusion_culling.cpp:308-370 in ORIGINAL index order for
@@ -1602,7 +1865,7 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
       cov_scratch = A.view_cov + (int64_t)v * A.cov_words;
       for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
     }
-    reset_view(sh, A.views[v], v);
+    reset_view(A, sh, nullptr, v);
     __syncthreads();
     cull_view(A, sh, chunk_list, vox_list,
               reinterpret_cast<uint32_t*>(A.ray_buf + ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 3 * kRayQueueCap),
@@ -1804,6 +2067,10 @@ size_t eval_smem_header_bytes() { return ((sizeof(ViewShared) + 15) & ~size_t(15
 cudaError_t configure_kernels(size_t smem_bytes) {
   cudaError_t e = cudaFuncSetAttribute(eval_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(eval_views_small_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(eval_views_small_kernel<kSmallMaxViews>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(ordered_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
 }
 
@@ -1819,6 +2086,18 @@ void launch_trig(const double* d_poses, int64_t nviews, ViewTrig* out, cudaStrea
 }
 void launch_eval(const EvalArgs& a, int ctas, int threads, size_t smem_bytes, cudaStream_t s) {
   eval_views_kernel<<<ctas, threads, smem_bytes, s>>>(a);
+}
+void launch_eval_small(const EvalArgs& a, const double* h_poses, int ctas, int threads, size_t smem_bytes, cudaStream_t s) {
+  // the launch copies the parameter block: the poses need not outlive this call
+  if (a.nviews <= 64) {
+    PoseBlock<64> pb;
+    memcpy(pb.p, h_poses, (size_t)a.nviews * 7 * sizeof(double));
+    eval_views_small_kernel<64><<<ctas, threads, smem_bytes, s>>>(a, pb);
+  } else {
+    PoseBlock<kSmallMaxViews> pb;
+    memcpy(pb.p, h_poses, (size_t)a.nviews * 7 * sizeof(double));
+    eval_views_small_kernel<kSmallMaxViews><<<ctas, threads, smem_bytes, s>>>(a, pb);
+  }
 }
 void launch_group_gain(const EvalArgs& a, int group, cudaStream_t s) {
   const int64_t ngroups = (a.nviews + group - 1) / group;

@@ -216,3 +216,65 @@ def test_eval_groups_union_gain(oracle_mod, etihad, space_2p5, model, split, mon
     with pytest.raises(A.AsscppError):
         ctx.eval_groups(poses[:4], 0)
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_small_batch_single_launch_equals_general_path(lib_built, etihad, space_2p5, monkeypatch):
+    """Small batches (the A* use, at most 512 views) are ONE launch: poses as kernel parameters, planes computed by
+    the CTA that takes the view, group gains by the last view of the group, gains mirrored into mapped host memory
+    (asscpp_b200/csrc/abi.cu run_eval / finalize_small).  Every field equals the general multi-launch path's, with
+    and without groups, accuracy terms included; a batch holding a quirk-Q5 view falls back to the general path."""
+    import asscpp_b200 as A
+    xyz = etihad[0]
+    monkeypatch.setenv("ASSCPP_NO_SMALL", "1")
+    general = A.CoverageContext(xyz, A.default_params())
+    monkeypatch.delenv("ASSCPP_NO_SMALL")
+    small = A.CoverageContext(xyz, A.default_params())
+    cov_g, cov_s = general.new_set(), small.new_set()
+    seed = space_2p5["cam0"][600:640]
+    cov_g.or_views(seed, 5); cov_s.or_views(seed, 5)
+    fields = ("survivors", "visible", "carry", "unique_rays", "cells", "steps", "gain_pts", "gain_vox", "vis_hash",
+              "surv_hash")
+    for n, group in ((1, 1), (2, 2), (7, 1), (40, 2), (63, 3), (64, 1), (66, 2), (400, 2), (512, 8), (512, 1)):
+        k = (n + 1) // 2
+        poses = np.stack([space_2p5["cam0"][500:500 + k], space_2p5["cam1"][500:500 + k]], 1).reshape(-1, 7)[:n]
+        for flags in (A.EVAL_HASH, A.EVAL_HASH | A.EVAL_ACCURACY):
+            out = []
+            for ctx, cov in ((general, cov_g), (small, cov_s)):
+                before = ctx.launch_count()
+                ctx.eval_ex(poses, covered=cov, group_size=group, flags=flags)
+                gp, gv = ctx.gains(n)
+                res = ctx.results(n)
+                acc = ctx.accuracy(n) if flags & A.EVAL_ACCURACY else None
+                out.append((gp, gv, res, acc, ctx.launch_count() - before))
+            (gp0, gv0, r0, a0, l0), (gp1, gv1, r1, a1, l1) = out
+            assert l1 == 1 and l0 >= 3, (n, group, l0, l1)
+            assert np.array_equal(gp0, gp1) and np.array_equal(gv0, gv1), (n, group)
+            assert np.array_equal(gp1, r1["gain_pts"]) and np.array_equal(gv1, r1["gain_vox"])
+            for f in fields:
+                assert np.array_equal(r0[f], r1[f]), (n, group, f)
+            if a0 is not None:
+                assert a0.tobytes() == a1.tobytes(), (n, group)
+        assert r1["visible"].sum() > 0 or n < 7
+    general.close(); small.close()
+    # a quirk-Q5 view (tests/test_gpu_parity.py::test_carry_inside_large_batch) in a small batch
+    rng = np.random.default_rng(5)
+    xyz = np.concatenate([np.array([(42, 6, 2), (14, 2, 2), (2.5, 2, 2), (14, 3, 6)], np.float32),
+                          (rng.random((5000, 3)) * np.array([60, 30, 12]) + np.array([0, -40, 0])).astype(np.float32)])
+    pa = A.default_params(leaf=4.0, far_dist=60.0, cov_leaf=2.0)
+    poses = np.array([[1, 2, 2, 0, 0, 0, 1.0], [1, -20, 2, 0, 0, 0, 1.0], [5, -30, 6, 0, 0, 0.38268343, 0.92387953],
+                      [1, 2, 2, 0, 0, 0, 1.0]])
+    monkeypatch.setenv("ASSCPP_NO_SMALL", "1")
+    general = A.CoverageContext(xyz, pa)
+    monkeypatch.delenv("ASSCPP_NO_SMALL")
+    small = A.CoverageContext(xyz, pa)
+    for group in (1, 2):
+        general.eval_ex(poses, group_size=group, flags=A.EVAL_HASH)
+        small.eval_ex(poses, group_size=group, flags=A.EVAL_HASH)
+        g0, g1 = general.gains(4), small.gains(4)
+        r0, r1 = general.results(4), small.results(4)
+        assert np.array_equal(g0[0], g1[0]) and np.array_equal(g0[1], g1[1])
+        for f in fields + ("status",):
+            assert np.array_equal(r0[f], r1[f]), (group, f)
+        assert r1["carry"][0] > 0 and (r1["status"][0] & A.VS_ORDERED)
+    general.close(); small.close()

@@ -9,7 +9,7 @@ g = np.load(os.path.join(ROOT, "tests", "golden", "etihad_model.npz"))
 sp = np.load(os.path.join(ROOT, "tests", "golden", "etihad_searchspace_2p5m.npz"))
 ctx = A.CoverageContext(g["xyz"], A.default_params())
 s = ctx.new_set(); s.or_views(sp["cam0"][600:620], 5)
-info = ctx.info() if hasattr(ctx, "info") else None
+
 print("model: points %d occ voxels %d cov voxels %d" % (ctx.n_points, ctx.n_occ_voxels if hasattr(ctx, "n_occ_voxels") else -1, ctx.n_cov_voxels))
 for n in (2, 40, 400):
     poses = np.stack([sp["cam0"][:n // 2], sp["cam1"][:n // 2]], 1).reshape(-1, 7)
