@@ -108,6 +108,7 @@ struct AsscppCtx {
   int64_t small_launches = 0, small_fallbacks = 0;
   uint4* d_ray_buf = nullptr;
   int64_t ray_cap = 0;
+  size_t l2_persist_bytes = 0;  // persisting-L2 window over the ray queues (0: not set)
   int walk_thresh = 16;
   int setup_iters = 1, halo_iters = 3;
   uint8_t* d_vstate = nullptr;
@@ -576,6 +577,31 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = dev_alloc(c, &c->d_vis_list, c->vis_cap * c->ctas))) return fail(rc);
   c->ray_cap = ray_queue_cap();  // records per warp queue; 32 warps per CTA
   if ((rc = dev_alloc(c, &c->d_ray_buf, 3 * c->ray_cap * 32 * c->ctas))) return fail(rc);
+  // The warps' ray queues are the most rewritten scratch (48 bytes written and read back per ray): ask L2 to keep
+  // them (persisting access window over the one contiguous buffer) so that the stream of model points does not push
+  // them out to DRAM.  ASSCPP_L2_PERSIST=0 turns it off; failure to set it up is not an error.
+  {
+    const char* pe = getenv("ASSCPP_L2_PERSIST");
+    int max_persist = 0;
+    cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, device);
+    const size_t ray_bytes = (size_t)3 * c->ray_cap * 32 * c->ctas * sizeof(uint4);
+    if ((!pe || atoi(pe) != 0) && max_persist > 0) {
+      const size_t want = std::min<size_t>((size_t)max_persist, ray_bytes);
+      int max_window = 0;
+      cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, device);
+      if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
+        cudaStreamAttrValue attr;
+        memset(&attr, 0, sizeof(attr));
+        attr.accessPolicyWindow.base_ptr = c->d_ray_buf;
+        attr.accessPolicyWindow.num_bytes = std::min<size_t>(ray_bytes, (size_t)std::max(max_window, 0));
+        attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)std::max<size_t>(ray_bytes, 1));
+        attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+        if (cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr) == cudaSuccess) c->l2_persist_bytes = want;
+      }
+      cudaGetLastError();
+    }
+  }
   if (const char* e = getenv("ASSCPP_HALO_ITERS")) c->halo_iters = std::max(0, std::min(64, atoi(e)));
   if (const char* e = getenv("ASSCPP_SETUP_ITERS")) c->setup_iters = std::max(1, std::min(64, atoi(e)));
   if (const char* e = getenv("ASSCPP_SPLIT_GROUP_MAX")) c->split_group_max_views = std::max(0, atoi(e));

@@ -200,7 +200,14 @@ constexpr unsigned kDescShared = 1024;
 // A voxel with at least this many points is not walked by one lane (a chain of dependent loads, one point after the
 // other): it is set aside and the points are tested 32 at a time by a whole warp (coarse lattices hold hundreds of
 // points per voxel; with few voxels per view that chain was most of a small batch's latency).
-constexpr uint32_t kCoopMinPoints = 8;
+#ifndef ASSCPP_COOP_MIN_POINTS
+#define ASSCPP_COOP_MIN_POINTS 8
+#endif
+constexpr uint32_t kCoopMinPoints = ASSCPP_COOP_MIN_POINTS;
+// ... and with few voxels in all (a small view: fewer voxels than lane groups in the CTA) every voxel of two or more
+// points is taken that way: idle warps cost nothing, a lane walking seven points one after the other costs microseconds
+constexpr unsigned kCoopAllBelow = 128;
+__device__ __forceinline__ uint32_t coop_min_points(unsigned nvoxels) { return nvoxels <= kCoopAllBelow ? 2u : kCoopMinPoints; }
 
 struct ViewShared {
   float planes[24];
@@ -376,7 +383,9 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     constexpr unsigned kSuperListCap = 1024;
     const bool prof = A.phase_cycles != nullptr && threadIdx.x == 0;
     const long long c0 = prof ? clock64() : 0;
-    for (int64_t s0 = (int64_t)warp * 32; s0 < m.n_super; s0 += (int64_t)nwarps * 32) {
+    // a model with no more super-chunks than warps: P1b tests each super-chunk itself, no list, one barrier less
+    const bool direct_supers = m.n_super <= (int64_t)nwarps;
+    for (int64_t s0 = (int64_t)warp * 32; s0 < m.n_super && !direct_supers; s0 += (int64_t)nwarps * 32) {
       const int64_t s = s0 + lane;
       bool keep = false;
       if (s < m.n_super) {
@@ -392,11 +401,11 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         if (keep && at < kSuperListCap) sh.seg_last[at] = (int)s;
       }
     }
-    __syncthreads();
+    if (!direct_supers) __syncthreads();
     const long long c1 = prof ? clock64() : 0;
     // P1b: the 32 children of each surviving super-chunk, one super per warp step, spread evenly over the warps
     const unsigned nsup = sh.super_count;
-    const bool listed = nsup <= kSuperListCap;  // otherwise (huge frustum): walk all super-chunks again
+    const bool listed = nsup <= kSuperListCap && !direct_supers;  // otherwise (huge frustum): walk all super-chunks again
     const int64_t nstep = listed ? (int64_t)nsup : m.n_super;
     for (int64_t k = warp; k < nstep; k += nwarps) {
       int64_t sup = k;
@@ -409,8 +418,10 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
       const int64_t c = sup * kSuperFanout + lane;
       bool ck = false;
       float4 lo, hi;
+      uint32_t vb0 = 0, vb1 = 0;
       if (c < m.n_chunks) {
         lo = m.chunk_lo[c]; hi = m.chunk_hi[c];
+        vb0 = (uint32_t)m.chunk_vox[c]; vb1 = (uint32_t)m.chunk_vox[c + 1];  // with the boxes, not after the test: one round trip less
         ck = !box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
       }
       const unsigned cb = __ballot_sync(0xffffffffu, ck);
@@ -419,7 +430,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         // one 64-bit atomic hands out descriptor slots (high word) and voxel offsets (low word) together, so
         // offsets ascend with the slot index
         uint32_t vb = 0, nv = 0;
-        if (ck) { vb = (uint32_t)m.chunk_vox[c]; nv = (uint32_t)m.chunk_vox[c + 1] - vb; }
+        if (ck) { vb = vb0; nv = vb1 - vb0; }
         uint32_t incl = nv;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -457,6 +468,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     // (frustum_culling.cpp:153-166) afterwards, one lane per such voxel.
     constexpr int kCullUnroll = 2;
     const unsigned total = (unsigned)sh.cand_state, ndesc = (unsigned)(sh.cand_state >> 32);
+    const uint32_t coop_min = coop_min_points(total);
     auto desc = [&](unsigned i) { return i < kDescShared ? sh.chunk_desc[i] : chunk_list[i]; };
     auto emit_voxels = [&](bool emit, uint32_t entry) {
       const unsigned ob = __ballot_sync(0xffffffffu, emit);
@@ -477,14 +489,12 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         const unsigned i = i0 + lane;
         unsigned cnt = 0;
         uint32_t u = 0;
-        bool big = false;
         if (i < ncut) {
           u = __ldcg(cut + i);
           const int4 vx = m.vox[u];
           const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
-          big = q1 - q0 >= kCoopMinPoints;
           // the points of a voxel four at a time: the loads, not the plane tests, are what this loop waits for
-          for (uint32_t qb = q0; qb < q1 && !big; qb += 4) {
+          for (uint32_t qb = q0; qb < q1; qb += 4) {
             float4 p[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) p[k] = ld_pt(&m.pts[min(qb + k, q1 - 1)]);
@@ -502,14 +512,6 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           }
         }
         emit_voxels(cnt != 0, u);
-        // voxels with many points: set aside for the whole CTA (one warp per voxel, below), from the top of the list
-        const unsigned bb = __ballot_sync(0xffffffffu, big);
-        if (bb) {
-          unsigned base = 0;
-          if (lane == 0) base = atomicAdd(&sh.big_count, (unsigned)__popc(bb));
-          base = __shfl_sync(0xffffffffu, base, 0);
-          if (big) __stcg(vox_list + (A.list_cap - 1 - (int64_t)(base + __popc(bb & ((1u << lane) - 1)))), u);
-        }
       }
       ncut = 0;
       __syncwarp();
@@ -596,9 +598,19 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           }
         }
         emit_voxels(cls == 2, uu[b] | kVoxInside);
-        const unsigned sb = __ballot_sync(0xffffffffu, cls == 1);
+        // cut by a plane: voxels with many points go to the CTA's list (one warp, or part of one, per voxel below),
+        // the others to this warp's list (one lane per voxel)
+        const bool bigcut = cls == 1 && q1[b] - (uint32_t)vx[b].w >= coop_min;
+        const unsigned bb = __ballot_sync(0xffffffffu, bigcut);
+        if (bb) {
+          unsigned base = 0;
+          if (lane == 0) base = atomicAdd(&sh.big_count, (unsigned)__popc(bb));
+          base = __shfl_sync(0xffffffffu, base, 0);
+          if (bigcut) __stcg(vox_list + (A.list_cap - 1 - (int64_t)(base + __popc(bb & ((1u << lane) - 1)))), uu[b]);
+        }
+        const unsigned sb = __ballot_sync(0xffffffffu, cls == 1 && !bigcut);
         if (sb) {
-          if (cls == 1) __stcg(cut + ncut + __popc(sb & ((1u << lane) - 1)), uu[b]);
+          if (cls == 1 && !bigcut) __stcg(cut + ncut + __popc(sb & ((1u << lane) - 1)), uu[b]);
           ncut += (unsigned)__popc(sb);
           if (ncut + 32 > cut_cap) flush_cut();
         }
@@ -608,35 +620,44 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     const long long d1 = prof2 ? clock64() : 0;
     if (prof2) atomicAdd(&A.phase_cycles[10], (unsigned long long)ncut);
     flush_cut();
-    // the cut voxels with many points, one warp per voxel, 64 points in flight per warp
+    // the cut voxels with many points (the top of the list): W lanes per voxel -- a whole warp each when there are
+    // few, so that a handful of voxels does not become a chain of dependent loads, a quarter warp each when there are many
     __syncthreads();
-    const unsigned nbig = sh.big_count;
-    for (unsigned i = warp; i < nbig; i += nwarps) {
-      const uint32_t u = __ldcg(vox_list + (A.list_cap - 1 - (int64_t)i));
-      const int4 vx = m.vox[u];
-      const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
-      unsigned c = 0;
-      for (uint32_t qb = q0; qb < q1; qb += 64) {
-        const uint32_t qa = qb + lane, qc = qa + 32;
-        const bool oa = qa < q1, oc = qc < q1;
-        float4 pa = make_float4(0.f, 0.f, 0.f, 0.f), pc = pa;
-        if (oa) pa = ld_pt(&m.pts[qa]);
-        if (oc) pc = ld_pt(&m.pts[qc]);
-        const bool ia = oa && point_in_frustum(sh.planes, pa.x, pa.y, pa.z);
-        const bool ic = oc && point_in_frustum(sh.planes, pc.x, pc.y, pc.z);
-        if (want_hash) {
-          if (ia) shash += mix64((uint64_t)(uint32_t)m.orig[qa]);
-          if (ic) shash += mix64((uint64_t)(uint32_t)m.orig[qc]);
+    {
+      const unsigned nbig = sh.big_count;
+      const int W = nbig <= (unsigned)nwarps ? 32 : (nbig <= 2u * nwarps ? 16 : 8);
+      const int sub = lane / W, sl = lane - sub * W, per = 32 / W;
+      const unsigned gmask = W == 32 ? 0xffffffffu : (((1u << W) - 1u) << (sub * W));
+      for (unsigned i = warp * per + sub; i < nbig; i += nwarps * per) {
+        const uint32_t u = __ldcg(vox_list + (A.list_cap - 1 - (int64_t)i));
+        const int4 vx = m.vox[u];
+        const uint32_t q0 = (uint32_t)vx.w, q1 = (uint32_t)m.vox[u + 1].w;
+        unsigned c = 0;
+        for (uint32_t qb = q0; qb < q1; qb += 4 * W) {
+          float4 p[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t q = qb + k * W + sl;
+            p[k] = q < q1 ? ld_pt(&m.pts[q]) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t q = qb + k * W + sl;
+            if (q >= q1 || !point_in_frustum(sh.planes, p[k].x, p[k].y, p[k].z)) continue;
+            ++c;
+            if (want_hash) shash += mix64((uint64_t)(uint32_t)m.orig[q]);
+          }
         }
-        c += (unsigned)__popc(__ballot_sync(0xffffffffu, ia)) + (unsigned)__popc(__ballot_sync(0xffffffffu, ic));
+        c = __reduce_add_sync(gmask, c);
+        if (c && sl == 0) {
+          surv_in += c;
+          bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
+          bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
+          const unsigned at = atomicAdd(&sh.list_count, 1u);
+          if (at < A.list_cap) vox_list[at] = u;
+        }
       }
-      if (c && lane == 0) {
-        surv_in += c;
-        bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
-        bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
-        const unsigned at = atomicAdd(&sh.list_count, 1u);
-        if (at < A.list_cap) vox_list[at] = u;
-      }
+      __syncwarp();
     }
     if (prof2) {
       atomicAdd(&A.phase_cycles[8], (unsigned long long)(d1 - d0));
@@ -873,8 +894,16 @@ __device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const View
       }
     }
   } else {
-    for (uint32_t pos = pb; pos < pe; ++pos) {
-      float4 p = ld_pt(&m.pts[pos]);
+    // four loads in flight: the loads, not the tests, are what this loop waits for
+    for (uint32_t p0 = pb; p0 < pe; p0 += 4) {
+    float4 pp[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) pp[k] = ld_pt(&m.pts[min(p0 + k, pe - 1)]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint32_t pos = p0 + k;
+      if (pos >= pe) break;
+      const float4 p = pp[k];
       if (!point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
       any = true;
       if (mode == 0) {
@@ -893,6 +922,7 @@ __device__ __forceinline__ void visit_voxel_points(const EvalArgs& A, const View
           atomicOr(&A.accum.vox[id >> 5], bit);
         }
       }
+    }
     }
   }
   if (any && vcov >= 0) {
@@ -1418,12 +1448,26 @@ __device__ __forceinline__ void acc_commit(ViewShared& sh, AccLocal& a) {
 // One warp, one voxel (every lane passes the same entry): visit_voxel_points with the points taken 32 at a time, four
 // loads in flight per lane.  MODE 0: counts / gains / hash; 1: OR into A.accum; 2: accuracy terms.
 // ------------------------------------------------------------------------------------------------
+struct LaneGroup {  // W consecutive lanes of a warp working on one voxel
+  int W, sub, sl;     // lanes per group, group index in the warp, lane index in the group
+  unsigned mask;
+};
+__device__ __forceinline__ LaneGroup lane_group(unsigned nvoxels, int nwarps) {
+  LaneGroup g;
+  const int lane = threadIdx.x & 31;
+  g.W = nvoxels <= (unsigned)nwarps ? 32 : (nvoxels <= 2u * nwarps ? 16 : 8);
+  g.sub = lane / g.W;
+  g.sl = lane - g.sub * g.W;
+  g.mask = g.W == 32 ? 0xffffffffu : (((1u << g.W) - 1u) << (g.sub * g.W));
+  return g;
+}
+
 template <int MODE>
-__device__ __forceinline__ void visit_voxel_warp(const EvalArgs& A, const ViewShared& sh, uint32_t uf, uint32_t* cov_scratch,
-                                                 unsigned& vis, unsigned& gain_p, unsigned& gain_v,
+__device__ __forceinline__ void visit_voxel_warp(const EvalArgs& A, const ViewShared& sh, const LaneGroup& lg, uint32_t uf,
+                                                 uint32_t* cov_scratch, unsigned& vis, unsigned& gain_p, unsigned& gain_v,
                                                  unsigned long long& vhash, const ViewTrig* tr, AccLocal* acc) {
   const ModelDev& m = A.m;
-  const int lane = threadIdx.x & 31;
+  const int lane = lg.sl, W = lg.W;
   const uint32_t u = uf & kVoxMask;
   const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
   const bool inside = (uf & kVoxInside) != 0;  // every point of the voxel passed the frustum test
@@ -1431,26 +1475,26 @@ __device__ __forceinline__ void visit_voxel_warp(const EvalArgs& A, const ViewSh
   const int32_t vcov = MODE == 2 ? 0 : m.vox_cov[u];
   bool any = false;
   constexpr int K = 4;
-  for (uint32_t p0 = pb; p0 < pe; p0 += 32 * K) {
+  for (uint32_t p0 = pb; p0 < pe; p0 += W * K) {
     float4 p[K];
     bool in[K];
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      const uint32_t pos = p0 + 32 * k + lane;
+      const uint32_t pos = p0 + W * k + lane;
       in[k] = pos < pe;
       p[k] = make_float4(0.f, 0.f, 0.f, 0.f);
       if (in[k] && (!inside || MODE == 2)) p[k] = ld_pt(&m.pts[pos]);
     }
 #pragma unroll
     for (int k = 0; k < K; ++k) {
-      if (p0 + 32 * k >= pe) break;  // warp-uniform
-      const uint32_t pos = p0 + 32 * k + lane;
+      if (p0 + W * k >= pe) break;  // uniform over the group
+      const uint32_t pos = p0 + W * k + lane;
       const bool on = in[k] && (inside || point_in_frustum(sh.planes, p[k].x, p[k].y, p[k].z));
       any |= on;
       if (MODE == 1) {
-        // the 32 positions straddle at most two words of the point bitset: two atomics per warp step
-        const unsigned mb = __ballot_sync(0xffffffffu, on);
-        const uint32_t base = p0 + 32 * k, sft = base & 31;
+        // the W positions straddle at most two words of the point bitset: two atomics per step of the group
+        const unsigned mb = __ballot_sync(lg.mask, on) >> (lg.sub * W);
+        const uint32_t base = p0 + W * k, sft = base & 31;
         if (lane == 0 && (mb << sft)) atomicOr(&A.accum.pts[base >> 5], mb << sft);
         if (lane == 1 && sft && (mb >> (32 - sft))) atomicOr(&A.accum.pts[(base >> 5) + 1], mb >> (32 - sft));
       }
@@ -1473,7 +1517,7 @@ __device__ __forceinline__ void visit_voxel_warp(const EvalArgs& A, const ViewSh
       }
     }
   }
-  if (MODE != 2 && vcov >= 0 && __any_sync(0xffffffffu, any) && lane == 0) {
+  if (MODE != 2 && vcov >= 0 && __any_sync(lg.mask, any) && lane == 0) {
     const uint32_t id = (uint32_t)vcov, bit = 1u << (id & 31);
     if (MODE == 0) {
       const uint32_t old = A.cov_direct ? 0u : atomicOr(&cov_scratch[id >> 5], bit);
@@ -1669,6 +1713,7 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
       for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
     reset_view(A, sh, param_poses ? param_poses + 7 * (int64_t)v : nullptr, v);
     __syncthreads();
+    if (prof) atomicAdd(&A.phase_cycles[12], (unsigned long long)(clock64() - t0));
     cull_view(A, sh, chunk_list, vox_list,
               reinterpret_cast<uint32_t*>(A.ray_buf + ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 3 * kRayQueueCap),
               3u * kRayQueueCap * 4u);  // the warp's ray queue is idle during the cull
@@ -1703,6 +1748,7 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
       unsigned vis = 0, gain_p = 0, gain_v = 0;
       unsigned long long vhash = 0;
       const unsigned nvis = sh.vis_count;
+      const uint32_t coop_min = coop_min_points(nvis);
       const GridView& g = sh.g;
       const float pcd_o[3] = {m.pcd_origin[0], m.pcd_origin[1], m.pcd_origin[2]};
       for (unsigned e0 = threadIdx.x & ~31u; e0 < nvis; e0 += blockDim.x) {
@@ -1717,7 +1763,7 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
           if (!second_gate(g, pcd_o, tc)) {
             vis_list[e] = 0xffffffffu;
           } else {
-            big = (uint32_t)m.vox[(u & kVoxMask) + 1].w - (uint32_t)vx.w >= kCoopMinPoints;
+            big = (uint32_t)m.vox[(u & kVoxMask) + 1].w - (uint32_t)vx.w >= coop_min;
             if (!big) visit_voxel_points(A, sh, u, 0, cov_scratch, vis, gain_p, gain_v, vhash);
           }
         }
@@ -1729,10 +1775,16 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
           if (big) __stcg(vox_list + base + __popc(bb & ((1u << lane) - 1)), u);
         }
       }
+      if (prof) atomicAdd(&A.phase_cycles[13], (unsigned long long)(clock64() - t3));
       __syncthreads();
       const unsigned nbig = sh.big_count;
-      for (unsigned i = warp; i < nbig; i += nwarps)
-        visit_voxel_warp<0>(A, sh, __ldcg(vox_list + i), cov_scratch, vis, gain_p, gain_v, vhash, nullptr, nullptr);
+      if (prof) atomicAdd(&A.phase_cycles[14], (unsigned long long)nbig);
+      {
+        const LaneGroup lg = lane_group(nbig, nwarps);
+        for (unsigned i = warp * (32 / lg.W) + lg.sub; i < nbig; i += nwarps * (32 / lg.W))
+          visit_voxel_warp<0>(A, sh, lg, __ldcg(vox_list + i), cov_scratch, vis, gain_p, gain_v, vhash, nullptr, nullptr);
+        __syncwarp();
+      }
       vis = warp_sum(vis); gain_p = warp_sum(gain_p); gain_v = warp_sum(gain_v);
       for (int o = 16; o; o >>= 1) vhash += __shfl_xor_sync(0xffffffffu, vhash, o);
       if (lane == 0) {
@@ -1753,7 +1805,7 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
         if (uf == 0xffffffffu) continue;
         const uint32_t u = uf & kVoxMask;
         const uint32_t pb = (uint32_t)m.vox[u].w, pe = (uint32_t)m.vox[u + 1].w;
-        if (pe - pb >= kCoopMinPoints) continue;  // in the list of P4b
+        if (pe - pb >= coop_min_points(nvis)) continue;  // in the list of P4b
         for (uint32_t pos = pb; pos < pe; ++pos) {
           const float4 p = ld_pt(&m.pts[pos]);
           if (!(uf & kVoxInside) && !point_in_frustum(sh.planes, p.x, p.y, p.z)) continue;
@@ -1764,8 +1816,10 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
         unsigned d0 = 0, d1 = 0, d2 = 0;
         unsigned long long d3 = 0;
         const unsigned nbig = sh.big_count;
-        for (unsigned i = warp; i < nbig; i += nwarps)
-          visit_voxel_warp<2>(A, sh, __ldcg(vox_list + i), cov_scratch, d0, d1, d2, d3, &tr, &acc);
+        const LaneGroup lg = lane_group(nbig, nwarps);
+        for (unsigned i = warp * (32 / lg.W) + lg.sub; i < nbig; i += nwarps * (32 / lg.W))
+          visit_voxel_warp<2>(A, sh, lg, __ldcg(vox_list + i), cov_scratch, d0, d1, d2, d3, &tr, &acc);
+        __syncwarp();
       }
       acc_commit(sh, acc);
       __syncthreads();
@@ -1791,17 +1845,22 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
       for (unsigned e = threadIdx.x; e < nvis; e += blockDim.x) {
         const uint32_t uf = vis_list[e];
         if (uf == 0xffffffffu) continue;
-        if ((uint32_t)m.vox[(uf & kVoxMask) + 1].w - (uint32_t)m.vox[uf & kVoxMask].w >= kCoopMinPoints) continue;
+        if ((uint32_t)m.vox[(uf & kVoxMask) + 1].w - (uint32_t)m.vox[uf & kVoxMask].w >= coop_min_points(nvis)) continue;
         visit_voxel_points(A, sh, uf, 1, cov_scratch, d0, d1, d2, d3);
       }
       const unsigned nbig = sh.big_count;
-      for (unsigned i = warp; i < nbig; i += nwarps)
-        visit_voxel_warp<1>(A, sh, __ldcg(vox_list + i), cov_scratch, d0, d1, d2, d3, nullptr, nullptr);
+      const LaneGroup lg = lane_group(nbig, nwarps);
+      for (unsigned i = warp * (32 / lg.W) + lg.sub; i < nbig; i += nwarps * (32 / lg.W))
+        visit_voxel_warp<1>(A, sh, lg, __ldcg(vox_list + i), cov_scratch, d0, d1, d2, d3, nullptr, nullptr);
+      __syncwarp();
     }
     if (threadIdx.x == 0) write_result(A, sh, v);
+    const long long tg = prof ? clock64() : 0;
     if (A.small && A.view_cov) finish_group_view(A, v, &s_group_last, s_group_gain);
     if (prof) {
       long long t4 = clock64();
+      atomicAdd(&A.phase_cycles[15], (unsigned long long)(t4 - tg));
+      t4 = tg;
       atomicAdd(&A.phase_cycles[0], (unsigned long long)(t1 - t0));  // cull (P1 + P2)
       atomicAdd(&A.phase_cycles[1], (unsigned long long)(t2 - t1));  // grid build (P3)
       atomicAdd(&A.phase_cycles[2], (unsigned long long)(t3 - t2));  // DDA (P4a)

@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round 2, GPU call: warp-per-voxel handling of many-point voxels + the one-launch small-batch path
 set -u
-O=gpurun_out/r02i
+O=gpurun_out/${RUN_TAG:-r02j}
 mkdir -p $O
 ( timeout 900 python -m pytest tests/test_search.py tests/test_gpu_parity.py -m gpu -q -x ) > $O/pytest_parity.txt 2>&1
 tail -15 $O/pytest_parity.txt

@@ -18,6 +18,16 @@ for n in (2, 40, 400, 2450):
     reps = 300
     for _ in range(reps): ctx.eval_groups(poses, 2, covered=s)
     dt = (time.perf_counter() - t) / reps
+    # the same two C-ABI calls with the arguments built once (what a C++ caller pays: no numpy / ctypes marshalling)
+    import ctypes as C
+    o = A.EvalOpts(s.handle, -1, 5, 2, 0, 0, 0)
+    pp = np.ascontiguousarray(poses, np.float64); pv = pp.ctypes.data_as(C.c_void_p)
+    out = np.zeros(n, A.RESULT_DTYPE); ov = out.ctypes.data_as(C.c_void_p)
+    f_eval, f_get, h, ob, nn = ctx.L.asscpp_eval_ex, ctx.L.asscpp_get_results, ctx.h, C.byref(o), C.c_int64(n)
+    for _ in range(20): f_eval(h, pv, nn, ob); f_get(h, ov, nn)
+    t = time.perf_counter()
+    for _ in range(reps): f_eval(h, pv, nn, ob); f_get(h, ov, nn)
+    dt_abi = (time.perf_counter() - t) / reps
     dev, kern = [], []
     for _ in range(50):
         ctx.timer_begin()
@@ -25,5 +35,5 @@ for n in (2, 40, 400, 2450):
         dev.append(ctx.timer_end())
         kern.append(ctx.eval_kernel_ms()[0])
         ctx.gains(n)
-    print("views %5d: %.1f us per call, %.0f VE/s; stream %.1f us, eval_views_kernel %.1f us" % (
-        n, dt * 1e6, n / dt, 1e3 * float(np.median(dev)), 1e3 * float(np.median(kern))))
+    print("views %5d: %.1f us per call, %.0f VE/s; C-ABI calls alone %.1f us; stream %.1f us, eval_views_kernel %.1f us" % (
+        n, dt * 1e6, n / dt, dt_abi * 1e6, 1e3 * float(np.median(dev)), 1e3 * float(np.median(kern))))
