@@ -1,6 +1,9 @@
 // abi.cu -- the C ABI of include/asscpp_gpu.h: context, device memory, kernel sequencing.
 // No torch, no CPU fallback: every compute entry point launches the sm_100a kernels of kernels.cu.
 #include <cuda_runtime.h>
+
+#include <atomic>
+#include <chrono>
 #include <dlfcn.h>
 
 #include <algorithm>
@@ -106,6 +109,8 @@ struct AsscppCtx {
   int small_covered = -1, small_group = 1;
   uint32_t small_flags = 0;
   int64_t small_launches = 0, small_fallbacks = 0;
+  int32_t small_epoch = 0;
+  int small_spin_us = 200;   // finalize_small spins this long on the completion flag before it synchronises the stream
   uint4* d_ray_buf = nullptr;
   int64_t ray_cap = 0;
   size_t l2_persist_bytes = 0;  // persisting-L2 window over the ray queues (0: not set)
@@ -370,7 +375,14 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   AsscppCtx::TimedSpan* evp = span_begin(c, 0);
   a.smem_grid_words = c->eval_grid_words;
   if (small) {
-    launch_eval_small(a, h_poses, ctas, c->cta_threads, c->eval_smem_bytes_, c->stream);
+    ViewDev tiny[8];
+    const bool tiny_batch = nviews <= std::min(8, tiny_max_views());
+    for (int64_t v = 0; tiny_batch && v < nviews; ++v) {
+      frustum_planes_host_fc(c->fc, h_poses + 7 * v, tiny[v].planes, tiny[v].origin, nullptr);
+      tiny[v].pad = 0.0f;
+    }
+    a.epoch = ++c->small_epoch;
+    launch_eval_small(a, h_poses, tiny_batch ? tiny : nullptr, ctas, c->cta_threads, c->eval_smem_bytes_, c->stream);
     span_end(c, evp);
     c->launches += 1;
     c->small_launches += 1;
@@ -394,7 +406,21 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
 // no view asked for the ordered replay; otherwise the batch is evaluated again by the general path.
 int finalize_small(AsscppCtx* c) {
   if (!c->small_pending) return ASSCPP_OK;
-  CU(c, cudaStreamSynchronize(c->stream));
+  {
+    // the kernel's last CTA writes the launch's epoch into mapped host memory after everything else (system-scope
+    // fences): seeing it is as good as the stream synchronisation and several microseconds sooner
+    volatile int32_t* flag = &c->h_small->counters[2];
+    bool seen = *flag == c->small_epoch;
+    if (!seen && c->small_spin_us > 0) {
+      const auto t0 = std::chrono::steady_clock::now();
+      for (;;) {
+        for (int k = 0; k < 64 && !seen; ++k) seen = *flag == c->small_epoch;
+        if (seen || std::chrono::steady_clock::now() - t0 > std::chrono::microseconds(c->small_spin_us)) break;
+      }
+    }
+    if (!seen) CU(c, cudaStreamSynchronize(c->stream));
+    std::atomic_thread_fence(std::memory_order_acquire);
+  }
   c->small_pending = false;
   if (c->h_small->counters[0] == 0) { c->small_valid = true; return ASSCPP_OK; }
   c->small_fallbacks += 1;
@@ -615,6 +641,7 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   if ((rc = dev_alloc(c, &c->d_group_ticket, kSmallMaxViews))) return fail(rc);
   cudaMemsetAsync(c->d_group_ticket, 0, kSmallMaxViews * sizeof(uint32_t), c->stream);
   if (getenv("ASSCPP_NO_SMALL")) c->small_enabled = false;
+  if (const char* sp = getenv("ASSCPP_SMALL_SPIN_US")) c->small_spin_us = std::max(0, atoi(sp));
   {
     void* hp = nullptr;
     void* dp = nullptr;

@@ -116,6 +116,7 @@ struct EvalArgs {
   // computed by the CTA that takes the view; the last view of a group to finish computes the group's union gains; gains
   // and counters are mirrored into mapped host memory; the last CTA resets the device counters for the next launch
   int small;                 // 1: eval_views_small_kernel
+  int32_t epoch;             // written to host_counters[2] when the launch is complete
   FrustumConst fc;
   uint2* host_gains;         // [nviews] mapped host mirror of gains
   AsscppViewResult* host_results;  // [nviews] ... of results

@@ -45,7 +45,9 @@ __device__ __forceinline__ float4 ld_pt(const float4* p) {
 #endif
 }
 
-__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+// not inlined: the hash is optional (ASSCPP_EVAL_HASH) and its 64-bit multiplies would sit in every point loop, in
+// the way of the instruction fetch of the paths that do not ask for it
+__device__ __noinline__ uint64_t mix64(uint64_t x) {
   x += 0x9E3779B97F4A7C15ull;
   x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
   x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
@@ -377,6 +379,9 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     const float h = 0.5f * m.leaf + 1e-6f * m.max_abs_coord;
     sh.vox_hi[threadIdx.x] = h * n1 + (1e-6f * (n1 * (m.max_abs_coord + m.leaf) + fabsf(pl[3])) + 1e-30f);
   }
+  int bmin[3] = {INT_MAX, INT_MAX, INT_MAX}, bmax[3] = {INT_MIN, INT_MIN, INT_MIN};
+  unsigned surv = 0, surv_in = 0;
+  unsigned long long shash = 0;
   if (brute) __syncthreads();
   if (!brute) {
     // P1a: every thread tests super-chunks; survivors go to a shared list (sh.seg_last doubles as that list)
@@ -424,13 +429,49 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         vb0 = (uint32_t)m.chunk_vox[c]; vb1 = (uint32_t)m.chunk_vox[c + 1];  // with the boxes, not after the test: one round trip less
         ck = !box_outside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
       }
-      const unsigned cb = __ballot_sync(0xffffffffu, ck);
+      // Chunks wholly inside the frustum: every point passes (box_inside is conservative), so nothing of them needs the
+      // per-voxel pass below.  Survivors = the chunk's points; their voxel box = the box of the chunk's tight point
+      // AABB (floor(x * inv_leaf) is monotone: the corners' voxels are the extreme voxels); their voxels go straight
+      // into the list, flagged "every point survives".
+      const bool in = ck && box_inside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+      const unsigned ib = __ballot_sync(0xffffffffu, in);
+      if (ib) {
+        const uint32_t nvi = in ? vb1 - vb0 : 0u;
+        uint32_t incl = nvi;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+          if (lane >= o) incl += t;
+        }
+        const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(&sh.list_count, tot);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (in) {
+          const uint32_t pb = __float_as_uint(lo.w), pe = __float_as_uint(hi.w);
+          surv_in += pe - pb;
+          if (want_hash)
+            for (uint32_t q = pb; q < pe; ++q) shash += mix64((uint64_t)(uint32_t)m.orig[q]);
+          bmin[0] = min(bmin[0], (int)floorf(fmul(lo.x, m.inv_leaf))); bmax[0] = max(bmax[0], (int)floorf(fmul(hi.x, m.inv_leaf)));
+          bmin[1] = min(bmin[1], (int)floorf(fmul(lo.y, m.inv_leaf))); bmax[1] = max(bmax[1], (int)floorf(fmul(hi.y, m.inv_leaf)));
+          bmin[2] = min(bmin[2], (int)floorf(fmul(lo.z, m.inv_leaf))); bmax[2] = max(bmax[2], (int)floorf(fmul(hi.z, m.inv_leaf)));
+        }
+        for (unsigned rest = ib; rest; rest &= rest - 1) {
+          const int src = __ffs(rest) - 1;
+          const uint32_t v0 = __shfl_sync(0xffffffffu, vb0, src), nvv = __shfl_sync(0xffffffffu, nvi, src);
+          const unsigned at0 = base + __shfl_sync(0xffffffffu, incl - nvi, src);
+          for (uint32_t k = lane; k < nvv; k += 32)
+            if (at0 + k < A.list_cap) vox_list[at0 + k] = (v0 + k) | kVoxInside;
+        }
+      }
+      const bool bd = ck && !in;  // cut by a plane (or not provably inside): its voxels are classified one by one
+      const unsigned cb = __ballot_sync(0xffffffffu, bd);
       if (cb) {
-        // candidate chunk -> descriptor {first voxel | inside flag, offset of its voxels in the flat candidate order};
+        // boundary chunk -> descriptor {first voxel, offset of its voxels in the flat candidate order};
         // one 64-bit atomic hands out descriptor slots (high word) and voxel offsets (low word) together, so
         // offsets ascend with the slot index
         uint32_t vb = 0, nv = 0;
-        if (ck) { vb = vb0; nv = vb1 - vb0; }
+        if (bd) { vb = vb0; nv = vb1 - vb0; }
         uint32_t incl = nv;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -441,11 +482,9 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(&sh.cand_state, ((unsigned long long)__popc(cb) << 32) | tot);
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (ck) {
-          // chunks wholly inside the frustum: every point passes, no voxel of it needs classifying
-          const bool in = box_inside(sh.planes, lo.x, lo.y, lo.z, hi.x, hi.y, hi.z);
+        if (bd) {
           const unsigned slot = (unsigned)(base >> 32) + __popc(cb & ((1u << lane) - 1));
-          const uint2 d = make_uint2(vb | (in ? kVoxInside : 0u), (uint32_t)base + incl - nv);
+          const uint2 d = make_uint2(vb, (uint32_t)base + incl - nv);
           if (slot < kDescShared) sh.chunk_desc[slot] = d;
           else chunk_list[slot] = d;
         }
@@ -457,9 +496,6 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
       atomicAdd(&A.phase_cycles[7], (unsigned long long)(clock64() - c1));
     }
   }
-  int bmin[3] = {INT_MAX, INT_MAX, INT_MAX}, bmax[3] = {INT_MIN, INT_MIN, INT_MIN};
-  unsigned surv = 0, surv_in = 0;
-  unsigned long long shash = 0;
   if (!brute) {
     // P2: the voxels of the candidate chunks in one flat order, cut into one contiguous segment per warp, one
     // lane per voxel, kCullUnroll blocks of 32 in flight.  Chunk inside the frustum: every point survives.
@@ -540,11 +576,11 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     for (unsigned jb = j_begin; jb < j_end; jb += 32 * kCullUnroll) {
       uint32_t uu[kCullUnroll], q1[kCullUnroll];
       int4 vx[kCullUnroll];
-      bool on[kCullUnroll], cin[kCullUnroll];
+      bool on[kCullUnroll];
 #pragma unroll
       for (int b = 0; b < kCullUnroll; ++b) {
         const unsigned j0 = jb + b * 32, j = j0 + lane;
-        on[b] = j < j_end; cin[b] = false; uu[b] = 0; q1[b] = 0; vx[b] = make_int4(0, 0, 0, 0);
+        on[b] = j < j_end; uu[b] = 0; q1[b] = 0; vx[b] = make_int4(0, 0, 0, 0);
         // The chunk of every candidate of the block, found by the warp together: a chunk holds at least one voxel,
         // so the chunks that start inside the block are among the 32 descriptors after c0, one per lane; the bit
         // mask of their starting positions turns "my descriptor" into a population count and two shuffles.
@@ -561,8 +597,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         const unsigned ly = __shfl_sync(0xffffffffu, dl.y, (nst - 1u) & 31u);
         if (nst) { d0 = make_uint2(lx, ly); c0 += nst; }
         if (on[b]) {
-          uu[b] = (d.x & kVoxMask) + (j - d.y);
-          cin[b] = (d.x & kVoxInside) != 0;
+          uu[b] = d.x + (j - d.y);
           vx[b] = m.vox[uu[b]];
           q1[b] = (uint32_t)m.vox[uu[b] + 1].w;
         }
@@ -572,8 +607,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         if (jb + b * 32 >= j_end) break;
         int cls = 0;  // 0 outside, 1 cut by a plane, 2 inside
         if (on[b]) {
-          cls = 2;
-          if (!cin[b]) {
+          {
             const float cx = ((float)vx[b].x + 0.5f) * m.leaf, cy = ((float)vx[b].y + 0.5f) * m.leaf,
                         cz = ((float)vx[b].z + 0.5f) * m.leaf;
             // conservative classifier (bounds in sh.vox_hi), not reference arithmetic: FMA allowed; the verdict is
@@ -1558,8 +1592,13 @@ __global__ void trig_kernel(const double* __restrict__ poses, int64_t nviews, Vi
   out[v] = t;
 }
 
-__device__ __forceinline__ void reset_view(const EvalArgs& A, ViewShared& sh, const double* pose, int v) {
-  if (pose) {
+__device__ __forceinline__ void reset_view(const EvalArgs& A, ViewShared& sh, const double* pose, const ViewDev* param_view,
+                                           int v) {
+  if (param_view) {
+    // tiny batches: the planes themselves are kernel parameters (computed by the host, same arithmetic)
+    if (threadIdx.x < 24) sh.planes[threadIdx.x] = param_view->planes[threadIdx.x];
+    if (threadIdx.x < 3) sh.origin[threadIdx.x] = param_view->origin[threadIdx.x];
+  } else if (pose) {
     // small batches: the planes of this view, computed here instead of by a planes_kernel launch
     if (threadIdx.x == 32) {
       ViewDev vd;
@@ -1636,24 +1675,19 @@ __device__ __forceinline__ void finish_group_view(const EvalArgs& A, int v, int*
   __syncthreads();
   if (!*s_last) return;
   __threadfence();
-  unsigned n[kSmallMaxGroup];
-#pragma unroll
-  for (int s = 0; s < kSmallMaxGroup; ++s) n[s] = 0;
-  for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) {
-    uint32_t seen = A.covered.vox ? A.covered.vox[w] : 0u;
-#pragma unroll
-    for (int s = 0; s < kSmallMaxGroup; ++s) {
-      if (s >= gsz) break;
-      const uint32_t mine = __ldcg(A.view_cov + (int64_t)(v0 + s) * A.cov_words + w);
-      n[s] += __popc(mine & ~seen);
-      seen |= mine;
+  // view s of the group: bits of its row that are neither covered nor in an earlier row (rows re-read per view: the
+  // groups are small and rolled loops keep this rarely run code short)
+#pragma unroll 1
+  for (int s = 0; s < gsz; ++s) {
+    unsigned n = 0;
+    for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) {
+      uint32_t seen = A.covered.vox ? A.covered.vox[w] : 0u;
+#pragma unroll 1
+      for (int t = 0; t < s; ++t) seen |= __ldcg(A.view_cov + (int64_t)(v0 + t) * A.cov_words + w);
+      n += __popc(__ldcg(A.view_cov + (int64_t)(v0 + s) * A.cov_words + w) & ~seen);
     }
-  }
-#pragma unroll
-  for (int s = 0; s < kSmallMaxGroup; ++s) {
-    if (s >= gsz) break;
-    const unsigned t = warp_sum(n[s]);
-    if ((threadIdx.x & 31) == 0 && t) atomicAdd(&s_gain[s], t);
+    n = warp_sum(n);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(&s_gain[s], n);
   }
   __syncthreads();
   if ((int)threadIdx.x < gsz) {
@@ -1667,7 +1701,7 @@ __device__ __forceinline__ void finish_group_view(const EvalArgs& A, int v, int*
 }
 
 // param_poses: the poses as kernel parameters (eval_views_small_kernel) or nullptr (planes_kernel has filled A.views)
-__device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double* param_poses) {
+__device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double* param_poses, const ViewDev* param_views) {
   ViewShared& sh = *reinterpret_cast<ViewShared*>(smem_raw);
   uint32_t* smem_grid = reinterpret_cast<uint32_t*>(smem_raw + ((sizeof(ViewShared) + 15) & ~size_t(15)));
   const ModelDev& m = A.m;
@@ -1711,7 +1745,7 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
     if (prof) t0 = clock64();
     if (A.view_cov && A.small)  // the view's coverage bitset starts empty (larger split-group batches: zeroed by the host)
       for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
-    reset_view(A, sh, param_poses ? param_poses + 7 * (int64_t)v : nullptr, v);
+    reset_view(A, sh, param_poses ? param_poses + 7 * (int64_t)v : nullptr, param_views ? param_views + v : nullptr, v);
     __syncthreads();
     if (prof) atomicAdd(&A.phase_cycles[12], (unsigned long long)(clock64() - t0));
     cull_view(A, sh, chunk_list, vox_list,
@@ -1876,17 +1910,19 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
     // small launch needs no memset: {work counter, ordered views, error views, CTAs done}
     __syncthreads();
     if (threadIdx.x == 0) {
-      __threadfence();
+      __threadfence_system();  // this CTA's results are in host memory before it counts as done
       if (atomicAdd(A.work_counter + 3, 1) == (int)gridDim.x - 1) {
         A.host_counters[0] = *(volatile int32_t*)A.ordered_count;
         A.host_counters[1] = *(volatile int32_t*)A.error_count;
         A.work_counter[0] = 0; A.work_counter[1] = 0; A.work_counter[2] = 0; A.work_counter[3] = 0;
+        __threadfence_system();
+        *(volatile int32_t*)(A.host_counters + 2) = A.epoch;  // the host may spin on this instead of synchronising
       }
     }
   }
 }
 
-__global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) { eval_views_body(A, nullptr); }
+__global__ void __launch_bounds__(1024, 1) eval_views_kernel(const EvalArgs A) { eval_views_body(A, nullptr, nullptr); }
 
 // Small batches: the poses travel with the launch (7 doubles per view) instead of through a host-to-device copy and a
 // planes_kernel launch.
@@ -1897,7 +1933,15 @@ struct PoseBlock {
 template <int NVIEWS>
 __global__ void __launch_bounds__(1024, 1) eval_views_small_kernel(const __grid_constant__ EvalArgs A,
                                                                    const __grid_constant__ PoseBlock<NVIEWS> P) {
-  eval_views_body(A, P.p);
+  eval_views_body(A, P.p, nullptr);
+}
+constexpr int kTinyMaxViews = 8;  // at most this many views: the host computes the planes (under a microsecond)
+struct PlaneBlock {
+  ViewDev v[kTinyMaxViews];
+};
+__global__ void __launch_bounds__(1024, 1) eval_views_tiny_kernel(const __grid_constant__ EvalArgs A,
+                                                                  const __grid_constant__ PlaneBlock P) {
+  eval_views_body(A, nullptr, P.v);
 }
 
 
@@ -1924,7 +1968,7 @@ __global__ void __launch_bounds__(1024, 1) ordered_views_kernel(const EvalArgs A
       cov_scratch = A.view_cov + (int64_t)v * A.cov_words;
       for (int64_t w = threadIdx.x; w < A.cov_words; w += blockDim.x) cov_scratch[w] = 0;
     }
-    reset_view(A, sh, nullptr, v);
+    reset_view(A, sh, nullptr, nullptr, v);
     __syncthreads();
     cull_view(A, sh, chunk_list, vox_list,
               reinterpret_cast<uint32_t*>(A.ray_buf + ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 3 * kRayQueueCap),
@@ -2121,10 +2165,13 @@ __global__ void fill_bytes_kernel(uint8_t* p, int64_t n, uint8_t v) {
 // ------------------------------------------------------------------------------------------------
 size_t eval_smem_bytes(uint32_t grid_words) { return ((sizeof(ViewShared) + 15) & ~size_t(15)) + (size_t)grid_words * 4; }
 int ray_queue_cap() { return kRayQueueCap; }
+int tiny_max_views() { return kTinyMaxViews; }
 size_t eval_smem_header_bytes() { return ((sizeof(ViewShared) + 15) & ~size_t(15)); }
 
 cudaError_t configure_kernels(size_t smem_bytes) {
   cudaError_t e = cudaFuncSetAttribute(eval_views_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(eval_views_tiny_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(eval_views_small_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes);
   if (e != cudaSuccess) return e;
@@ -2146,9 +2193,14 @@ void launch_trig(const double* d_poses, int64_t nviews, ViewTrig* out, cudaStrea
 void launch_eval(const EvalArgs& a, int ctas, int threads, size_t smem_bytes, cudaStream_t s) {
   eval_views_kernel<<<ctas, threads, smem_bytes, s>>>(a);
 }
-void launch_eval_small(const EvalArgs& a, const double* h_poses, int ctas, int threads, size_t smem_bytes, cudaStream_t s) {
+void launch_eval_small(const EvalArgs& a, const double* h_poses, const ViewDev* h_views, int ctas, int threads,
+                       size_t smem_bytes, cudaStream_t s) {
   // the launch copies the parameter block: the poses need not outlive this call
-  if (a.nviews <= 64) {
+  if (h_views && a.nviews <= kTinyMaxViews) {
+    PlaneBlock pb;
+    memcpy(pb.v, h_views, (size_t)a.nviews * sizeof(ViewDev));
+    eval_views_tiny_kernel<<<ctas, threads, smem_bytes, s>>>(a, pb);
+  } else if (a.nviews <= 64) {
     PoseBlock<64> pb;
     memcpy(pb.p, h_poses, (size_t)a.nviews * 7 * sizeof(double));
     eval_views_small_kernel<64><<<ctas, threads, smem_bytes, s>>>(a, pb);

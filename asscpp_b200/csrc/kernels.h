@@ -14,7 +14,9 @@ cudaError_t configure_kernels(size_t smem_bytes);
 void launch_planes(const double* d_poses, int64_t nviews, const FrustumConst& fc, ViewDev* views, cudaStream_t s);
 void launch_trig(const double* d_poses, int64_t nviews, ViewTrig* out, cudaStream_t s);
 void launch_eval(const EvalArgs& a, int ctas, int threads, size_t smem_bytes, cudaStream_t s);
-void launch_eval_small(const EvalArgs& a, const double* h_poses, int ctas, int threads, size_t smem_bytes, cudaStream_t s);
+void launch_eval_small(const EvalArgs& a, const double* h_poses, const ViewDev* h_views, int ctas, int threads,
+                       size_t smem_bytes, cudaStream_t s);
+int tiny_max_views();
 void launch_group_gain(const EvalArgs& a, int group, cudaStream_t s);
 void launch_ordered(const EvalArgs& a, int ctas, size_t smem_bytes, cudaStream_t s);
 void launch_or_words(uint32_t* dst, const uint32_t* src, int64_t words, cudaStream_t s);

@@ -121,9 +121,13 @@ void viewport_trig_host(const double pose[7], ViewTrig* out) {
 
 void frustum_planes_host(const AsscppParams& p, const double pose[7], float planes[24], float origin[3],
                          float corners[24]) {
+  frustum_planes_host_fc(frustum_const(p), pose, planes, origin, corners);
+}
+
+void frustum_planes_host_fc(const FrustumConst& fc, const double pose[7], float planes[24], float origin[3],
+                            float corners[24]) {
   // occlusion_culling.cpp:271-290 (tf::Matrix3x3(q) in double, cast to float) then
   // frustum_culling.cpp:82-141.  Mirrors planes_kernel in kernels.cu operation for operation.
-  FrustumConst fc = frustum_const(p);
   double x = pose[3], y = pose[4], z = pose[5], w = pose[6];
   double d = x * x + y * y + z * z + w * w;
   double s = 2.0 / d;

@@ -28,6 +28,8 @@ int preprocess_model(const float* xyz, int64_t n, const AsscppParams& p, ModelHo
 
 // frustum helpers (host; same arithmetic as planes_kernel)
 FrustumConst frustum_const(const AsscppParams& p);
+void frustum_planes_host_fc(const FrustumConst& fc, const double pose[7], float planes[24], float origin[3],
+                            float corners[24]);
 void frustum_planes_host(const AsscppParams& p, const double pose[7], float planes[24], float origin[3],
                          float corners[24]);
 // pointCloudViewportTransform constants (occlusion_culling.cpp:545-584) with the host's libm
