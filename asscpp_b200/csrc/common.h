@@ -7,7 +7,10 @@
 
 namespace asscpp {
 
-constexpr int kChunkMaxPoints = 128;  // leaf bucket of the cull hierarchy (whole voxels)
+#ifndef ASSCPP_CHUNK_MAX_POINTS
+#define ASSCPP_CHUNK_MAX_POINTS 128
+#endif
+constexpr int kChunkMaxPoints = ASSCPP_CHUNK_MAX_POINTS;  // leaf bucket of the cull hierarchy (whole voxels)
 constexpr int kSuperFanout = 32;      // chunks per super-chunk (one warp ballot)
 
 // Frustum constants that depend only on the parameters; evaluated once on the host with libm so

@@ -555,7 +555,10 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     const bool prof2 = A.phase_cycles != nullptr && threadIdx.x == 0;
     const long long d0 = prof2 ? clock64() : 0;
     // warps claim runs of kCullClaim candidates (cut voxels make the cost per candidate uneven)
-    constexpr unsigned kCullClaim = 256;
+#ifndef ASSCPP_CULL_CLAIM
+#define ASSCPP_CULL_CLAIM 256
+#endif
+    constexpr unsigned kCullClaim = ASSCPP_CULL_CLAIM;
     for (;;) {
     unsigned j_begin = 0;
     if (lane == 0) j_begin = atomicAdd(&sh.chunk_next, kCullClaim);
@@ -1282,11 +1285,14 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
       const int delta = p - pt;
       // cells of the target's 3x3x3 neighbourhood (delta = a + b P0 + c P01, |a|,|b|,|c| <= 1) never occlude
       // (quirk Q4: d^2 <= 3 < 4), whatever their occupancy: step over them
-      const int c = (delta > h01) - (delta < -h01);
-      const int rem = delta - c * P01;
-      const int b = (rem > h0) - (rem < -h0);
-      const int a = rem - b * P0;
-      const bool near27 = (abs(delta) <= near_max) & (abs(rem) <= P0 + 1) & (abs(a) <= 1);
+      auto in_near27 = [&](int dl) {
+        const int c = (dl > h01) - (dl < -h01);
+        const int rem = dl - c * P01;
+        const int b = (rem > h0) - (rem < -h0);
+        const int a = rem - b * P0;
+        return (abs(dl) <= near_max) & (abs(rem) <= P0 + 1) & (abs(a) <= 1);
+      };
+      const bool near27 = in_near27(delta);
       bool go_on = near27 & (delta != 0);
       if (!go_on) {
         const int qs0 = w_s01 & 0xffff, qs1 = w_s01 >> 16, qs2 = w_s2t2 & 0xffff;
@@ -1314,8 +1320,30 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
       if (go_on) {
         int pp = p;
         dda_step(tx, ty, tz, pp, dtx, dty, dtz, k0, k1, k2);
-        pbit = (unsigned)pp + bit_base;
-        walking = 1;
+        if (near27) {
+          // Inside the target's neighbourhood nothing occludes, occupied or not: walk on here -- the target is at most
+          // three cells away -- instead of parking on every occupied neighbour (surface voxels have several).  The
+          // same float steps in the same order; a ray that leaves the neighbourhood goes back to the step loop.
+#pragma unroll 1
+          for (int it = 0; it < 4; ++it) {
+            const int d2 = pp - pt;
+            if (d2 == 0) {                                                  // :551-552
+              steps_lo += (unsigned)(abs((int)(w_t01 & 0xffff) - (int)(w_s01 & 0xffff)) + abs((int)(w_t01 >> 16) - (int)(w_s01 >> 16)) +
+                                     abs((int)(w_s2t2 >> 16) - (int)(w_s2t2 & 0xffff)) + 1);
+              freed = 1;
+              go_on = false;
+              break;
+            }
+            if (!in_near27(d2)) break;
+            dda_step(tx, ty, tz, pp, dtx, dty, dtz, k0, k1, k2);
+          }
+        }
+        if (go_on) {
+          pbit = (unsigned)pp + bit_base;
+          walking = 1;
+        } else {
+          have = 0;
+        }
       } else {
         have = 0;
       }
