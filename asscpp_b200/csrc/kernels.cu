@@ -221,7 +221,8 @@ struct ViewShared {
   int view;
   int use_smem;
   unsigned long long cand_state;  // cull: descriptors handed out (high word) | candidate voxels so far (low word)
-  unsigned big_count, chunk_next, super_count, list_count, vis_count, ray_next, big_next;  // big_*: voxels handled one warp per voxel
+  unsigned big_count, chunk_next, super_count, list_count, vis_count, ray_next;  // big_count: voxels handled by lane groups
+  unsigned big_next;  // cull P1b: super-chunks handed out so far (beyond the first of every warp)
   unsigned survivors, visible, carry, unique, gain_p, gain_v, status;
   unsigned long long steps, vis_hash, surv_hash;
   unsigned long long acc[4];  // accuracy: fixed-point sums (depth hi / lo, z hi / lo)
@@ -412,7 +413,16 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     const unsigned nsup = sh.super_count;
     const bool listed = nsup <= kSuperListCap && !direct_supers;  // otherwise (huge frustum): walk all super-chunks again
     const int64_t nstep = listed ? (int64_t)nsup : m.n_super;
-    for (int64_t k = warp; k < nstep; k += nwarps) {
+    // the first super-chunk of a warp is its own, the others are claimed (inside chunks make the cost per super uneven)
+    bool first_super = true;
+    for (int64_t k = warp;;) {
+      if (!first_super) {
+        unsigned t = 0;
+        if (lane == 0) t = atomicAdd(&sh.big_next, 1u);
+        k = (int64_t)nwarps + __shfl_sync(0xffffffffu, t, 0);
+      }
+      first_super = false;
+      if (k >= nstep) break;
       int64_t sup = k;
       if (listed) {
         sup = sh.seg_last[k];
