@@ -657,7 +657,11 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         }
         const unsigned sb = __ballot_sync(0xffffffffu, cls == 1 && !bigcut);
         if (sb) {
-          if (cls == 1 && !bigcut) __stcg(cut + ncut + __popc(sb & ((1u << lane) - 1)), uu[b]);
+          if (cls == 1 && !bigcut) {
+            __stcg(cut + ncut + __popc(sb & ((1u << lane) - 1)), uu[b]);
+            // its points are read when this warp's claims are done: start them on their way from DRAM now
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(m.pts + (uint32_t)vx[b].w));
+          }
           ncut += (unsigned)__popc(sb);
           if (ncut + 32 > cut_cap) flush_cut();
         }
@@ -667,9 +671,11 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     const long long d1 = prof2 ? clock64() : 0;
     if (prof2) atomicAdd(&A.phase_cycles[10], (unsigned long long)ncut);
     flush_cut();
+    const long long d2 = prof2 ? clock64() : 0;
     // the cut voxels with many points (the top of the list): W lanes per voxel -- a whole warp each when there are
     // few, so that a handful of voxels does not become a chain of dependent loads, a quarter warp each when there are many
     __syncthreads();
+    if (prof2) atomicAdd(&A.phase_cycles[14], (unsigned long long)(clock64() - d2));  // wait for the other warps' claims
     {
       const unsigned nbig = sh.big_count;
       const int W = nbig <= (unsigned)nwarps ? 32 : (nbig <= 2u * nwarps ? 16 : 8);
@@ -1850,7 +1856,6 @@ __device__ __forceinline__ void eval_views_body(const EvalArgs& A, const double*
       if (prof) atomicAdd(&A.phase_cycles[13], (unsigned long long)(clock64() - t3));
       __syncthreads();
       const unsigned nbig = sh.big_count;
-      if (prof) atomicAdd(&A.phase_cycles[14], (unsigned long long)nbig);
       {
         const LaneGroup lg = lane_group(nbig, nwarps);
         for (unsigned i = warp * (32 / lg.W) + lg.sub; i < nbig; i += nwarps * (32 / lg.W))

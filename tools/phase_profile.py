@@ -26,6 +26,8 @@ for flags, name in ((0, "bucketed"), (A.EVAL_FORCE_GLOBAL, "global-grid")):
     print("  cull split: P1a supers %.1f%% P1b chunks %.1f%% P2 points %.1f%% of all phase cycles" % (100 * c[6] / tot, 100 * c[7] / tot, 100 * (c[0] - c[6] - c[7]) / tot))
     print("  P2 warp 0: classify loop %.1f%% cut-voxel points %.1f%% (rest = bbox/atomics/barrier wait); per view: candidates %.0f, cut voxels of warp 0 %.1f"
           % (100 * c[8] / tot, 100 * c[9] / tot, c[11] / max(c[4], 1), c[10] / max(c[4], 1)))
+    print("  warp 0 at the end of P2: waits %.1f%% of all phase cycles for the other warps; reset %.1f%%; visit pass A %.1f%%"
+          % (100 * c[14] / tot, 100 * c[12] / tot, 100 * c[13] / tot))
     print("%s: %.2f ms for %d views (%.0f VE/s); phases cull %.1f%% grid %.1f%% dda %.1f%% visit %.1f%%; "
           "busy/lifetime %.2f; cycles/view %.0f; smem views %d global %d; mean S %.0f U %.0f vis %.0f steps/ray %.1f words(mean) %.0f"
           % (name, ms, nv, nv / ms * 1e3, 100 * c[0] / tot, 100 * c[1] / tot, 100 * c[2] / tot, 100 * c[3] / tot,

@@ -27,7 +27,7 @@ for n in (2, 40, 400):
               views // reps, n, ph[5] / reps))
     print("   cull split per view: P1a %.0f P1b %.0f P2 classify %.0f P2 cut points %.0f; cut voxels(warp0) %.1f candidates %.0f" % (
         ph[6] / views, ph[7] / views, ph[8] / views, ph[9] / views, ph[10] / views, ph[11] / views))
-    print("   reset+planes %.0f; visit pass A (lane per voxel) %.0f of the visit, many-point voxels per view %.1f; group gains %.0f" % (
+    print("   reset+planes %.0f; visit pass A (lane per voxel) %.0f of the visit; warp 0 waits %.0f for the other warps at the end of P2; group gains %.0f" % (
         ph[12] / views, ph[13] / views, ph[14] / views, ph[15] / views))
     ne = res["survivors"] > 0
     print("   work per non-empty view: survivors %.0f rays %.0f visible %.0f steps %.0f cells %.0f; max survivors %d max rays %d" % (
