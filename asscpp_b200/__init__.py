@@ -11,13 +11,13 @@ import ctypes as C
 import numpy as np
 
 from . import _abi
-from ._abi import (ACCURACY_DTYPE, CLUSTER_DTYPE, EVAL_ACCURACY, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, RESULT_DTYPE,
+from ._abi import (ACCURACY_DTYPE, CLUSTER_DTYPE, EVAL_ACCURACY, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_HASH, EVAL_VIEW_CELLS, RESULT_DTYPE,
                    VS_GRID_GLOBAL, VS_GRID_SHARED, VS_ORDERED, EvalOpts, ModelInfo, Params)
 
 __all__ = [
     "CoverageContext", "CoveredSet", "Mesh", "AsscppError", "default_params", "synth_structure", "synth_views",
     "robot2sensor", "frustum_planes", "pose_rpy", "viewport_transform", "EVAL_HASH", "EVAL_BRUTE",
-    "EVAL_FORCE_GLOBAL", "EVAL_ACCURACY", "RESULT_DTYPE", "ACCURACY_DTYPE",
+    "EVAL_FORCE_GLOBAL", "EVAL_ACCURACY", "EVAL_VIEW_CELLS", "RESULT_DTYPE", "ACCURACY_DTYPE",
 ]
 
 SEED_STRUCTURE, SEED_POINTS, SEED_VIEWS = 0xA55C0001, 0xA55C0002, 0xA55C0003
@@ -323,6 +323,15 @@ class CoverageContext:
         out = np.zeros(nviews, ACCURACY_DTYPE)
         self._ck(self.L.asscpp_get_accuracy(self.h, out.ctypes.data_as(C.c_void_p), nviews))
         return out
+
+    def view_cells(self, nviews):
+        """Per-view coverage-voxel sets of the last evaluation issued with EVAL_VIEW_CELLS: bool array
+        [nviews, n_cov_voxels] (asscpp_get_view_cells)."""
+        words = self.L.asscpp_view_cells_words(self.h)
+        rows = np.zeros((nviews, max(words, 1)), np.uint32)
+        self._ck(self.L.asscpp_get_view_cells(self.h, rows.ctypes.data_as(C.c_void_p), nviews))
+        bits = np.unpackbits(rows.view(np.uint8), axis=1, bitorder="little")[:, :self.n_cov_voxels]
+        return bits.astype(bool)
 
     def eval_device(self, d_poses_ptr, nviews, covered=None, flags=0):
         """poses already in HBM (raw device pointer); results stay on the device."""

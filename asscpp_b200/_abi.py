@@ -12,7 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("ASSCPP_LIB") or os.path.join(_HERE, "lib", "libasscpp_b200.so")
 
 OK, EINVAL, ENODEVICE, ECUDA, ERANGE, ENOMEM, ESTATE, ENCCL = 0, -1, -2, -3, -4, -5, -6, -7
-EVAL_HASH, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_ACCURACY = 1, 2, 4, 8
+EVAL_HASH, EVAL_BRUTE, EVAL_FORCE_GLOBAL, EVAL_ACCURACY, EVAL_VIEW_CELLS = 1, 2, 4, 8, 16
 VS_GRID_SHARED, VS_GRID_GLOBAL, VS_ORDERED = 1, 2, 4
 
 
@@ -125,7 +125,7 @@ SYMBOLS = [
     "asscpp_comm_unique_id", "asscpp_comm_init", "asscpp_allgather_results", "asscpp_allreduce_or",
     "asscpp_comm_destroy", "asscpp_synth_structure_v1", "asscpp_synth_views_v1", "asscpp_robot2sensor",
     "asscpp_frustum_planes", "asscpp_get_accuracy", "asscpp_pose_rpy", "asscpp_viewport_transform",
-    "asscpp_uncovered_voxels", "asscpp_uncovered_voxels_ex", "asscpp_uncovered_clusters", "asscpp_uncovered_ids_noalloc",
+    "asscpp_uncovered_voxels", "asscpp_uncovered_voxels_ex", "asscpp_uncovered_clusters", "asscpp_uncovered_ids_noalloc", "asscpp_view_cells_words", "asscpp_get_view_cells",
     "asscpp_eval_groups", "asscpp_mesh_create", "asscpp_mesh_destroy", "asscpp_mesh_num_triangles", "asscpp_mesh_launch_count",
     "asscpp_mesh_last_error", "asscpp_mesh_filter", "asscpp_mesh_segments_free",
     "asscpp_covered_or_cloud", "asscpp_covered_invert_voxels", "asscpp_comm_init_all",
@@ -201,6 +201,8 @@ def load():
         "asscpp_robot2sensor": (i32, [f64p, f64p, f64p, f64p]),
         "asscpp_frustum_planes": (i32, [C.POINTER(Params), f64p, f32p, f32p]),
         "asscpp_get_accuracy": (i32, [vp, vp, i64]),
+        "asscpp_view_cells_words": (i64, [vp]),
+        "asscpp_get_view_cells": (i32, [vp, vp, i64]),
         "asscpp_pose_rpy": (i32, [f64p, f64p]),
         "asscpp_viewport_transform": (i32, [f64p, f32p, i64, f32p]),
         "asscpp_mesh_create": (i32, [i32, f32p, i64, i32p, i64, C.POINTER(vp)]),

@@ -133,7 +133,7 @@ struct AsscppCtx {
   std::vector<ViewTrig> h_trig;
   std::vector<AccRaw> h_acc;
   double acc_scale_d = 1, acc_scale_z = 1;
-  bool last_had_acc = false;
+  bool last_had_acc = false, last_had_cells = false;
   int64_t last_nviews = -1;
   std::vector<AsscppViewResult> h_results;
   // uncovered regions (allocated on first use)
@@ -290,6 +290,12 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   }
   c->last_nviews = nviews;
   c->last_had_acc = (flags & ASSCPP_EVAL_ACCURACY) != 0;
+  const bool want_cells = (flags & ASSCPP_EVAL_VIEW_CELLS) != 0;
+  if (want_cells && (accum_set >= 0 || nviews > c->split_group_max_views || group > kSmallMaxGroup)) {
+    c->err = "ASSCPP_EVAL_VIEW_CELLS: at most 4096 views per call, groups of at most 8, no accumulator set";
+    return ASSCPP_EINVAL;
+  }
+  c->last_had_cells = want_cells;
   c->small_pending = false; c->small_valid = false;
   if (nviews == 0) return ASSCPP_OK;
   const bool small = allow_small && takes_small_path(c, nviews, accum_set, group, h_poses);
@@ -353,7 +359,7 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   // runs the group's views one after the other.  Split-group mode makes every VIEW a work unit; each writes the
   // coverage-voxel bitset of its visible cloud and group_gain_kernel turns those into the union gains.
   const int64_t split_max = c->split_group_max_views;
-  if (group > 1 && nviews <= split_max && accum_set < 0) {
+  if ((group > 1 || want_cells) && nviews <= split_max && accum_set < 0) {
     const int64_t need = nviews * c->cov_words;
     if (need > c->view_cov_cap) {
       CU(c, cudaStreamSynchronize(c->stream));
@@ -733,6 +739,20 @@ int asscpp_get_results(AsscppCtx* c, AsscppViewResult* out, int64_t nviews) {
   int rc = fetch_results(c, nviews);
   if (rc) return rc;
   if (nviews > 0) memcpy(out, c->h_results.data(), (size_t)nviews * sizeof(AsscppViewResult));
+  return ASSCPP_OK;
+}
+
+int64_t asscpp_view_cells_words(const AsscppCtx* c) { return c ? c->cov_words : 0; }
+
+int asscpp_get_view_cells(AsscppCtx* c, uint32_t* rows, int64_t nviews) {
+  if (!c || (!rows && nviews > 0) || nviews < 0) return ASSCPP_EINVAL;
+  cudaSetDevice(c->device);
+  if (c->last_nviews < 0 || !c->last_had_cells) { c->err = "the last evaluation was not issued with ASSCPP_EVAL_VIEW_CELLS"; return ASSCPP_ESTATE; }
+  if (nviews > c->last_nviews) { c->err = "more rows requested than views evaluated"; return ASSCPP_EINVAL; }
+  if (int rc = finalize_small(c)) return rc;
+  if (nviews > 0)
+    CU(c, cudaMemcpyAsync(rows, c->d_view_cov, (size_t)nviews * c->cov_words * 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
   return ASSCPP_OK;
 }
 

@@ -2105,8 +2105,22 @@ __global__ void group_gain_kernel(uint32_t* __restrict__ view_cov, int64_t cov_w
   const int64_t g = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t v0 = g * group;
   if (v0 >= nviews) return;
-  uint32_t* acc = view_cov + v0 * cov_words;  // the first view's bitset becomes the running union
   const int64_t v1 = min(nviews, v0 + group);
+  if (group <= kSmallMaxGroup) {
+    // small groups: the earlier rows are re-read per view and every row stays what its view saw (asscpp_get_view_cells)
+    for (int64_t v = v0; v < v1; ++v) {
+      unsigned n = 0;
+      for (int64_t w = lane; w < cov_words; w += 32) {
+        uint32_t seen = covered ? covered[w] : 0u;
+        for (int64_t t = v0; t < v; ++t) seen |= view_cov[t * cov_words + w];
+        n += __popc(view_cov[v * cov_words + w] & ~seen);
+      }
+      n = warp_sum(n);
+      if (lane == 0) { results[v].gain_vox = n; gains[v].y = n; }
+    }
+    return;
+  }
+  uint32_t* acc = view_cov + v0 * cov_words;  // the first view's bitset becomes the running union
   for (int64_t v = v0; v < v1; ++v) {
     const uint32_t* mine = view_cov + v * cov_words;
     unsigned n = 0;

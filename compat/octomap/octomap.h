@@ -40,7 +40,7 @@ struct OcTreeKey {
   bool operator!=(const OcTreeKey& o) const { return !(*this == o); }
   uint16_t operator[](int i) const { return k[i]; }
   struct KeyHash {
-    size_t operator()(const OcTreeKey& key) const { return key.k[0] + 1337 * key.k[1] + 345637 * key.k[2]; }
+    size_t operator()(const OcTreeKey& key) const { return (size_t)key.k[0] + 1447 * (size_t)key.k[1] + 345637 * (size_t)key.k[2]; }
   };
 };
 typedef std::unordered_set<OcTreeKey, OcTreeKey::KeyHash> KeySet;

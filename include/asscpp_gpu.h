@@ -86,7 +86,10 @@ enum {
   ASSCPP_EVAL_HASH = 1u,        /* also compute vis_hash / surv_hash                               */
   ASSCPP_EVAL_BRUTE = 2u,       /* no bucket pre-cull: stream every point for every view           */
   ASSCPP_EVAL_FORCE_GLOBAL = 4u, /* keep every per-view grid in global memory (test / profiling)   */
-  ASSCPP_EVAL_ACCURACY = 8u      /* also reduce the accuracy terms of the visible set (asscpp_get_accuracy) */
+  ASSCPP_EVAL_ACCURACY = 8u,     /* also reduce the accuracy terms of the visible set (asscpp_get_accuracy) */
+  ASSCPP_EVAL_VIEW_CELLS = 16u   /* also keep, per view, the coverage voxels its visible cloud touches
+                                    (asscpp_get_view_cells); at most 4 096 views per call, groups of at most 8,
+                                    no accumulator set */
 };
 
 /* Accuracy terms of one viewpoint's visible cloud (ASSCPP_EVAL_ACCURACY).
@@ -160,6 +163,13 @@ typedef struct AsscppEvalOpts {
 } AsscppEvalOpts;
 int asscpp_eval_ex(AsscppCtx* ctx, const double* poses, int64_t nviews, const AsscppEvalOpts* opts);
 
+/* Per-view coverage-voxel sets of the last evaluation issued with ASSCPP_EVAL_VIEW_CELLS: nviews rows of
+ * asscpp_view_cells_words(ctx) 32-bit words, bit i of a row = the view's visible cloud has a point in the coverage voxel
+ * with compact id i (the ids of asscpp_uncovered_voxels).  This is what the per-voxel heuristics of the reference walk:
+ * the occupied octomap keys of a sensor's visible cloud (coverage_path_planning_heuristic.cpp:657-674 -- at the
+ * reference's volumetricVoxelRes = 0.5 m the octomap cell of a point is its coverage voxel).  Synchronises. */
+int64_t asscpp_view_cells_words(const AsscppCtx* ctx);
+int asscpp_get_view_cells(AsscppCtx* ctx, uint32_t* rows, int64_t nviews);
 /* accuracy terms of the last evaluation issued with ASSCPP_EVAL_ACCURACY (synchronises) */
 int asscpp_get_accuracy(AsscppCtx* ctx, AsscppViewAccuracy* out, int64_t nviews);
 

@@ -17,7 +17,7 @@
 //   displayProgress, findClusterOuterPoints   RViz output / never called by the planners: unavailable on this box
 // Heuristic types: SurfaceCoverageH, SurfaceCoveragewithOrientationH, SurfaceCoveragewithAccuracyH, VolumetricCoverageH.
 // InfoGainVolumetricH: see info_gain_b200.h (the reference's own block dereferences a pointer Node::Node(Node*) never
-// sets, sspp/src/node.cpp:43-68, so only its evidently intended form can be offered).
+// sets, sspp/src/node.cpp:43-68, so only its evidently intended form can be offered; opt-in, allowIntendedInfoGain()).
 //
 // No CPU fallback: construction throws when no sm_100 GPU is usable.
 #pragma once
@@ -30,6 +30,7 @@
 #include <map>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include <ros/ros.h>
@@ -106,6 +107,9 @@ class CoveragePathPlanningHeuristic : public Heuristic {
   // reference does (:344-346).  false = keep the union only as a covered set on the device (pointCloudDiff then ignores
   // the cloud it is handed and uses that set): no point traffic at all.
   bool appendGlobalCloud;
+  // InfoGainVolumetricH in its evidently intended form (info_gain_b200.h): a child inherits the tree of the node it
+  // was expanded from.  Off by default: calculateHeuristic then refuses the type and says why.
+  void allowIntendedInfoGain(bool on = true) { intended_info_gain_ = on; }
   OcclusionCulling* occlusionCulling() { return occlussionCulling; }
   AsscppMesh* mesh() { return mesh_; }
   int globalCoveredSet() const { return global_set_; }
@@ -153,6 +157,19 @@ class CoveragePathPlanningHeuristic : public Heuristic {
     double err_sum_z;              // sum of 0.0000285 z^2 over visibleCloud (calcAvgAccuracy one-argument form, :445-458)
     bool exact;                    // false: a view took the ordered replay (quirk Q5), group sum not union-exact
   };
+  struct InfoTree {                    // InfoGainVolumetricH: a node's octree as a flat array
+    std::vector<float> logodds;        // per compact coverage-voxel id; valid where known
+    std::vector<unsigned char> known;  // the cell has a leaf in the tree (octomap search() != NULL)
+  };
+  std::map<std::pair<int, const Node*>, InfoTree> info_trees_;  // by (node id, node->parent): survives astar.cpp:262's copy
+  std::vector<float> info_centres_;
+  int64_t info_cells_;
+  double modelVolume, modelTotalEntroby;
+  bool intended_info_gain_;
+  void info_gain_init();
+  void calculateInfoGain(Node* node);
+  static float oct_logodds(double p);
+  static double oct_probability(double l);
   OcclusionCulling* occlussionCulling;
   AsscppMesh* mesh_;
   bool debug, gradualVisualization;
@@ -183,3 +200,4 @@ class CoveragePathPlanningHeuristic : public Heuristic {
 }  // namespace SSPP
 
 #include "coverage_path_planning_heuristic_b200_impl.h"
+#include "info_gain_b200.h"

@@ -24,12 +24,13 @@ inline void CoveragePathPlanningHeuristic::init_defaults() {
   launches_scored_ = nodes_scored_ = 0;
   fillCloudFiltered = false;
   appendGlobalCloud = true;
+  info_cells_ = 0; modelVolume = 0; modelTotalEntroby = 0;
+  intended_info_gain_ = false;
 }
 
 inline void CoveragePathPlanningHeuristic::finish_init() {
-  if (heuristicType == InfoGainVolumetricH || heuristicType == SurfaceAreaCoverageH)
-    throw std::runtime_error("CoveragePathPlanningHeuristic: heuristic type not offered by this class "
-                             "(InfoGainVolumetricH: see info_gain_b200.h; SurfaceAreaCoverageH is commented out in the reference)");
+  if (heuristicType == SurfaceAreaCoverageH)
+    throw std::runtime_error("CoveragePathPlanningHeuristic: SurfaceAreaCoverageH is commented out in the reference");
   check(asscpp_covered_new(ctx(), &parent_set_));
   check(asscpp_covered_new(ctx(), &global_set_));
   check(asscpp_covered_new(ctx(), &scratch_set_));

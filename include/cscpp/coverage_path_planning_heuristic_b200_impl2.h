@@ -6,6 +6,15 @@ namespace SSPP {
 // coverage_path_planning_heuristic.cpp:425-1300
 inline void CoveragePathPlanningHeuristic::calculateHeuristic(Node* node) {
   if (node == NULL) return;
+  if (heuristicType == InfoGainVolumetricH) {
+    if (!intended_info_gain_)
+      throw std::runtime_error("CoveragePathPlanningHeuristic: the reference's InfoGainVolumetricH block copies "
+                               "*node->parent->octree (coverage_path_planning_heuristic.cpp:649), a pointer "
+                               "Node::Node(Node*) never sets (sspp/src/node.cpp:43-68): undefined behaviour, no result to "
+                               "reproduce.  allowIntendedInfoGain() enables the evidently intended form (info_gain_b200.h)");
+    calculateInfoGain(node);
+    return;
+  }
   const bool volumetric = heuristicType == VolumetricCoverageH;
   // the parent's accumulated cloud: cloud_filtered (:473), for VolumetricCoverageH its twin Node::voxels (:549)
   Node* parent = node->parent;

@@ -74,6 +74,7 @@ def lib(path=LIB_PATH):
     L.ref_planner_clusters.argtypes = [vp, f32p, i64, i32p, f64p, i64]; L.ref_planner_clusters.restype = i64
     L.ref_planner_set_accuracy_range.argtypes = [vp]; L.ref_planner_set_accuracy_range.restype = None
     L.ref_planner_search.argtypes = [vp, f64p, f64p, i64]; L.ref_planner_search.restype = i64
+    L.ref_planner_infogain_chain.argtypes = [vp, f64p, f64p, C.c_int, i64, f64p]; L.ref_planner_infogain_chain.restype = i64
     _libs[path] = L
     return L
 
@@ -246,3 +247,13 @@ class RefPlanner:
         rows = np.zeros((100000, 10), np.float64)
         n = self.L.ref_planner_search(self.h, _p(st, C.c_double), _p(rows, C.c_double), len(rows))
         return rows[:n].copy()
+
+    def infogain_chain(self, robot_poses, sensor_poses):
+        """InfoGainVolumetricH (heuristic.cpp:643-759, 1128-1225) of a chain of nodes, node i's parent = the real node
+        i-1 (the form in which the reference's block is well defined).  sensor_poses [k, ns, 7].
+        Rows {totalEntroby, coveredVolume, coverage, f_value, distance, coveredVoxelsNum}."""
+        rp = np.ascontiguousarray(robot_poses, np.float64).reshape(-1, 7)
+        sp = np.ascontiguousarray(sensor_poses, np.float64).reshape(len(rp), -1, 7)
+        out = np.zeros((len(rp), 6), np.float64)
+        self.L.ref_planner_infogain_chain(self.h, _p(rp, C.c_double), _p(sp, C.c_double), sp.shape[1], len(rp), _p(out, C.c_double))
+        return out

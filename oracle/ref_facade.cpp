@@ -383,4 +383,34 @@ int64_t ref_planner_search(void* h, const double start_xyz[3], double* rows, int
   return n;
 }
 
+// InfoGainVolumetricH (heuristic.cpp:643-759, 974-1085, 1128-1225) on a chain of k nodes: node 0 is a root, node i's parent
+// is node i-1 -- the REAL scored node, which owns the octree its block creates.  (Under the reference's own A* a child's
+// parent is the copy made at astar.cpp:262, whose octree pointer Node::Node(Node*) never sets, node.cpp:43-68: the
+// block is undefined there; on real parents it is the reference's code doing what it evidently means.)
+// out: k x 6 {totalEntroby, coveredVolume, coverage, f_value, distance, coveredVoxelsNum}
+int64_t ref_planner_infogain_chain(void* h, const double* robot_poses, const double* sensor_poses, int ns, int64_t k,
+                                   double* out) {
+  RefPlanner* r = static_cast<RefPlanner*>(h);
+  std::vector<SSPP::Node*> nodes;
+  for (int64_t i = 0; i < k; ++i) {
+    SSPP::Node* n = new SSPP::Node();
+    n->id = (int)i;
+    n->depth = (int)i;
+    n->parent = i ? nodes[(size_t)i - 1] : NULL;
+    n->pose.p = to_pose(robot_poses + 7 * i);
+    for (int s = 0; s < ns; ++s) {
+      Pose sp;
+      sp.p = to_pose(sensor_poses + 7 * (i * ns + s));
+      n->senPoses.push_back(sp);
+    }
+    r->heuristic->calculateHeuristic(n);
+    double* o = out + 6 * i;
+    o[0] = n->totalEntroby; o[1] = n->coveredVolume; o[2] = n->coverage; o[3] = n->f_value; o[4] = n->distance;
+    o[5] = (double)n->coveredVoxelsNum;
+    nodes.push_back(n);
+  }
+  for (size_t i = 0; i < nodes.size(); ++i) { delete nodes[i]->octree; delete nodes[i]; }
+  return k;
+}
+
 }  // extern "C"

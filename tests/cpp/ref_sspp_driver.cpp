@@ -12,6 +12,9 @@
 //   ref_sspp_driver grid    <pcd> <obj> sx sy sz  gx gy gz  res          one filtered sampling stage
 //   ref_sspp_driver dynamic <pcd> <obj> sx sy sz  gx gy gz  res dec      the whole adaptive sampling loop
 //   ref_sspp_driver astar   <pcd> <obj> <robot.txt> <cam0.txt> <cam1.txt> htype target tol batch   A* over a loaded space
+//   ref_sspp_driver infogain <pcd> <obj> <robot.txt> <cam0.txt> <cam1.txt> i0 i1 i2 ...   InfoGainVolumetricH (intended
+//                            form) along the chain of search-space rows i0 -> i1 -> ...: every child's parent is a COPY of
+//                            the scored node (Node::Node(Node*), as astar.cpp:262 makes it), not the node itself
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -91,6 +94,52 @@ int main(int argc, char** argv) {
         std::printf("NODE %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g %.17g\n", p->pose.p.position.x,
                     p->pose.p.position.y, p->pose.p.position.z, p->pose.p.orientation.x, p->pose.p.orientation.y,
                     p->pose.p.orientation.z, p->pose.p.orientation.w, p->coverage, p->f_value, p->distance);
+      std::printf("LAUNCHES %ld NODES %ld\n", heuristic.launchesScored(), heuristic.nodesScored());
+    } else if (mode == "infogain") {
+      if (argc < 9) return 2;
+      CoveragePathPlanningHeuristic heuristic(nh, obj, pcd, false, false, InfoGainVolumetricH);
+      {  // the type is refused, with the reason, until the intended form is asked for
+        Node probe;
+        try { heuristic.calculateHeuristic(&probe); std::printf("\nREFUSED no\n"); }
+        catch (const std::exception& e) { std::printf("\nREFUSED %s\n", e.what()); }
+      }
+      heuristic.allowIntendedInfoGain();
+      planner->setHeuristicFucntion(&heuristic);
+      planner->loadRegularGrid(argv[4], argv[5], argv[6]);
+      geometry_msgs::PoseArray rp;
+      std::vector<geometry_msgs::PoseArray> sp;
+      planner->getRobotSensorPoses(rp, sp);
+      heuristic.setMaxMinSensorAccuracy(sp);
+      std::printf("\nACCURACY %.17g %.17g\n", heuristic.occlusionCulling()->maxAccuracyError,
+                  heuristic.occlusionCulling()->minAccuracyError);
+      // the chain's poses by FILE row (the planner keeps its search space newest first)
+      std::vector<std::vector<geometry_msgs::Pose> > file_rows(3);
+      for (int f = 0; f < 3; ++f) {
+        FILE* fp = std::fopen(argv[4 + f], "r");
+        if (!fp) return 2;
+        double v[7];
+        while (std::fscanf(fp, "%lf %lf %lf %lf %lf %lf %lf", &v[0], &v[1], &v[2], &v[3], &v[4], &v[5], &v[6]) == 7) {
+          geometry_msgs::Pose q;
+          q.position.x = v[0]; q.position.y = v[1]; q.position.z = v[2];
+          q.orientation.x = v[3]; q.orientation.y = v[4]; q.orientation.z = v[5]; q.orientation.w = v[6];
+          file_rows[f].push_back(q);
+        }
+        std::fclose(fp);
+      }
+      Node* prev_copy = NULL;
+      for (int a = 7; a < argc; ++a) {
+        const size_t row = (size_t)std::atoi(argv[a]);
+        Node* n = new Node();
+        n->id = a - 7;
+        n->depth = a - 7;
+        n->parent = prev_copy;
+        n->pose.p = file_rows[0][row];
+        for (size_t s = 1; s < 3; ++s) { Pose q; q.p = file_rows[s][row]; n->senPoses.push_back(q); }
+        heuristic.calculateHeuristic(n);
+        std::printf("IG %.17g %.17g %.17g %.17g %.17g %d\n", n->totalEntroby, n->coveredVolume, n->coverage, n->f_value,
+                    n->distance, n->coveredVoxelsNum);
+        prev_copy = new Node(n);  // what the children of the next expansion see as their parent (astar.cpp:262)
+      }
       std::printf("LAUNCHES %ld NODES %ld\n", heuristic.launchesScored(), heuristic.nodesScored());
     } else {
       return 2;

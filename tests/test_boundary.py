@@ -165,3 +165,35 @@ def test_adaptive_sampling_loop_gpu_plugin_equals_reference_run(tmp_path, lib_bu
     rows = parse(out.stdout, "ROW")
     assert len(rows) == len(g["rows"])
     assert np.array_equal(rows, g["rows"])
+
+
+@pytest.mark.gpu
+def test_info_gain_intended_form_equals_reference_block_on_real_parents(tmp_path, lib_built, R, etihad, space_2p5):
+    """InfoGainVolumetricH.  The reference's block inherits `*node->parent->octree` (heuristic.cpp:649), a pointer the
+    node copy of astar.cpp:262 never gets (node.cpp:43-68): undefined under its own A*.  The plugin offers the evidently
+    intended form (include/cscpp/info_gain_b200.h, opt-in): visible cells from one launch per node, a child finds the
+    tree of the node it was expanded from even through that copy.  Checked against the reference's OWN block run on real
+    parents (oracle/_ref, where it is well defined): counts, volumes, coverage and distances equal, entropies and f equal
+    to the order of the double sums over a sensor's keys."""
+    exe = build_driver()
+    pcd, obj = write_model(tmp_path, etihad[0])
+    files = write_space(tmp_path, space_2p5)
+    chain = [600, 601, 610, 633, 700, 815, 816]
+    out = subprocess.run([exe, "infogain", pcd, obj] + files + [str(i) for i in chain], capture_output=True, text=True,
+                         timeout=1800)
+    assert out.returncode == 0, out.stderr[-2000:]
+    got = parse(out.stdout, "IG")
+    p = R.RefPlanner(obj, pcd, heuristic_type=5, target=20.0, tolerance=1.0, conn_radius=2.5)
+    p.load_grid(*files)
+    p.set_accuracy_range()
+    sens = np.stack([space_2p5["cam0"][chain], space_2p5["cam1"][chain]], 1)
+    want = p.infogain_chain(space_2p5["uav"][chain], sens)
+    p.close()
+    assert got.shape == want.shape == (len(chain), 6)
+    assert np.array_equal(got[:, [1, 2, 4, 5]], want[:, [1, 2, 4, 5]])   # coveredVolume, coverage, distance, coveredVoxelsNum
+    assert np.allclose(got[:, 0], want[:, 0], rtol=1e-13, atol=0) and np.allclose(got[:, 3], want[:, 3], rtol=1e-13, atol=0)
+    assert want[-1, 5] > want[0, 5] > 0
+    launches = [ln for ln in out.stdout.splitlines() if ln.startswith("LAUNCHES")][0].split()
+    assert int(launches[1]) == len(chain)  # one launch per scored node
+    refused = [ln for ln in out.stdout.splitlines() if ln.startswith("REFUSED")][0]
+    assert "undefined behaviour" in refused and "allowIntendedInfoGain" in refused  # off by default, and it says why

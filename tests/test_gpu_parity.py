@@ -612,3 +612,32 @@ def test_adaptive_sampling_host_loop(A, etihad):
     assert n == 2112
     mesh.close()
     m.close()
+
+
+def test_view_cells_equal_oracle(A, oracle_mod, etihad_ctx, etihad_oracle, space_2p5):
+    """ASSCPP_EVAL_VIEW_CELLS / asscpp_get_view_cells: per view, the coverage voxels its visible cloud touches (the
+    occupied octomap keys of coverage_path_planning_heuristic.cpp:657-674 at volumetricVoxelRes 0.5) -- small-batch
+    path, general path, grouped and not; the gains are unchanged by the flag."""
+    o = etihad_oracle
+    n_cov = etihad_ctx.n_cov_voxels
+    for n, group in ((6, 1), (40, 2), (600, 1), (600, 2)):
+        k = n // 2
+        poses = np.stack([space_2p5["cam0"][600:600 + k], space_2p5["cam1"][600:600 + k]], 1).reshape(-1, 7)
+        etihad_ctx.eval_ex(poses, group_size=group, flags=A.EVAL_VIEW_CELLS | A.EVAL_HASH)
+        cells = etihad_ctx.view_cells(n)
+        res = etihad_ctx.results(n)
+        etihad_ctx.eval_ex(poses, group_size=group, flags=A.EVAL_HASH)
+        plain = etihad_ctx.results(n)
+        for f in ("visible", "gain_pts", "gain_vox", "vis_hash"):
+            assert np.array_equal(res[f], plain[f]), (n, group, f)
+        assert cells.shape == (n, n_cov)
+        step = 1 if n <= 40 else 37
+        for v in range(0, n, step):
+            cp = np.zeros(o.pts_words(), np.uint64)
+            cv = np.zeros(o.vox_words(), np.uint64)
+            o.accumulate(poses[v:v + 1], cp, cv, min_visible=-1, nthreads=1)
+            want = np.unpackbits(cv.view(np.uint8), bitorder="little")[:n_cov].astype(bool)
+            assert np.array_equal(cells[v], want), (n, group, v)
+        assert cells.any()
+    with pytest.raises(A.AsscppError):
+        etihad_ctx.eval_ex(np.tile(space_2p5["cam0"][600], (5000, 1)), flags=A.EVAL_VIEW_CELLS)

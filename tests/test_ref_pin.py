@@ -185,3 +185,105 @@ def test_uncovered_regions_of_the_adaptive_loop(R, oracle_mod, etihad):
         start, size = oracle_mod.cluster_bb(ctr[lab_o == c], 0.5)
         assert boxes[c].tolist() == start.tolist() + size.tolist()
     p.close()
+
+
+IG_CHAIN = [600, 601, 610, 633, 700, 815, 816]
+
+
+def info_gain_chain_restated(oracle_mod, xyz, sp, chain, cells_of_view=None):
+    """InfoGainVolumetricH (heuristic.cpp:643-759, 974-1085, 1128-1225) restated on top of the oracle's visible sets, in the
+    form in which the block is well defined (a child's parent is the real scored node).  A sensor's occupied octomap keys
+    = the 0.5 m cells floor(2 x) of its visible points (<octomap coordToKey>), keyToCoord = (cell + 0.5) * 0.5, the tree a
+    dict of float32 log-odds, setNodeValue clamped to [logodds(0.5), logodds(0.9999999)].  Keys are walked in ascending
+    order (the reference walks an unordered set: same terms, another order of the double sums).
+    include/cscpp/info_gain_b200.h is this function in C++ with the visible cells coming from the GPU."""
+    import math
+    o = oracle_mod.Oracle(xyz)
+    f32 = np.float32
+    logodds = lambda p: f32(math.log(p / (1 - p)))
+    prob_of = lambda l: 1. - (1. / (1. + math.exp(float(l))))
+    # SSMaxMinAccuracy (occlusion_culling.cpp:477-520) over the whole search space
+    mx = 2.2250738585072014e-308
+    for cam in ("cam0", "cam1"):
+        for pose in sp[cam]:
+            vis = o.eval_view(pose)["visible"]
+            if len(vis):
+                mx = max(mx, float(o.accuracy_idx(pose, vis)[3]))
+    max_err = 0.0000285 * mx * mx
+    max_depth = math.sqrt(max_err / 0.0000285)
+    cells_all = np.unique(np.floor(xyz.astype(np.float64) * 2.0).astype(np.int64), axis=0)
+    model_volume = len(cells_all) * (0.5 * 0.5 * 0.5)
+    model_entropy = len(cells_all) * (-1 * (0.5) * (math.log(0.5) / math.log(2)))
+    lo, hi = logodds(0.5), logodds(0.9999999)
+    rows, prev, tree = [], None, {}
+    for i, k in enumerate(chain):
+        tree = dict(tree)
+        total = prev["total"] if prev else model_entropy
+        vol = prev["vol"] if prev else 0.0
+        nvox = prev["nvox"] if prev else 0
+        for cam in ("cam0", "cam1"):
+            pose = sp[cam][k]
+            if cells_of_view is not None:
+                cells = cells_of_view(pose)
+            else:
+                vis = o.eval_view(pose)["visible"]
+                cells = np.unique(np.floor(xyz[vis].astype(np.float64) * 2.0).astype(np.int64), axis=0) if len(vis) else np.zeros((0, 3), np.int64)
+            if len(cells) == 0:
+                continue
+            centres = ((cells.astype(np.float64) + 0.5) * 0.5).astype(np.float32)
+            depth = oracle_mod.viewport_transform(pose, centres)[:, 0]
+            # ascending compact id = ascending (k, j, i): the order info_gain_b200.h walks
+            order = np.lexsort((cells[:, 0], cells[:, 1], cells[:, 2]))
+            for j in order:
+                key = tuple(cells[j])
+                dist = min(float(depth[j]), max_depth) if float(depth[j]) > max_depth else float(depth[j])
+                norm_acc = (max_err - (0.0000285 * dist * dist * 0.5)) / max_err
+                if key in tree:
+                    prob = prob_of(tree[key])
+                    before = (-1 * prob * (math.log(prob) / math.log(2)))
+                    post = (norm_acc * prob) / ((norm_acc * prob) + ((1 - norm_acc) * (1 - prob)))
+                else:
+                    nvox += 1
+                    before = (-1 * (0.5) * (math.log(0.5) / math.log(2)))
+                    post = (norm_acc * 0.5) / ((norm_acc * 0.5) + ((1 - norm_acc) * (1 - 0.5)))
+                    vol += 0.5 * 0.5 * 0.5
+                total -= before
+                tree[key] = min(max(logodds(post), lo), hi)
+                total += (-1 * post * (math.log(post) / math.log(2)))
+        cov = (vol / model_volume) * 100
+        if prev:
+            d = float(np.sqrt(((sp["uav"][k][:3] - sp["uav"][chain[i - 1]][:3]) ** 2).sum()))
+            dist_total = prev["dist"] + d
+            f = prev["f"] + (total - prev["total"]) * math.exp(d * -0.2)
+        else:
+            dist_total, f = 0.0, total
+        prev = {"total": total, "vol": vol, "nvox": nvox, "f": f, "dist": dist_total}
+        rows.append([total, vol, cov, f, dist_total, nvox])
+    return np.array(rows)
+
+
+def test_info_gain_block_on_real_parents_restated(R, oracle_mod, etihad, space_2p5, tmp_path):
+    """The reference's own InfoGainVolumetricH block (compiled from /root/reference, against the stand-in octomap of
+    compat/) on a chain of nodes with real parents vs the restatement above: counts and volumes equal, entropies and f
+    equal to the order of the sums."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import reproduce_dsscpp as D
+    if not os.path.exists(D.OBJ):
+        pytest.skip("/root/reference is not mounted")
+    files = []
+    for key in ("uav", "cam0", "cam1"):
+        f = str(tmp_path / (key + ".txt"))
+        np.savetxt(f, space_2p5[key], fmt="%.17g")
+        files.append(f)
+    p = R.RefPlanner(D.OBJ, D.PCD, heuristic_type=5, target=20.0, tolerance=1.0, conn_radius=2.5)
+    p.load_grid(*files)
+    p.set_accuracy_range()
+    sens = np.stack([space_2p5["cam0"][IG_CHAIN], space_2p5["cam1"][IG_CHAIN]], 1)
+    ref_rows = p.infogain_chain(space_2p5["uav"][IG_CHAIN], sens)
+    p.close()
+    mine = info_gain_chain_restated(oracle_mod, etihad[0], space_2p5, IG_CHAIN)
+    assert np.array_equal(ref_rows[:, [1, 5]], mine[:, [1, 5]])            # coveredVolume, coveredVoxelsNum
+    assert np.array_equal(ref_rows[:, 2], mine[:, 2]) and np.array_equal(ref_rows[:, 4], mine[:, 4])  # coverage, distance
+    assert np.allclose(ref_rows[:, 0], mine[:, 0], rtol=1e-13, atol=0) and np.allclose(ref_rows[:, 3], mine[:, 3], rtol=1e-13, atol=0)
+    assert ref_rows[-1, 5] > ref_rows[0, 5] > 0 and ref_rows[-1, 0] < ref_rows[0, 0]
