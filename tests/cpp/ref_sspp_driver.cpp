@@ -77,7 +77,8 @@ int main(int argc, char** argv) {
       if (std::atoi(argv[10])) heuristic.batchSiblingsFrom(&planner->childList);  // the one added line of the batcher
       planner->loadRegularGrid(argv[4], argv[5], argv[6]);                        // coverage_heuristic_test.cpp:126
       planner->connectNodes();                                                    // :127
-      if (htype == SurfaceCoveragewithAccuracyH || htype == VolumetricCoverageH) {
+      if (htype == InfoGainVolumetricH) heuristic.allowIntendedInfoGain();  // the reference's own block is undefined here
+      if (htype == SurfaceCoveragewithAccuracyH || htype == VolumetricCoverageH || htype == InfoGainVolumetricH) {
         geometry_msgs::PoseArray rp;
         std::vector<geometry_msgs::PoseArray> sp;
         planner->getRobotSensorPoses(rp, sp);

@@ -197,3 +197,22 @@ def test_info_gain_intended_form_equals_reference_block_on_real_parents(tmp_path
     assert int(launches[1]) == len(chain)  # one launch per scored node
     refused = [ln for ln in out.stdout.splitlines() if ln.startswith("REFUSED")][0]
     assert "undefined behaviour" in refused and "allowIntendedInfoGain" in refused  # off by default, and it says why
+
+
+@pytest.mark.gpu
+def test_reference_astar_runs_info_gain_over_the_plugin(tmp_path, lib_built, etihad, space_2p5):
+    """The demo's default heuristic type under the reference's unmodified Astar::astarSearch: with the intended form
+    switched on the search runs to its coverage target (the reference itself cannot: undefined behaviour at
+    heuristic.cpp:649).  No reference result exists to compare with; checked here: it terminates, the path starts at
+    the start pose, coverage grows along the path and reaches the target, f (total entropy, a cost) falls."""
+    exe = build_driver()
+    pcd, obj = write_model(tmp_path, etihad[0])
+    files = write_space(tmp_path, space_2p5)
+    out = subprocess.run([exe, "astar", pcd, obj] + files + ["5", "3.0", "1.0", "0"], capture_output=True, text=True,
+                         timeout=1800)
+    assert out.returncode == 0, out.stderr[-2000:]
+    path = parse(out.stdout, "NODE")
+    assert len(path) >= 2
+    assert np.all(np.diff(path[:, 7]) >= 0) and path[-1, 7] >= 2.0     # coverage: coveredVolume / modelVolume * 100
+    assert np.all(np.diff(path[:, 8]) <= 0)                            # f: entropy-based cost
+
