@@ -114,6 +114,7 @@ struct AsscppCtx {
   uint4* d_ray_buf = nullptr;
   int64_t ray_cap = 0;
   size_t l2_persist_bytes = 0;  // persisting-L2 window over the ray queues (0: not set)
+  size_t l2_persist_max = 0;
   int walk_thresh = 16;
   int setup_iters = 1, halo_iters = 3;
   uint8_t* d_vstate = nullptr;
@@ -618,7 +619,10 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
     cudaDeviceGetAttribute(&max_persist, cudaDevAttrMaxPersistingL2CacheSize, device);
     const size_t ray_bytes = (size_t)3 * c->ray_cap * 32 * c->ctas * sizeof(uint4);
     if ((!pe || atoi(pe) != 0) && max_persist > 0) {
-      const size_t want = std::min<size_t>((size_t)max_persist, ray_bytes);
+      // (+ room for evict-last lines of the voxel lists when built with -DASSCPP_KEEP_LISTS: not adopted, kernels.cu)
+      size_t extra = 0;
+      if (const char* xe = getenv("ASSCPP_L2_PERSIST_EXTRA_MB")) extra = (size_t)std::max(0, atoi(xe)) << 20;
+      const size_t want = std::min<size_t>((size_t)max_persist, ray_bytes + extra);
       int max_window = 0;
       cudaDeviceGetAttribute(&max_window, cudaDevAttrMaxAccessPolicyWindowSize, device);
       if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) == cudaSuccess) {
@@ -627,6 +631,7 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
         attr.accessPolicyWindow.base_ptr = c->d_ray_buf;
         attr.accessPolicyWindow.num_bytes = std::min<size_t>(ray_bytes, (size_t)std::max(max_window, 0));
         attr.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)want / (double)std::max<size_t>(ray_bytes, 1));
+        c->l2_persist_max = (size_t)max_persist;
         attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
         attr.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
         if (cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &attr) == cudaSuccess) c->l2_persist_bytes = want;

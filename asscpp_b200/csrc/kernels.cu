@@ -37,6 +37,21 @@ __device__ __forceinline__ float fdiv(float a, float b) { return __fdiv_rn(a, b)
 // Model points are read once per view and never reused by the CTA; the per-CTA scratch (voxel lists, ray queues) is
 // rewritten every view and should stay in L2.  The point reads are marked evict-first (ld.global.cs) so that
 // they do not push dirty scratch lines out to DRAM.
+// The per-CTA voxel lists (occupied voxels, free voxels) are written once and read back one or two phases later; in
+// between the SM streams several hundred KB of model data through L2.  With -DASSCPP_KEEP_LISTS their stores carry an
+// L2 evict-last policy.  Measured (profiles/r02aa_keep_lists_ab.txt, 32 MB more persisting carve-out): DRAM writes
+// 1.25 -> 0.65 GB per 10 000-view launch, DRAM reads +0.67 GB (less L2 left for the model), 0.7 % slower -- not
+// adopted; plain stores are the default.
+__device__ __forceinline__ void st_list(uint32_t* a, uint32_t v) {
+#ifndef ASSCPP_KEEP_LISTS
+  *a = v;
+#else
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  asm volatile("st.global.L2::cache_hint.u32 [%0], %1, %2;" ::"l"(a), "r"(v), "l"(pol) : "memory");
+#endif
+}
+
 __device__ __forceinline__ float4 ld_pt(const float4* p) {
 #ifdef ASSCPP_NO_STREAM_POINTS
   return *p;
@@ -471,7 +486,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           const uint32_t v0 = __shfl_sync(0xffffffffu, vb0, src), nvv = __shfl_sync(0xffffffffu, nvi, src);
           const unsigned at0 = base + __shfl_sync(0xffffffffu, incl - nvi, src);
           for (uint32_t k = lane; k < nvv; k += 32)
-            if (at0 + k < A.list_cap) vox_list[at0 + k] = (v0 + k) | kVoxInside;
+            if (at0 + k < A.list_cap) st_list(vox_list + at0 + k, (v0 + k) | kVoxInside);
         }
       }
       const bool bd = ck && !in;  // cut by a plane (or not provably inside): its voxels are classified one by one
@@ -524,7 +539,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
       slot = __shfl_sync(0xffffffffu, slot, 0);
       if (emit) {
         const unsigned at = slot + __popc(ob & ((1u << lane) - 1));
-        if (at < A.list_cap) vox_list[at] = entry;
+        if (at < A.list_cap) st_list(vox_list + at, entry);
       }
     };
     uint32_t* cut = cut_list;  // this warp's list of voxels cut by a plane
@@ -707,7 +722,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
           bmin[0] = min(bmin[0], vx.x); bmin[1] = min(bmin[1], vx.y); bmin[2] = min(bmin[2], vx.z);
           bmax[0] = max(bmax[0], vx.x); bmax[1] = max(bmax[1], vx.y); bmax[2] = max(bmax[2], vx.z);
           const unsigned at = atomicAdd(&sh.list_count, 1u);
-          if (at < A.list_cap) vox_list[at] = u;
+          if (at < A.list_cap) st_list(vox_list + at, u);
         }
       }
       __syncwarp();
@@ -763,7 +778,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         slot = __shfl_sync(0xffffffffu, slot, 0);
         if (emit) {
           unsigned at = slot + __popc(eb & ((1u << lane) - 1));
-          if (at < A.list_cap) vox_list[at] = u;
+          if (at < A.list_cap) st_list(vox_list + at, u);
           // voxel coordinates as <PCL getGridCoordinates>: floor(x * inverse_leaf) (same value as m.vox[u])
           int vi = (int)floorf(fmul(p.x, m.inv_leaf)), vj = (int)floorf(fmul(p.y, m.inv_leaf)),
               vk = (int)floorf(fmul(p.z, m.inv_leaf));
@@ -1369,7 +1384,7 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
       unsigned base = 0;
       if (lane == 0) base = atomicAdd(&sh.vis_count, (unsigned)__popc(fb));
       base = __shfl_sync(0xffffffffu, base, 0);
-      if (freed) cand_list[base + __popc(fb & lt)] = u;
+      if (freed) st_list(cand_list + base + __popc(fb & lt), u);
     }
     unsigned idle = __ballot_sync(0xffffffffu, have == 0);
     if (idle && qhead < qtail) {
@@ -1434,7 +1449,7 @@ __device__ __forceinline__ void trace_rays_fast(const EvalArgs& A, ViewShared& s
             unsigned base = 0;
             if (lane == 0) base = atomicAdd(&sh.vis_count, (unsigned)__popc(cb));
             base = __shfl_sync(0xffffffffu, base, 0);
-            if (kind == 1) cand_list[base + __popc(cb & lt)] = uu;
+            if (kind == 1) st_list(cand_list + base + __popc(cb & lt), uu);
           }
           const unsigned wb = __ballot_sync(0xffffffffu, kind == 2);
           if (kind == 2) {

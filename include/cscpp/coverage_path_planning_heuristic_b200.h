@@ -162,6 +162,13 @@ class CoveragePathPlanningHeuristic : public Heuristic {
     std::vector<unsigned char> known;  // the cell has a leaf in the tree (octomap search() != NULL)
   };
   std::map<std::pair<int, const Node*>, InfoTree> info_trees_;  // by (node id, node->parent): survives astar.cpp:262's copy
+  struct InfoViews {                   // what one launch returns for the sensors of one node
+    std::vector<uint32_t> rows;        // per sensor: the coverage voxels its visible cloud touches
+    std::vector<AsscppViewResult> res;
+    std::vector<AsscppViewAccuracy> acc;
+  };
+  std::map<const Node*, InfoViews> info_cache_;  // siblings scored by the launch of the expansion's first child
+  const Node* info_cache_parent_;
   std::vector<float> info_centres_;
   int64_t info_cells_;
   double modelVolume, modelTotalEntroby;

@@ -26,6 +26,7 @@ inline void CoveragePathPlanningHeuristic::init_defaults() {
   appendGlobalCloud = true;
   info_cells_ = 0; modelVolume = 0; modelTotalEntroby = 0;
   intended_info_gain_ = false;
+  info_cache_parent_ = NULL;
 }
 
 inline void CoveragePathPlanningHeuristic::finish_init() {

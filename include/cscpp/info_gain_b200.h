@@ -70,22 +70,50 @@ inline void CoveragePathPlanningHeuristic::calculateInfoGain(Node* node) {
   const double res = volumetricVoxelRes;
 
   const int64_t words = asscpp_view_cells_words(ctx());
-  std::vector<uint32_t> rows((size_t)(words * (int64_t)std::max<size_t>(ns, 1)));
-  std::vector<AsscppViewResult> vres(std::max<size_t>(ns, 1));
-  std::vector<AsscppViewAccuracy> vacc(std::max<size_t>(ns, 1));
-  if (ns) {
-    std::vector<double> p(7 * ns);
-    for (size_t s = 0; s < ns; ++s) OcclusionCulling::pack(node->senPoses[s].p, &p[7 * s]);
-    AsscppEvalOpts o;
-    std::memset(&o, 0, sizeof(o));
-    o.covered_set = -1; o.accum_set = -1; o.group_size = 1;
-    o.flags = (uint32_t)(ASSCPP_EVAL_VIEW_CELLS | ASSCPP_EVAL_ACCURACY);
-    check(asscpp_eval_ex(ctx(), p.data(), (int64_t)ns, &o));
-    check(asscpp_get_results(ctx(), vres.data(), (int64_t)ns));
-    check(asscpp_get_accuracy(ctx(), vacc.data(), (int64_t)ns));
-    check(asscpp_get_view_cells(ctx(), rows.data(), (int64_t)ns));
-    launches_scored_ += 1;
+  // the visible clouds of this node's sensors: from the cache of the expansion's batch, or one launch -- for this
+  // node alone, or (batchSiblingsFrom) for it and every not yet scored sibling in Astar::childList
+  InfoViews mine;
+  std::map<const Node*, InfoViews>::iterator hit = info_cache_.find(node);
+  if (hit != info_cache_.end() && info_cache_parent_ == parent) {
+    mine.rows.swap(hit->second.rows); mine.res.swap(hit->second.res); mine.acc.swap(hit->second.acc);
+    info_cache_.erase(hit);
+  } else {
+    std::vector<Node*> group(1, node);
+    if (sibling_source_ && parent)
+      for (Node* sib = *sibling_source_; sib != NULL; sib = sib->next)
+        if (sib != node && sib->parent == parent && sib->senPoses.size() == ns) group.push_back(sib);
+    info_cache_.clear();
+    info_cache_parent_ = parent;
+    const size_t nv = ns * group.size();
+    if (nv > 4096) group.resize(std::max<size_t>(1, 4096 / std::max<size_t>(ns, 1)));  // the limit of ASSCPP_EVAL_VIEW_CELLS
+    const size_t nviews = ns * group.size();
+    std::vector<uint32_t> rows((size_t)words * std::max<size_t>(nviews, 1));
+    std::vector<AsscppViewResult> vres(std::max<size_t>(nviews, 1));
+    std::vector<AsscppViewAccuracy> vacc(std::max<size_t>(nviews, 1));
+    if (nviews) {
+      std::vector<double> p(7 * nviews);
+      for (size_t i = 0; i < group.size(); ++i)
+        for (size_t s = 0; s < ns; ++s) OcclusionCulling::pack(group[i]->senPoses[s].p, &p[7 * (i * ns + s)]);
+      AsscppEvalOpts o;
+      std::memset(&o, 0, sizeof(o));
+      o.covered_set = -1; o.accum_set = -1; o.group_size = 1;
+      o.flags = (uint32_t)(ASSCPP_EVAL_VIEW_CELLS | ASSCPP_EVAL_ACCURACY);
+      check(asscpp_eval_ex(ctx(), p.data(), (int64_t)nviews, &o));
+      check(asscpp_get_results(ctx(), vres.data(), (int64_t)nviews));
+      check(asscpp_get_accuracy(ctx(), vacc.data(), (int64_t)nviews));
+      check(asscpp_get_view_cells(ctx(), rows.data(), (int64_t)nviews));
+      launches_scored_ += 1;
+    }
+    for (size_t i = 0; i < group.size(); ++i) {
+      InfoViews& dst = i == 0 ? mine : info_cache_[group[i]];
+      dst.rows.assign(rows.begin() + (size_t)words * ns * i, rows.begin() + (size_t)words * ns * (i + 1));
+      dst.res.assign(vres.begin() + ns * i, vres.begin() + ns * (i + 1));
+      dst.acc.assign(vacc.begin() + ns * i, vacc.begin() + ns * (i + 1));
+    }
   }
+  const std::vector<uint32_t>& rows = mine.rows;
+  const std::vector<AsscppViewResult>& vres = mine.res;
+  const std::vector<AsscppViewAccuracy>& vacc = mine.acc;
   nodes_scored_ += 1;
 
   std::vector<size_t> ids;

@@ -208,11 +208,17 @@ def test_reference_astar_runs_info_gain_over_the_plugin(tmp_path, lib_built, eti
     exe = build_driver()
     pcd, obj = write_model(tmp_path, etihad[0])
     files = write_space(tmp_path, space_2p5)
-    out = subprocess.run([exe, "astar", pcd, obj] + files + ["5", "3.0", "1.0", "0"], capture_output=True, text=True,
-                         timeout=1800)
-    assert out.returncode == 0, out.stderr[-2000:]
-    path = parse(out.stdout, "NODE")
+    paths, launches = [], []
+    for batch in ("0", "1"):  # one launch per child / one per expansion (the batcher hook): the same numbers
+        out = subprocess.run([exe, "astar", pcd, obj] + files + ["5", "3.0", "1.0", batch], capture_output=True, text=True,
+                             timeout=1800)
+        assert out.returncode == 0, out.stderr[-2000:]
+        paths.append(parse(out.stdout, "NODE"))
+        launches.append([int(x) for x in [ln for ln in out.stdout.splitlines() if ln.startswith("LAUNCHES")][0].split()[1::2]])
+    path = paths[0]
     assert len(path) >= 2
     assert np.all(np.diff(path[:, 7]) >= 0) and path[-1, 7] >= 2.0     # coverage: coveredVolume / modelVolume * 100
     assert np.all(np.diff(path[:, 8]) <= 0)                            # f: entropy-based cost
+    assert np.array_equal(paths[0], paths[1])
+    assert launches[0][1] == launches[1][1] and launches[1][0] < launches[0][0]  # same nodes scored, fewer launches
 
