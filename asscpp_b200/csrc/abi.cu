@@ -601,6 +601,20 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
   }
   if (cells_cap > 2147483647.0) cells_cap = 2147483647.0;
   c->grid_cap_words = (int64_t)(cells_cap / 32.0) + 2;
+  // Coarse lattices: no view's grid can be larger than the frustum's cell capacity, so the kernels ask for no more
+  // shared memory than that (the rest of the SM's 256 KB stays L1 for the voxel table and the point runs).
+  // ASSCPP_FULL_SMEM=1 keeps the full request (A/B).
+  if (!getenv("ASSCPP_FULL_SMEM")) {
+    const int64_t need = ((c->grid_cap_words + 63) / 64) * 64;
+    if (need < (int64_t)c->eval_grid_words) {
+      c->eval_grid_words = (uint32_t)need;
+      c->eval_smem_bytes_ = eval_smem_bytes(c->eval_grid_words);
+    }
+    if (need < (int64_t)c->smem_grid_words) {
+      c->smem_grid_words = (uint32_t)need;
+      c->smem_bytes = eval_smem_bytes(c->smem_grid_words);
+    }
+  }
   c->chunk_cap = std::max<int64_t>(m.n_chunks, 1);
   c->list_cap = m.n_vox + m.n / 32 + m.n_chunks + 64;
   c->cov_words = c->vox_words;
