@@ -641,3 +641,36 @@ def test_view_cells_equal_oracle(A, oracle_mod, etihad_ctx, etihad_oracle, space
         assert cells.any()
     with pytest.raises(A.AsscppError):
         etihad_ctx.eval_ex(np.tile(space_2p5["cam0"][600], (5000, 1)), flags=A.EVAL_VIEW_CELLS)
+
+
+def test_view_cells_with_a_replayed_view(A, oracle_mod, monkeypatch):
+    """ASSCPP_EVAL_VIEW_CELLS when a view of the batch takes the ordered replay (quirk Q5): the replay rewrites that
+    view's row; the one-launch path falls back to the general one.  Scene of test_carry_inside_large_batch."""
+    rng = np.random.default_rng(5)
+    xyz = np.concatenate([np.array([(42, 6, 2), (14, 2, 2), (2.5, 2, 2), (14, 3, 6)], np.float32),
+                          (rng.random((5000, 3)) * np.array([60, 30, 12]) + np.array([0, -40, 0])).astype(np.float32)])
+    pa = A.default_params(leaf=4.0, far_dist=60.0, cov_leaf=2.0)
+    po = oracle_mod.make_params(leaf=4.0, far=60.0, cov_leaf=2.0)
+    poses = np.array([[1, 2, 2, 0, 0, 0, 1.0], [1, -20, 2, 0, 0, 0, 1.0], [5, -30, 6, 0, 0, 0.38268343, 0.92387953],
+                      [1, 2, 2, 0, 0, 0, 1.0]])
+    orc = oracle_mod.Oracle(xyz, po)
+    want = []
+    for v in range(len(poses)):
+        cp = np.zeros(orc.pts_words(), np.uint64)
+        cv = np.zeros(orc.vox_words(), np.uint64)
+        orc.accumulate(poses[v:v + 1], cp, cv, min_visible=-1, nthreads=1)
+        want.append(np.unpackbits(cv.view(np.uint8), bitorder="little")[:orc.n_cov].astype(bool))
+    want = np.array(want)
+    for no_small in (False, True):
+        if no_small:
+            monkeypatch.setenv("ASSCPP_NO_SMALL", "1")
+        ctx = A.CoverageContext(xyz, pa)
+        monkeypatch.delenv("ASSCPP_NO_SMALL", raising=False)
+        for group in (1, 2):
+            ctx.eval_ex(poses, group_size=group, flags=A.EVAL_VIEW_CELLS | A.EVAL_HASH)
+            cells = ctx.view_cells(len(poses))
+            res = ctx.results(len(poses))
+            assert res["carry"][0] > 0 and (res["status"][0] & A.VS_ORDERED)
+            assert np.array_equal(cells, want), (no_small, group)
+        ctx.close()
+    assert want.any()
