@@ -115,6 +115,7 @@ struct AsscppCtx {
   int64_t ray_cap = 0;
   size_t l2_persist_bytes = 0;  // persisting-L2 window over the ray queues (0: not set)
   size_t l2_persist_max = 0;
+  int chunk_cull = 0;  // coarse lattice (>= 16 points per occupied voxel): cull boundary chunks chunk by chunk
   int walk_thresh = 16;
   int setup_iters = 1, halo_iters = 3;
   uint8_t* d_vstate = nullptr;
@@ -339,6 +340,7 @@ int run_eval(AsscppCtx* c, const double* d_poses, int64_t nviews, int covered_se
   a.trig = small ? c->d_small->trig : c->d_trig;
   a.acc = (flags & ASSCPP_EVAL_ACCURACY) ? c->d_acc : nullptr;
   a.small = small ? 1 : 0;
+  a.chunk_cull = c->chunk_cull;
   a.fc = c->fc;
   a.host_gains = small ? c->d_small->gains : nullptr;
   a.host_counters = small ? c->d_small->counters : nullptr;
@@ -653,6 +655,8 @@ int asscpp_create(int device, const float* xyz, int64_t n, const AsscppParams* p
       cudaGetLastError();
     }
   }
+  c->chunk_cull = (m.n_vox > 0 && m.n >= 16 * m.n_vox) ? 1 : 0;
+  if (const char* e = getenv("ASSCPP_CHUNK_CULL")) c->chunk_cull = atoi(e) != 0;
   if (const char* e = getenv("ASSCPP_HALO_ITERS")) c->halo_iters = std::max(0, std::min(64, atoi(e)));
   if (const char* e = getenv("ASSCPP_SETUP_ITERS")) c->setup_iters = std::max(1, std::min(64, atoi(e)));
   if (const char* e = getenv("ASSCPP_SPLIT_GROUP_MAX")) c->split_group_max_views = std::max(0, atoi(e));

@@ -118,6 +118,7 @@ struct EvalArgs {
   // small batches (the A* use), one launch for the whole evaluation: poses arrive as kernel parameters and the planes are
   // computed by the CTA that takes the view; the last view of a group to finish computes the group's union gains; gains
   // and counters are mirrored into mapped host memory; the last CTA resets the device counters for the next launch
+  int chunk_cull;            // coarse lattice: boundary chunks are culled chunk by chunk (no per-voxel pass)
   int small;                 // 1: eval_views_small_kernel
   int32_t epoch;             // written to host_counters[2] when the launch is complete
   FrustumConst fc;

@@ -383,6 +383,9 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
   const ModelDev& m = A.m;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const bool brute = (A.flags & ASSCPP_EVAL_BRUTE) != 0;
+  // coarse lattices (a leaf bucket is a handful of voxels): the boundary chunks' points are tested chunk by chunk with the
+  // brute loop below instead of voxel by voxel (P2) -- the per-voxel cube test can reject nothing a chunk's tight box did not
+  const bool by_chunk = A.chunk_cull != 0 && !brute;
   const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
   if (threadIdx.x < 6) {
     // Voxel cube vs plane k, centre / radius form: every point of a voxel lies within h = leaf/2 + slack of the
@@ -509,7 +512,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
         base = __shfl_sync(0xffffffffu, base, 0);
         if (bd) {
           const unsigned slot = (unsigned)(base >> 32) + __popc(cb & ((1u << lane) - 1));
-          const uint2 d = make_uint2(vb, (uint32_t)base + incl - nv);
+          const uint2 d = by_chunk ? make_uint2((uint32_t)c, 0u) : make_uint2(vb, (uint32_t)base + incl - nv);
           if (slot < kDescShared) sh.chunk_desc[slot] = d;
           else chunk_list[slot] = d;
         }
@@ -521,7 +524,7 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
       atomicAdd(&A.phase_cycles[7], (unsigned long long)(clock64() - c1));
     }
   }
-  if (!brute) {
+  if (!brute && !by_chunk) {
     // P2: the voxels of the candidate chunks in one flat order, cut into one contiguous segment per warp, one
     // lane per voxel, kCullUnroll blocks of 32 in flight.  Chunk inside the frustum: every point survives.
     // Otherwise the voxel's cube is classified against the planes (centre / radius form with the per-view
@@ -734,15 +737,16 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     }
   }
   // brute mode: exact test of every point, 32 points per warp step
-  const int64_t nwork = brute ? m.n_chunks : 0;
+  const int64_t nwork = brute ? m.n_chunks : (by_chunk ? (int64_t)(sh.cand_state >> 32) : 0);
   for (;;) {
     // chunks are handed out one at a time: inside chunks are cheap, boundary chunks are not
     unsigned w = 0;
     if (lane == 0) w = atomicAdd(&sh.chunk_next, 1u);
     w = __shfl_sync(0xffffffffu, w, 0);
     if ((int64_t)w >= nwork) break;
+    const int64_t ch = by_chunk ? (int64_t)(w < kDescShared ? sh.chunk_desc[w].x : chunk_list[w].x) : (int64_t)w;
     uint32_t pb, pe;
-    pb = __float_as_uint(m.chunk_lo[w].w); pe = __float_as_uint(m.chunk_hi[w].w);
+    pb = __float_as_uint(m.chunk_lo[ch].w); pe = __float_as_uint(m.chunk_hi[ch].w);
     for (uint32_t base0 = pb; base0 < pe; base0 += 128) {
       // four independent 512-byte loads in flight per warp before any is consumed (latency, not bandwidth,
       // bounds this phase: a chunk holds at most kChunkMaxPoints = 128 points unless it is one big voxel)
