@@ -378,14 +378,15 @@ __device__ __forceinline__ unsigned warp_sum(unsigned v) { return __reduce_add_s
 // P1 + P2: cull.  Fills sh.survivors / bb_* / surv_hash and the per-CTA list of occupied voxels
 // (duplicates possible when a voxel's points straddle two 32-point loads; P3 removes them).
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list,
-                          uint32_t* cut_list, unsigned cut_cap) {
+template <bool BY_CHUNK>
+__device__ __forceinline__ void cull_view_t(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list,
+                                            uint32_t* cut_list, unsigned cut_cap) {
   const ModelDev& m = A.m;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const bool brute = (A.flags & ASSCPP_EVAL_BRUTE) != 0;
   // coarse lattices (a leaf bucket is a handful of voxels): the boundary chunks' points are tested chunk by chunk with the
   // brute loop below instead of voxel by voxel (P2) -- the per-voxel cube test can reject nothing a chunk's tight box did not
-  const bool by_chunk = A.chunk_cull != 0 && !brute;
+  const bool by_chunk = BY_CHUNK && !brute;  // (a template parameter: the fine-lattice path compiles exactly as without it)
   const bool want_hash = (A.flags & ASSCPP_EVAL_HASH) != 0;
   if (threadIdx.x < 6) {
     // Voxel cube vs plane k, centre / radius form: every point of a voxel lies within h = leaf/2 + slack of the
@@ -804,6 +805,13 @@ __device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uin
     if (lane == 0 && shash) atomicAdd(&sh.surv_hash, shash);
   }
   __syncthreads();
+}
+
+// two instances, chosen per model: the fine-lattice one compiles exactly as it did before the coarse form existed
+__device__ __forceinline__ void cull_view(const EvalArgs& A, ViewShared& sh, uint2* chunk_list, uint32_t* vox_list,
+                                          uint32_t* cut_list, unsigned cut_cap) {
+  if (A.chunk_cull) cull_view_t<true>(A, sh, chunk_list, vox_list, cut_list, cut_cap);
+  else cull_view_t<false>(A, sh, chunk_list, vox_list, cut_list, cut_cap);
 }
 
 // ------------------------------------------------------------------------------------------------

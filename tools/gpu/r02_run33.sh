@@ -1,0 +1,10 @@
+#!/bin/bash
+# Round 2, GPU call: same-box A/B on config 3 of the library before and after the chunk-by-chunk cull (which config 3 does not use)
+set -u
+O=gpurun_out/${RUN_TAG:-r02ak}
+mkdir -p $O
+for rep in 1 2; do for v in base prechunk; do
+  if [ $v = base ]; then export ASSCPP_LIB=$PWD/asscpp_b200/lib/libasscpp_b200.so; else export ASSCPP_LIB=$PWD/asscpp_b200/lib/variants/lib_$v.so; fi
+  timeout 600 python bench.py --steps 8 --warmup 3 --no-cpu-baseline > $O/bench_${v}_$rep.json 2> $O/bench_${v}_$rep.err
+  python -c "import json;d=json.loads(open('$O/bench_${v}_$rep.json').read().strip().splitlines()[-1]);print('$v rep $rep',round(d['value']),round(d['e2e']['value']))"
+done; done | tee $O/ab.txt
